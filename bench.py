@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""bench.py -- pooled rows/sec of the fused gather + sequence_pool + CVM front end.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl reference]
+
+One "step" = one pass of the hot path over one synthetic batch (all slots, ONE kernel
+launch).  Default workload: BASELINE.json configs[1] (DeepFM: 39 slots, one shared
+1e8 x 16 fp32 table, batch 8192, Zipf ids, SUM + CVM).  N > 1 (torchrun): every rank
+holds a replica of the table and its own batches -- weak scaling, no data-path
+collective (the row-sharded mode is measured by --workload cfg4).
+
+Prints ONE JSON line (contract in the task statement): value = whole-job pooled rows/s
+with inputs resident in HBM; e2e = same metric through the host-buffer call (H2D of ids
++ LoD, D2H of the pooled block inside the timed region); roofline for the fused kernel
+from CUDA events; cpu_baseline = the reference CPU arithmetic timed on this box's cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "pooled rows/sec (gather+seqpool+CVM)"
+UNIT = "pooled_rows/s"
+N_BATCHES = 16  # distinct pre-generated batches the timed loop rotates through
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _traffic_from_profiles(workload):
+    """dram bytes per launch from the committed ncu summary, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(workload)
+    return None
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons via NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv = nv
+            # torch's device index follows CUDA_VISIBLE_DEVICES; map through the UUID-less simple case
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def sample(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+                     0x4: "sw_power_cap", 0x80: "hw_power_brake", 0x2: "applications_clocks_setting",
+                     0x100: "display_clock_setting", 0x10: "sync_boost"}
+            for bit, name in names.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def start(self):
+        def loop():
+            while not self._stop.is_set():
+                self.sample()
+                time.sleep(0.002)
+        self._t = threading.Thread(target=loop, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def _env_rank():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def _workload_name(cfg):
+    return (f"{cfg.name}: {cfg.slots} slots, {'shared' if cfg.shared_table else 'per-slot'} {cfg.rows} x {cfg.dim} "
+            f"{cfg.dtype} table, batch {cfg.batch}, Zipf(1.05) ids, mean {cfg.mean_len} ids/seq, "
+            f"{'/'.join(sorted(set(cfg.pooltypes)))} pool"
+            f"{' + CVM' if cfg.use_cvm else (' + CVM(strip)' if cfg.use_cvm is False else '')}")
+
+
+# --------------------------------------------------------------------------------------
+# CPU leg (cpu_baseline of our arm, and the whole of --impl reference)
+# --------------------------------------------------------------------------------------
+def cpu_leg(cfg, table_host, batches, budget_s=10.0, threads=None):
+    """Times the reference CPU arithmetic on whole batches of the workload until ~budget_s of
+    work is done.  Uses oracle/_ref (the reference's refer::EmbSeqPool compiled from
+    /root/reference) when present and the workload is the fp32 SUM+CVM shape it covers,
+    else the oracle port.  Returns a cpu_baseline dict."""
+    import ctypes as C
+    from oracle import oracle as O
+    threads = threads or (os.cpu_count() or 1)
+    R = O.ref_lib()
+    use_ref = (R is not None and cfg.dtype == "f32" and cfg.use_cvm is True and cfg.shared_table
+               and all(p == "SUM" for p in cfg.pooltypes))
+    S, Bsz, D = cfg.slots, cfg.batch, cfg.dim
+    out = np.empty((Bsz, S * cfg.d_out), dtype=table_host[0].dtype)
+    n_rows = table_host[0].shape[0]
+
+    def run(batch, nthreads, fast=True):
+        if use_ref:
+            t = table_host[0]
+            for s in range(S):
+                rc = R.ref_fused_lod_f32(t.ctypes.data, n_rows, D, batch.ids[s].ctypes.data, batch.lods[s].ctypes.data,
+                                         Bsz, 0.0, 1, out.ctypes.data + s * D * 4, S * D, nthreads)
+                assert rc == 0
+        else:
+            cvm_mode = O.CVM_NONE if cfg.use_cvm is None else (O.CVM_USE if cfg.use_cvm else O.CVM_STRIP)
+            O.fused_forward(table_host, batch.ids, batch.lods, cfg.pooltypes, cvm_mode=cvm_mode,
+                            bf16=cfg.dtype == "bf16", concat=True, threads=nthreads, fast=fast)
+
+    def timed(nthreads, budget):
+        run(batches[0], nthreads)  # warm
+        n, t0 = 0, time.perf_counter()
+        while True:
+            run(batches[n % len(batches)], nthreads)
+            n += 1
+            el = time.perf_counter() - t0
+            if el >= budget or n >= 20000:
+                return S * Bsz * n / el, n, el
+
+    v_all, n_all, t_all = timed(threads, budget_s * 0.6)
+    v_one, n_one, t_one = timed(1, budget_s * 0.4)
+    return {"value": v_all, "unit": UNIT, "cores": threads,
+            "kind": "reference" if use_ref else "port",
+            "sample": (f"{n_all} full batches ({S} slots x {Bsz} seqs) in {t_all:.2f}s at {threads} threads; "
+                       + ("refer::EmbSeqPool from the reference tree (oracle/_ref) + pad/CVM glue"
+                          if use_ref else "oracle port (oracle/ctr_oracle.c, -O3 -mavx2)")
+                       + (f"; table folded to {n_rows} rows" if n_rows != cfg.rows else "")),
+            "value_1thread": v_one, "sample_1thread": f"{n_one} batches in {t_one:.2f}s"}
+
+
+def host_table_and_batches(cfg, synth, n_batches, torch=None, dev_tables=None, max_host_gb=24.0):
+    """Host copies of the table(s) (D2H from the device when it exists, else regenerated with
+    rows folded so that it stays small) and host batches whose ids index them."""
+    bytes_needed = cfg.n_tables() * cfg.rows * cfg.dim * cfg.elem_size
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 32 << 30
+    limit = min(max_host_gb * (1 << 30), avail * 0.5)
+    if dev_tables is not None and bytes_needed <= limit:
+        tabs = []
+        for t in dev_tables:
+            h = t.view(torch.int16).cpu().numpy().view(np.uint16) if t.dtype == torch.bfloat16 else t.cpu().numpy()
+            tabs.append(h)
+        rows = cfg.rows
+    else:
+        rows = cfg.rows
+        while cfg.n_tables() * rows * cfg.dim * cfg.elem_size > min(limit, 2 << 30):
+            rows //= 2
+        tabs = [synth.table_rows_numpy(cfg.seed + 1000 * t, np.arange(rows), cfg.dim, cfg.dtype,
+                                       cvm_cols=cfg.use_cvm is not None) for t in range(cfg.n_tables())]
+    batches = []
+    for b in range(n_batches):
+        bt = synth.draw_batch(cfg, step=b)
+        if rows != cfg.rows:
+            bt.ids = [i % rows for i in bt.ids]
+        batches.append(bt)
+    return tabs, batches, rows
+
+
+def run_reference(args):
+    rank, local_rank, world = _env_rank()
+    if rank != 0:
+        return 0
+    from benchtools import synth
+    from oracle import oracle as O
+    O.build()
+    cfg = synth.configs()[args.workload]
+    torch = None
+    dev_tables = None
+    try:
+        import torch as _torch
+        if _torch.cuda.is_available():
+            torch = _torch
+            dev = torch.device("cuda", local_rank)
+            tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
+            import __graft_entry__ as g
+            g.build()
+            dev_tables = []
+            for t in range(cfg.n_tables()):
+                tab = torch.empty((cfg.rows, cfg.dim), dtype=tdt, device=dev)
+                synth.fill_table(tab, cfg.seed + 1000 * t, cvm_cols=cfg.use_cvm is not None)
+                dev_tables.append(tab)
+            torch.cuda.synchronize()
+    except Exception:
+        dev_tables = None
+    tabs, batches, rows = host_table_and_batches(cfg, synth, 4, torch, dev_tables)
+    del dev_tables
+    # K steps of a bounded sample each; one step = one full batch here
+    base = cpu_leg(cfg, tabs, batches, budget_s=min(60.0, max(5.0, 0.2 * (args.steps + args.warmup))))
+    value = base["value"]
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * cfg.slots * cfg.batch / value,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": cfg.dtype,
+            "data": "synthetic", "config": {"workload": _workload_name(cfg), "host_threads": base["cores"]},
+            "cpu_baseline": base,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_ours(args):
+    import torch
+    import __graft_entry__ as g
+    rank, local_rank, world = _env_rank()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: paddle_infer_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        g.build()
+    if world > 1:
+        dist.barrier()
+    from benchtools import synth
+    from paddle_infer_b200 import ops
+
+    cfg = synth.configs()[args.workload]
+    S, Bsz, D = cfg.slots, cfg.batch, cfg.dim
+    tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
+    tables = []
+    for t in range(cfg.n_tables()):
+        tab = torch.empty((cfg.rows, D), dtype=tdt, device=dev)
+        synth.fill_table(tab, cfg.seed + 1000 * t, cvm_cols=cfg.use_cvm is not None)
+        tables.append(tab)
+    W = tables if len(tables) > 1 else tables[0]
+
+    # ---- batches resident in HBM (ids, LoD, output blocks), one plan each ----------------
+    host_batches = [synth.draw_batch(cfg, step=rank * 1000 + b) for b in range(N_BATCHES)]
+    plans, k_tots = [], []
+    for hb in host_batches:
+        ids_d = [torch.from_numpy(i).to(dev) for i in hb.ids]
+        lods_d = [torch.from_numpy(l.astype(np.int64)).to(dev) for l in hb.lods]
+        plans.append(ops.ctr_fused_emb_seqpool_cvm(W, ids_d, lods_d, cfg.pooltypes, use_cvm=cfg.use_cvm, concat=True,
+                                                   plan_only=True))
+        k_tots.append(hb.k_tot)
+    torch.cuda.synchronize()
+    ctx = plans[0].ctx
+    stream = torch.cuda.current_stream(dev)
+
+    K, Wm = args.steps, max(args.warmup, 0)
+    for i in range(Wm):
+        plans[i % N_BATCHES].launch()
+    ctx.check_ids()  # also a sync
+
+    n_ev = K + 1 if K <= 20000 else 0
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_ev)] if n_ev else \
+        [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+    sampler = ClockSampler(local_rank)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    if n_ev:
+        evs[0].record(stream)
+        for i in range(K):
+            plans[(Wm + i) % N_BATCHES].launch()
+            evs[i + 1].record(stream)
+    else:
+        evs[0].record(stream)
+        for i in range(K):
+            plans[(Wm + i) % N_BATCHES].launch()
+        evs[1].record(stream)
+    sampler.sample()  # the queue is still draining: a sample under load even for tiny K
+    torch.cuda.synchronize()
+    sampler.stop()
+    if world > 1:
+        dist.barrier()
+    elapsed_ms = evs[0].elapsed_time(evs[-1])
+    ctx.check_ids()
+    if n_ev:
+        per = np.array([evs[i].elapsed_time(evs[i + 1]) for i in range(K)])
+        kern_ms = float(per.mean())
+        kern_ms_med = float(np.median(per))
+    else:
+        kern_ms = kern_ms_med = elapsed_ms / K
+    k_used = [k_tots[(Wm + i) % N_BATCHES] for i in range(K)]
+    alg_bytes = float(np.mean([cfg.algorithmic_bytes(k) for k in k_used]))
+
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_max = float(t.item())
+    value = S * Bsz * K * world / (elapsed_max * 1e-3)
+
+    # ---- e2e: host buffers in, host block out, through the public host-buffer call -------
+    Ke = max(3, min(K, args.e2e_steps))
+    max_ids = max(int(i.size) for hb in host_batches for i in hb.ids)
+    fe = ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx)
+    pinned = [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
+    for i in range(3):
+        fe.run(pinned[i % N_BATCHES], host_batches[i % N_BATCHES].lods)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_host0 = time.perf_counter()
+    e0.record(stream)
+    h2d = d2h = 0
+    for i in range(Ke):
+        fe.run(pinned[i % N_BATCHES], host_batches[i % N_BATCHES].lods)
+        h2d += fe.h2d_bytes
+        d2h += fe.d2h_bytes
+    e1.record(stream)
+    torch.cuda.synchronize()
+    t_host = (time.perf_counter() - t_host0) * 1e3
+    e2e_ms = max(e0.elapsed_time(e1), t_host)  # the call is synchronous: host time is the truth when larger
+    te = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = S * Bsz * Ke * world / (float(te.item()) * 1e-3)
+
+    peak, peak_src = _peaks()
+    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": elapsed_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": cfg.dtype, "data": "synthetic",
+        "config": {"workload": _workload_name(cfg), "global_batch": Bsz * world, "parallelism": f"replica x{world}",
+                   "l2_hygiene": f"table {cfg.n_tables() * cfg.rows * D * cfg.elem_size / 1e9:.1f} GB >> L2; timed loop "
+                                 f"rotates {N_BATCHES} distinct resident batches (ids+LoD+out "
+                                 f"{N_BATCHES * alg_bytes / 1e6:.0f} MB > 126 MB L2); hot table rows stay cached as in "
+                                 "steady-state serving",
+                   "lod": "resident in HBM (value); host LoD uploaded per call (e2e)"},
+        "clocks": sampler.summary(),
+        "gpu_launches": K * plans[0].num_kernels(),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": _traffic_from_profiles(args.workload), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": kern_ms, "kernel_ms_median": kern_ms_med,
+                     "frac_of_nominal_8000": achieved / 8000.0, "kernel": "ctrfe::fused_pool_kernel"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // Ke, "d2h_bytes_per_step": d2h // Ke,
+                "steps": Ke, "ms_per_step": float(te.item()) / Ke},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        tabs, hb4, rows = host_table_and_batches(cfg, synth, 4, torch, tables)
+        line["cpu_baseline"] = cpu_leg(cfg, tabs, hb4, budget_s=args.cpu_budget)
+    elif rank == 0:
+        line["cpu_baseline"] = None
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--e2e-steps", type=int, default=40)
+    ap.add_argument("--cpu-budget", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    return run_reference(args) if args.impl == "reference" else run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,183 @@
+/*
+ * ctrfe.h -- C ABI of the B200 (sm_100a) sparse-feature front end for Paddle Inference
+ * CTR models:  lookup_table_v2 (embedding gather over LoD-packed id slots)
+ *              -> sequence_pool (SUM / AVERAGE / SQRT / MAX / LAST / FIRST)
+ *              -> cvm (show/click transform).
+ *
+ * This is the drop-in boundary.  Everything is extern "C", plain pointers and sizes;
+ * no C++ types, no exceptions, no torch/paddle types.  Streams are passed as void*
+ * (a cudaStream_t).  Every function returns CTRFE_OK (0) or a CTRFE_ERR_* code and
+ * leaves a human-readable message for ctrfe_last_error() (thread-local).
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * reference tree, chao9527/Paddle_infer).  INTEGRATION.md shows the Paddle-side binding
+ * (PD_BUILD_OP shim, ctypes) a maintainer would add.
+ *
+ * There is no CPU fallback anywhere behind this header: every compute entry point
+ * launches sm_100a kernels or fails.
+ */
+#ifndef CTRFE_H_
+#define CTRFE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTRFE_VERSION 100 /* 0.1.0 */
+
+/* ---- status codes ------------------------------------------------------------------ */
+enum {
+  CTRFE_OK = 0,
+  CTRFE_ERR_BAD_ID = 1,   /* an id outside [0, table_rows): what EmbeddingCPUFunctor throws,
+                             paddle/phi/kernels/cpu/embedding_kernel.cc:59-76 */
+  CTRFE_ERR_ARG = 2,      /* malformed argument / LoD (framework CheckLoD, lod_tensor.h:74-104;
+                             sequence_pool_op.h:42-60) */
+  CTRFE_ERR_CUDA = 3,     /* a CUDA runtime call failed */
+  CTRFE_ERR_UNSUPPORTED = 4,
+  CTRFE_ERR_NCCL = 5
+};
+
+/* ---- element types (phi::DataType subset this path is registered for) --------------- */
+enum { CTRFE_F32 = 0, CTRFE_F16 = 1, CTRFE_BF16 = 2, CTRFE_F64 = 3 };
+/* ---- id types: embedding_kernel.cu:108-117 dispatches int32 / int64 ----------------- */
+enum { CTRFE_I64 = 0, CTRFE_I32 = 1 };
+/* ---- pooltype, in the order SequencePoolOpMaker lists them
+ *      (sequence_ops/sequence_pool_op.cc:64-70) ---------------------------------------- */
+enum {
+  CTRFE_POOL_AVERAGE = 0, CTRFE_POOL_SUM = 1, CTRFE_POOL_SQRT = 2,
+  CTRFE_POOL_LAST = 3, CTRFE_POOL_FIRST = 4, CTRFE_POOL_MAX = 5
+};
+/* ---- what happens after pooling ------------------------------------------------------ */
+enum {
+  CTRFE_CVM_NONE = 0,  /* no cvm op downstream: write the pooled row */
+  CTRFE_CVM_USE = 1,   /* cvm, use_cvm=true: y0=log(x0+1), y1=log(x1+1)-y0 (cvm_op.h:34-37) */
+  CTRFE_CVM_STRIP = 2  /* cvm, use_cvm=false: drop the leading cvm_offset columns (cvm_op.h:30-32) */
+};
+/* ---- how AVERAGE / SQRT scale the sum ------------------------------------------------ */
+enum {
+  CTRFE_SCALE_DIVIDE = 0,     /* sum/h, sum/sqrt(h): sequence_pool CPU, math/sequence_pooling.cc:422-426 */
+  CTRFE_SCALE_RECIPROCAL = 1  /* sum*(1/h), sum*(1/sqrt(h)): the jit kernel the fused CPU op calls,
+                                 jit/refer/refer.h:381-389 */
+};
+/* ---- what the accumulator starts from ------------------------------------------------ */
+enum {
+  CTRFE_INIT_ZERO = 0,      /* T(0): jit/refer/refer.h:375, sequence_pooling.cu:93 */
+  CTRFE_INIT_PAD = 1,       /* pad_value, also for empty segments: fused_seqpool_cvm_op.cu:49 */
+  CTRFE_INIT_FIRST_ROW = 2  /* copy of the first row: refer.h:513-517, jit/gen/seqpool.h:61-64 */
+};
+/* ---- where a slot's LoD offsets live ------------------------------------------------- */
+enum {
+  CTRFE_LOD_HOST = 0,   /* as Paddle holds them (tensor_meta.h:43); uploaded once per call,
+                           all slots in ONE async copy, no stream sync (contrast
+                           mixed_vector.cc:57-76, which syncs per sequence_pool call) */
+  CTRFE_LOD_DEVICE = 1  /* already resident in HBM; not validated */
+};
+
+/* Opaque per-device context: pinned staging ring, device scratch, the bad-id flag. */
+typedef struct ctrfe_ctx ctrfe_ctx;
+/* Opaque prepared batch: slot descriptors + LoD resident on the device. */
+typedef struct ctrfe_plan ctrfe_plan;
+
+/* One id slot of a CTR batch.  Replaces the (W, Ids+LoD) -> Out triple of ops for one
+ * sparse feature: LookupTableV2Op (lookup_table_v2_op.cc:26-104), SequencePoolOp
+ * (sequence_ops/sequence_pool_op.cc:23-112), CVMOp (cvm_op.cc:26-59). */
+typedef struct ctrfe_slot {
+  const void* table;     /* device [table_rows, dim] row-major ("W").  When ids == NULL this is
+                            the pre-gathered X [lod[n_seg], dim] (sequence_pool's input). */
+  int64_t table_rows;
+  const void* ids;       /* device [lod[n_seg]] int64/int32 ("Ids"), or NULL for dense rows */
+  const uint64_t* lod;   /* [n_seg + 1] offsets of the LAST LoD level (size_t, lod_tensor.h:59);
+                            host or device per ctrfe_fused_desc.lod_location */
+  int64_t n_seg;         /* number of sequences (batch size for this slot) */
+  void* out;             /* device; pooled row i is written at out + i*out_ld elements.
+                            out_ld > D_out gives the concat(axis=1) layout of
+                            fusion_seqpool_cvm_concat_op.cc:132-157 */
+  int64_t out_ld;
+  int32_t pooltype;      /* CTRFE_POOL_* ("pooltype" attr) */
+  int32_t ids_dtype;     /* CTRFE_I64 / CTRFE_I32 */
+} ctrfe_slot;
+
+typedef struct ctrfe_fused_desc {
+  int32_t n_slots;
+  int32_t dtype;          /* CTRFE_F32 / F16 / BF16: storage type of tables and outputs;
+                             accumulation is always fp32 */
+  const ctrfe_slot* slots;/* host array [n_slots] */
+  int64_t dim;            /* row width D in elements */
+  int64_t padding_idx;    /* "padding_idx" attr, -1 = none (embedding_util.h:19) */
+  float pad_value;        /* "pad_value" attr: output of an empty sequence
+                             (sequence_pooling.cc:395-398) */
+  int32_t cvm_mode;       /* CTRFE_CVM_* ("use_cvm" attr, or no cvm op) */
+  int32_t cvm_offset;     /* columns dropped by CTRFE_CVM_STRIP; 2 for cvm_op, the
+                             "cvm_offset" attr for fused_seqpool_cvm (fused_seqpool_cvm_op.cc:141) */
+  int32_t scale_mode;     /* CTRFE_SCALE_* */
+  int32_t init_mode;      /* CTRFE_INIT_* */
+  int32_t lod_location;   /* CTRFE_LOD_* */
+  int32_t reserved;
+} ctrfe_fused_desc;
+
+/* ---- library ------------------------------------------------------------------------ */
+int ctrfe_version(void);
+const char* ctrfe_last_error(void);
+
+/* Context bound to one CUDA device.  Re-entrant across contexts; one context must not be
+ * used from two host threads at once (one predictor = one thread in Paddle). */
+int ctrfe_ctx_create(int device, ctrfe_ctx** out);
+int ctrfe_ctx_destroy(ctrfe_ctx* ctx);
+
+/* Bad-id report.  The kernels never fault on an out-of-range id: they treat the row as
+ * zero and record the first offender.  This call synchronises `stream`, and returns
+ * CTRFE_ERR_BAD_ID (filling slot / position / the id value when non-NULL) if any launch
+ * since the last check saw one; the flag is then cleared.
+ * Replaces the PADDLE_ENFORCE_LT/GE pair of embedding_kernel.cc:59-76 (the reference GPU
+ * kernel has no check at all, embedding_kernel.cu:36-51). */
+int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* position, int64_t* id);
+
+/* ---- the fused hot path: gather + segmented pool + CVM, all slots in ONE launch ------
+ * Replaces, per slot, EmbeddingKernel<GPU> (phi/kernels/gpu/embedding_kernel.cu:99-118)
+ * + SequencePoolFunctor<GPUContext> (math/sequence_pooling.cu:192-280)
+ * + CVMCUDAKernel (cvm_op.cu:86-125), and as a whole FusedSeqpoolCVMCUDAKernel
+ * (fused/fused_seqpool_cvm_op.cu:423-506) and the CPU FusionSeqPoolCVMConcatKernel
+ * (fused/fusion_seqpool_cvm_concat_op.cc:97-159).
+ * Asynchronous on `stream`.  Summation order per sequence is the reference's (row order,
+ * one accumulator per column). */
+int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream);
+
+/* Same, split in two so a serving loop can keep the launch minimal: create validates the
+ * descriptor (and host LoD), uploads descriptors + LoD in one async copy on `stream`;
+ * launch enqueues exactly one kernel.  A plan may be launched any number of times (the
+ * buffers it names must stay valid) and on any stream ordered after the create stream. */
+int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream, ctrfe_plan** out);
+int ctrfe_plan_launch(ctrfe_plan* plan, void* stream);
+int ctrfe_plan_destroy(ctrfe_plan* plan);
+/* Number of kernels one ctrfe_plan_launch enqueues (for launch accounting). */
+int ctrfe_plan_num_kernels(const ctrfe_plan* plan);
+
+/* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
+
+/* lookup_table_v2 / phi embedding: out[k,:] = (ids[k]==padding_idx) ? 0 : table[ids[k],:].
+ * Pure byte copy, any element size.  Replaces EmbeddingCUDAFunctor / EmbeddingFW
+ * (phi/kernels/gpu/embedding_kernel.cu:25-88). */
+int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes,
+                    const void* ids, int32_t ids_dtype, int64_t n_ids, int64_t padding_idx,
+                    void* out, void* stream);
+
+/* sequence_pool: x device [lod[n_seg], width], lod HOST offsets of the last level,
+ * out device [n_seg, width]; max_index device int32 [n_seg, width] or NULL (is_test).
+ * Replaces SequencePoolFunctor<GPUContext,T>::operator() (math/sequence_pooling.cu:192-280),
+ * with the CPU functor's semantics for MAX (sequence_pooling.cc:159-175). */
+int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t width,
+                        const uint64_t* lod_host, int64_t n_seg, int32_t pooltype, float pad_value,
+                        void* out, int32_t* max_index, void* stream);
+
+/* cvm: x device [rows, width] -> y [rows, width] (use_cvm) or [rows, width-2].
+ * Replaces CVMCUDAKernel<T>::Compute (cvm_op.cu:86-125); the op's CVM input is not read
+ * in forward (cvm_op.h:60-99) and is not a parameter. */
+int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_t width,
+              int32_t use_cvm, void* y, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTRFE_H_ */

@@ -116,6 +116,8 @@ def ref_lib():
                                               C.c_void_p, C.c_int64]
             R.ref_embseqpool_lod_f32.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                                  C.c_int64, C.c_void_p, C.c_int64]
+            R.ref_fused_lod_f32.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                                            C.c_float, C.c_int, C.c_void_p, C.c_int64, C.c_int]
             _libs["ref"] = R
     return _libs["ref"]
 

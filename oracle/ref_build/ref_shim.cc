@@ -73,6 +73,44 @@ int ref_embseqpool_lod_f32(const float* table, int64_t tbl_h, int64_t tbl_w, con
   } catch (...) { return 1; }
 }
 
+// The whole CPU path for one slot, as a CPU predictor runs it after
+// seqpool_cvm_concat_fuse_pass with the gather folded in: per sequence the REFERENCE's
+// refer::EmbSeqPool (gather + SUM in id order), an empty sequence -> pad_value
+// (sequence_pooling.cc:395-398), then the two CVM lines of
+// fusion_seqpool_cvm_concat_op.cc:152-153 (log in double, narrowed).  The loop and the
+// CVM lines are this shim's; the arithmetic that dominates is the reference's.
+// Threads split the sequences (OpenMP), each under FTZ/DAZ as naive_executor.cc:66 sets.
+int ref_fused_lod_f32(const float* table, int64_t tbl_h, int64_t tbl_w, const int64_t* ids,
+                      const uint64_t* lod, int64_t n_seg, float pad_value, int use_cvm, float* out,
+                      int64_t out_ld, int n_threads) {
+  int bad = 0;
+  if (n_threads < 1) n_threads = 1;
+#pragma omp parallel num_threads(n_threads) if (n_threads > 1)
+  {
+    const unsigned old_csr = __builtin_ia32_stmxcsr();
+    __builtin_ia32_ldmxcsr(old_csr | 0x8040u);
+    jit::emb_seq_pool_attr_t attr(tbl_h, tbl_w, 0, 1, tbl_w);
+#pragma omp for schedule(static)
+    for (int64_t i = 0; i < n_seg; ++i) {
+      float* dst = out + i * out_ld;
+      attr.index_height = static_cast<int64_t>(lod[i + 1] - lod[i]);
+      if (attr.index_height == 0) {
+        for (int64_t k = 0; k < tbl_w; ++k) dst[k] = pad_value;
+      } else {
+        try {
+          jit::refer::EmbSeqPool<float>(table, ids + lod[i], dst, &attr);
+        } catch (...) { bad = 1; continue; }
+      }
+      if (use_cvm) {
+        dst[0] = static_cast<float>(std::log(static_cast<double>(dst[0] + 1)));
+        dst[1] = static_cast<float>(std::log(static_cast<double>(dst[1] + 1)) - static_cast<double>(dst[0]));
+      }
+    }
+    __builtin_ia32_ldmxcsr(old_csr);
+  }
+  return bad;
+}
+
 int ref_seqpool_type_sum() { return static_cast<int>(jit::SeqPoolType::kSum); }
 int ref_seqpool_type_avg() { return static_cast<int>(jit::SeqPoolType::kAvg); }
 int ref_seqpool_type_sqrt() { return static_cast<int>(jit::SeqPoolType::kSqrt); }

@@ -1,0 +1,535 @@
+// ctrfe_api.cu -- the C ABI declared in include/ctrfe.h: argument checking (mirroring the
+// reference's enforce checks), one-copy LoD/descriptor upload, kernel launches.
+// No CPU compute path exists in this file: every entry point launches sm_100a kernels.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "ctrfe_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e__ = (call);                                                                 \
+    if (e__ != cudaSuccess)                                                                   \
+      return fail(CTRFE_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),     \
+                  __FILE__, __LINE__);                                                        \
+  } while (0)
+
+constexpr int kRing = 4;  // pinned staging buffers in flight
+
+struct Staging {
+  char* host = nullptr;
+  size_t cap = 0;
+  cudaEvent_t done = nullptr;
+  bool pending = false;
+};
+
+struct IdSource {  // what ctrfe_check_ids needs to fetch the offending id value
+  const void* ids;
+  int ids_i32;
+};
+
+}  // namespace
+
+struct ctrfe_ctx {
+  int device = 0;
+  unsigned long long* err_dev = nullptr;   // [1]
+  unsigned long long* err_host = nullptr;  // pinned [2]: flag, id value
+  Staging ring[kRing];
+  int ring_next = 0;
+  // scratch of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
+  char* scratch = nullptr;
+  size_t scratch_cap = 0;
+  std::vector<IdSource> last_ids;  // slots of the most recent fused launch
+  int sm_count = 148;
+};
+
+struct ctrfe_plan {
+  ctrfe_ctx* ctx = nullptr;
+  char* dev = nullptr;       // descriptors + LoD (owned unless borrowed)
+  bool owns_dev = false;
+  ctrfe::FusedParams params{};
+  int dtype = 0;
+  bool vect = false;
+  dim3 grid{};
+  std::vector<IdSource> id_src;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+int elem_size(int dtype) {
+  switch (dtype) {
+    case CTRFE_F32: return 4;
+    case CTRFE_F16: case CTRFE_BF16: return 2;
+    case CTRFE_F64: return 8;
+    default: return 0;
+  }
+}
+
+int stage_acquire(ctrfe_ctx* ctx, size_t bytes, Staging** out) {
+  Staging& s = ctx->ring[ctx->ring_next];
+  ctx->ring_next = (ctx->ring_next + 1) % kRing;
+  if (s.pending) {
+    CU(cudaEventSynchronize(s.done));  // normally long complete
+    s.pending = false;
+  }
+  if (s.cap < bytes) {
+    if (s.host) CU(cudaFreeHost(s.host));
+    s.host = nullptr;
+    size_t cap = bytes < (1u << 16) ? (1u << 16) : bytes + bytes / 4;
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&s.host), cap, cudaHostAllocDefault));
+    s.cap = cap;
+  }
+  if (!s.done) CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  *out = &s;
+  return CTRFE_OK;
+}
+
+int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
+  if (ctx->scratch_cap >= bytes) return CTRFE_OK;
+  if (ctx->scratch) {
+    // work already enqueued may still read the old buffer
+    CU(cudaStreamSynchronize(stream));
+    CU(cudaFree(ctx->scratch));
+    ctx->scratch = nullptr;
+  }
+  size_t cap = bytes < (1u << 20) ? (1u << 20) : bytes + bytes / 4;
+  CU(cudaMalloc(reinterpret_cast<void**>(&ctx->scratch), cap));
+  ctx->scratch_cap = cap;
+  return CTRFE_OK;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Validates a descriptor the way the reference ops' InferShape/Compute do, and derives the
+// launch geometry.  Returns the bytes needed for descriptors + (host) LoDs.
+int plan_geometry(const ctrfe_fused_desc* d, ctrfe::FusedParams* p, bool* vect, dim3* grid,
+                  size_t* bytes_needed) {
+  if (!d || !d->slots || d->n_slots <= 0) return fail(CTRFE_ERR_ARG, "fused: no slots");
+  if (d->n_slots > 65535) return fail(CTRFE_ERR_ARG, "fused: at most 65535 slots per call (got %d)", d->n_slots);
+  if (d->dtype != CTRFE_F32 && d->dtype != CTRFE_F16 && d->dtype != CTRFE_BF16)
+    return fail(CTRFE_ERR_UNSUPPORTED, "fused: dtype %d not supported (f32, f16, bf16)", d->dtype);
+  if (d->dim <= 0 || d->dim > (1 << 20)) return fail(CTRFE_ERR_ARG, "fused: bad dim %lld", (long long)d->dim);
+  if (d->cvm_mode < CTRFE_CVM_NONE || d->cvm_mode > CTRFE_CVM_STRIP)
+    return fail(CTRFE_ERR_ARG, "fused: bad cvm_mode %d", d->cvm_mode);
+  if (d->cvm_mode != CTRFE_CVM_NONE && d->dim < 2)
+    return fail(CTRFE_ERR_ARG, "cvm needs at least the show and click columns (dim=%lld)", (long long)d->dim);
+  if (d->cvm_mode == CTRFE_CVM_STRIP && (d->cvm_offset < 0 || d->cvm_offset >= d->dim))
+    return fail(CTRFE_ERR_ARG, "fused: cvm_offset %d outside [0, dim)", d->cvm_offset);
+  if (d->scale_mode != CTRFE_SCALE_DIVIDE && d->scale_mode != CTRFE_SCALE_RECIPROCAL)
+    return fail(CTRFE_ERR_ARG, "fused: bad scale_mode %d", d->scale_mode);
+  if (d->init_mode < CTRFE_INIT_ZERO || d->init_mode > CTRFE_INIT_FIRST_ROW)
+    return fail(CTRFE_ERR_ARG, "fused: bad init_mode %d", d->init_mode);
+  if (d->lod_location != CTRFE_LOD_HOST && d->lod_location != CTRFE_LOD_DEVICE)
+    return fail(CTRFE_ERR_ARG, "fused: bad lod_location %d", d->lod_location);
+
+  const int es = elem_size(d->dtype);
+  const long long row_bytes = d->dim * es;
+  const int d_out = static_cast<int>(d->dim) - (d->cvm_mode == CTRFE_CVM_STRIP ? d->cvm_offset : 0);
+  bool v = (row_bytes % 16) == 0;
+  long long max_seg = 0;
+  size_t lod_bytes = 0;
+  for (int s = 0; s < d->n_slots; ++s) {
+    const ctrfe_slot& sl = d->slots[s];
+    if (sl.n_seg < 0) return fail(CTRFE_ERR_ARG, "slot %d: negative n_seg", s);
+    if (sl.n_seg > 0 && (!sl.table || !sl.lod || !sl.out))
+      return fail(CTRFE_ERR_ARG, "slot %d: null table / lod / out", s);
+    if (sl.pooltype < CTRFE_POOL_AVERAGE || sl.pooltype > CTRFE_POOL_MAX)
+      return fail(CTRFE_ERR_ARG,
+                  "slot %d: unsupported pooling pooltype %d (AVERAGE, SUM, SQRT, LAST, FIRST, MAX)", s,
+                  sl.pooltype);
+    if (sl.ids_dtype != CTRFE_I64 && sl.ids_dtype != CTRFE_I32)
+      return fail(CTRFE_ERR_UNSUPPORTED, "slot %d: ids must be int32 or int64", s);
+    if (sl.out_ld < d_out) return fail(CTRFE_ERR_ARG, "slot %d: out_ld %lld < output width %d", s,
+                                       (long long)sl.out_ld, d_out);
+    if (sl.table_rows < 0) return fail(CTRFE_ERR_ARG, "slot %d: negative table_rows", s);
+    if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
+    if (sl.n_seg > max_seg) max_seg = sl.n_seg;
+    lod_bytes += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+  }
+
+  p->padding_idx = d->padding_idx;
+  p->dim = static_cast<int>(d->dim);
+  p->row_bytes = static_cast<int>(row_bytes);
+  const long long units = v ? row_bytes / 16 : d->dim;  // lane-sized pieces per row
+  int g_shift = 0;
+  while ((1 << g_shift) < units && g_shift < 5) ++g_shift;
+  p->g_shift = g_shift;
+  p->tiles = static_cast<int>((units + (1 << g_shift) - 1) >> g_shift);
+  p->cvm_mode = d->cvm_mode;
+  p->cvm_offset = d->cvm_offset;
+  p->scale_mode = d->scale_mode;
+  p->init_mode = d->init_mode;
+  p->pad_value = d->pad_value;
+  *vect = v;
+  const long long items = max_seg * p->tiles;
+  const long long gx = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
+  if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "fused: batch too large for one launch");
+  *grid = dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(d->n_slots), 1);
+  *bytes_needed = align_up(sizeof(ctrfe::SlotDev) * d->n_slots, 16) +
+                  (d->lod_location == CTRFE_LOD_HOST ? lod_bytes : 0);
+  return CTRFE_OK;
+}
+
+// Fills the staging image (descriptors, then host LoDs) and validates the LoDs in the same
+// pass: non-decreasing offsets (framework CheckLoD, lod_tensor.h:74-104) and, for dense
+// rows, lod.back() <= rows (sequence_pool_op.h:52-60).
+int plan_stage(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, std::vector<IdSource>* id_src) {
+  auto* sd = reinterpret_cast<ctrfe::SlotDev*>(host_img);
+  size_t off = align_up(sizeof(ctrfe::SlotDev) * d->n_slots, 16);
+  id_src->resize(d->n_slots);
+  for (int s = 0; s < d->n_slots; ++s) {
+    const ctrfe_slot& sl = d->slots[s];
+    ctrfe::SlotDev& o = sd[s];
+    o.table = static_cast<const char*>(sl.table);
+    o.ids = sl.ids;
+    o.out = static_cast<char*>(sl.out);
+    o.table_rows = sl.table_rows;
+    o.out_ld = sl.out_ld;
+    o.n_seg = sl.n_seg;
+    o.pooltype = sl.pooltype;
+    o.ids_i32 = sl.ids_dtype == CTRFE_I32;
+    (*id_src)[s] = IdSource{sl.ids, o.ids_i32};
+    if (d->lod_location == CTRFE_LOD_DEVICE) {
+      o.lod = reinterpret_cast<const unsigned long long*>(sl.lod);
+      continue;
+    }
+    auto* dst = reinterpret_cast<uint64_t*>(host_img + off);
+    o.lod = reinterpret_cast<const unsigned long long*>(dev_img + off);
+    if (sl.n_seg == 0) {
+      dst[0] = sl.lod ? sl.lod[0] : 0;
+    } else {
+      uint64_t prev = sl.lod[0];
+      dst[0] = prev;
+      bool mono = true;
+      for (int64_t i = 1; i <= sl.n_seg; ++i) {
+        const uint64_t v = sl.lod[i];
+        mono &= v >= prev;
+        dst[i] = v;
+        prev = v;
+      }
+      if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
+      if (prev > (1ull << 43)) return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large", s,
+                                           (unsigned long long)prev);
+      if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows)
+        return fail(CTRFE_ERR_ARG,
+                    "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)",
+                    s, (long long)sl.table_rows, (unsigned long long)prev);
+    }
+    off += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+  }
+  return CTRFE_OK;
+}
+
+template <int DT>
+void launch_fused_t(bool vect, dim3 grid, cudaStream_t st, const ctrfe::FusedParams& p) {
+  if (vect) ctrfe::fused_pool_kernel<DT, true><<<grid, ctrfe::kThreads, 0, st>>>(p);
+  else ctrfe::fused_pool_kernel<DT, false><<<grid, ctrfe::kThreads, 0, st>>>(p);
+}
+
+int launch_fused(int dtype, bool vect, dim3 grid, cudaStream_t st, const ctrfe::FusedParams& p) {
+  switch (dtype) {
+    case CTRFE_F32: launch_fused_t<CTRFE_F32>(vect, grid, st, p); break;
+    case CTRFE_F16: launch_fused_t<CTRFE_F16>(vect, grid, st, p); break;
+    default: launch_fused_t<CTRFE_BF16>(vect, grid, st, p); break;
+  }
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
+// Builds a plan image in `dev` (capacity checked by the caller) via a pinned staging slot.
+int plan_build(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, cudaStream_t st, char* dev, size_t bytes,
+               ctrfe_plan* plan) {
+  Staging* sg = nullptr;
+  int rc = stage_acquire(ctx, bytes, &sg);
+  if (rc) return rc;
+  rc = plan_stage(d, sg->host, dev, &plan->id_src);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dev, sg->host, bytes, cudaMemcpyHostToDevice, st));
+  CU(cudaEventRecord(sg->done, st));
+  sg->pending = true;
+  plan->params.slots = reinterpret_cast<const ctrfe::SlotDev*>(dev);
+  plan->params.err = ctx->err_dev;
+  plan->dtype = d->dtype;
+  plan->ctx = ctx;
+  plan->dev = dev;
+  return CTRFE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ctrfe_version(void) { return CTRFE_VERSION; }
+const char* ctrfe_last_error(void) { return g_err; }
+
+int ctrfe_ctx_create(int device, ctrfe_ctx** out) {
+  if (!out) return fail(CTRFE_ERR_ARG, "ctx_create: null out");
+  int n = 0;
+  CU(cudaGetDeviceCount(&n));
+  if (device < 0 || device >= n) return fail(CTRFE_ERR_ARG, "ctx_create: device %d of %d", device, n);
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CTRFE_ERR_CUDA, "ctx_create: cannot select device %d", device);
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(CTRFE_ERR_UNSUPPORTED, "this library is built for sm_100a only; device %d is sm_%d%d", device,
+                prop.major, prop.minor);
+  auto* c = new ctrfe_ctx();
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&c->err_dev), 8);
+  if (e == cudaSuccess) e = cudaMemset(c->err_dev, 0xff, 8);
+  if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), 16, cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    ctrfe_ctx_destroy(c);
+    return fail(CTRFE_ERR_CUDA, "ctx_create: %s", cudaGetErrorString(e));
+  }
+  *out = c;
+  return CTRFE_OK;
+}
+
+int ctrfe_ctx_destroy(ctrfe_ctx* c) {
+  if (!c) return CTRFE_OK;
+  DeviceGuard g(c->device);
+  cudaDeviceSynchronize();
+  for (auto& s : c->ring) {
+    if (s.done) cudaEventDestroy(s.done);
+    if (s.host) cudaFreeHost(s.host);
+  }
+  if (c->scratch) cudaFree(c->scratch);
+  if (c->err_dev) cudaFree(c->err_dev);
+  if (c->err_host) cudaFreeHost(c->err_host);
+  delete c;
+  return CTRFE_OK;
+}
+
+int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* position, int64_t* id) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "check_ids: null ctx");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  CU(cudaMemcpyAsync(ctx->err_host, ctx->err_dev, 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  const unsigned long long key = ctx->err_host[0];
+  if (key == ~0ull) return CTRFE_OK;
+  CU(cudaMemsetAsync(ctx->err_dev, 0xff, 8, st));
+  const int64_t s = static_cast<int64_t>(key >> 44);
+  const int64_t pos = static_cast<int64_t>(key & ((1ull << 44) - 1));
+  long long bad = -1;
+  if (s < static_cast<int64_t>(ctx->last_ids.size()) && ctx->last_ids[s].ids) {
+    const IdSource& src = ctx->last_ids[s];
+    if (src.ids_i32) {
+      int v = 0;
+      CU(cudaMemcpyAsync(&v, static_cast<const int*>(src.ids) + pos, 4, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      bad = v;
+    } else {
+      CU(cudaMemcpyAsync(&bad, static_cast<const long long*>(src.ids) + pos, 8, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+    }
+  }
+  if (slot) *slot = s;
+  if (position) *position = pos;
+  if (id) *id = bad;
+  return fail(CTRFE_ERR_BAD_ID,
+              "Variable value (input) of OP(fluid.layers.embedding) expected >= 0 and < table rows, but got "
+              "%lld (slot %lld, position %lld). Please check input value.",
+              bad, (long long)s, (long long)pos);
+}
+
+int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream, ctrfe_plan** out) {
+  if (!ctx || !out) return fail(CTRFE_ERR_ARG, "plan_create: null ctx / out");
+  DeviceGuard g(ctx->device);
+  auto* plan = new ctrfe_plan();
+  size_t bytes = 0;
+  int rc = plan_geometry(desc, &plan->params, &plan->vect, &plan->grid, &bytes);
+  if (rc) { delete plan; return rc; }
+  char* dev = nullptr;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
+  if (e != cudaSuccess) { delete plan; return fail(CTRFE_ERR_CUDA, "plan_create: cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); }
+  plan->owns_dev = true;
+  rc = plan_build(ctx, desc, static_cast<cudaStream_t>(stream), dev, bytes, plan);
+  if (rc) { cudaFree(dev); delete plan; return rc; }
+  *out = plan;
+  return CTRFE_OK;
+}
+
+int ctrfe_plan_launch(ctrfe_plan* plan, void* stream) {
+  if (!plan) return fail(CTRFE_ERR_ARG, "plan_launch: null plan");
+  DeviceGuard g(plan->ctx->device);
+  plan->ctx->last_ids = plan->id_src;
+  return launch_fused(plan->dtype, plan->vect, plan->grid, static_cast<cudaStream_t>(stream), plan->params);
+}
+
+int ctrfe_plan_destroy(ctrfe_plan* plan) {
+  if (!plan) return CTRFE_OK;
+  DeviceGuard g(plan->ctx->device);
+  if (plan->owns_dev && plan->dev) {
+    cudaDeviceSynchronize();
+    cudaFree(plan->dev);
+  }
+  delete plan;
+  return CTRFE_OK;
+}
+
+int ctrfe_plan_num_kernels(const ctrfe_plan*) { return 1; }
+
+int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "fused_forward: null ctx");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  ctrfe_plan plan;
+  size_t bytes = 0;
+  int rc = plan_geometry(desc, &plan.params, &plan.vect, &plan.grid, &bytes);
+  if (rc) return rc;
+  rc = scratch_reserve(ctx, bytes, st);
+  if (rc) return rc;
+  rc = plan_build(ctx, desc, st, ctx->scratch, bytes, &plan);
+  if (rc) return rc;
+  ctx->last_ids.swap(plan.id_src);
+  return launch_fused(plan.dtype, plan.vect, plan.grid, st, plan.params);
+}
+
+int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes, const void* ids,
+                    int32_t ids_dtype, int64_t n_ids, int64_t padding_idx, void* out, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "embedding: null ctx");
+  if (ids_dtype != CTRFE_I64 && ids_dtype != CTRFE_I32)
+    return fail(CTRFE_ERR_UNSUPPORTED, "emebdding input only support int32 and int64");
+  if (row_bytes <= 0 || table_rows < 0 || n_ids < 0) return fail(CTRFE_ERR_ARG, "embedding: bad sizes");
+  if (n_ids == 0) return CTRFE_OK;
+  if (!table || !ids || !out) return fail(CTRFE_ERR_ARG, "embedding: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out) |
+                       static_cast<uintptr_t>(row_bytes);
+  int ub = 16;
+  while (ub > 1 && (al % ub) != 0) ub >>= 1;
+  const long long total = n_ids * (row_bytes / ub);
+  long long blocks = (total + static_cast<long long>(ctrfe::kThreads) * ctrfe::kUnroll - 1) /
+                     (static_cast<long long>(ctrfe::kThreads) * ctrfe::kUnroll);
+  const long long cap = static_cast<long long>(ctx->sm_count) * 8 * 4;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  ctx->last_ids.assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
+  const char* t = static_cast<const char*>(table);
+  char* o = static_cast<char*>(out);
+  const int i32 = ids_dtype == CTRFE_I32;
+  const unsigned gb = static_cast<unsigned>(blocks);
+#define CTRFE_GATHER(UB) \
+  ctrfe::gather_rows_kernel<UB><<<gb, ctrfe::kThreads, 0, st>>>(t, table_rows, row_bytes, ids, i32, n_ids, padding_idx, o, ctx->err_dev)
+  switch (ub) {
+    case 16: CTRFE_GATHER(16); break;
+    case 8: CTRFE_GATHER(8); break;
+    case 4: CTRFE_GATHER(4); break;
+    case 2: CTRFE_GATHER(2); break;
+    default: CTRFE_GATHER(1); break;
+  }
+#undef CTRFE_GATHER
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
+int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t width, const uint64_t* lod_host,
+                        int64_t n_seg, int32_t pooltype, float pad_value, void* out, int32_t* max_index,
+                        void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "sequence_pool: null ctx");
+  if (!lod_host) return fail(CTRFE_ERR_ARG, "sequence_pool: Input(X) must carry LoD (1 or 2 levels)");
+  if (n_seg < 0) return fail(CTRFE_ERR_ARG, "sequence_pool: negative n_seg");
+  ctrfe_slot sl{};
+  sl.table = x;
+  sl.table_rows = static_cast<int64_t>(lod_host[n_seg]);
+  sl.ids = nullptr;
+  sl.lod = lod_host;
+  sl.n_seg = n_seg;
+  sl.out = out;
+  sl.out_ld = width;
+  sl.pooltype = pooltype;
+  sl.ids_dtype = CTRFE_I64;
+  ctrfe_fused_desc d{};
+  d.n_slots = 1;
+  d.dtype = dtype;
+  d.slots = &sl;
+  d.dim = width;
+  d.padding_idx = -1;
+  d.pad_value = pad_value;
+  d.cvm_mode = CTRFE_CVM_NONE;
+  d.cvm_offset = 2;
+  d.scale_mode = CTRFE_SCALE_DIVIDE;
+  d.init_mode = CTRFE_INIT_ZERO;
+  d.lod_location = CTRFE_LOD_HOST;
+  if (n_seg == 0) return CTRFE_OK;
+  int rc = ctrfe_fused_forward(ctx, &d, stream);
+  if (rc) return rc;
+  if (max_index && pooltype == CTRFE_POOL_MAX) {
+    DeviceGuard g(ctx->device);
+    auto st = static_cast<cudaStream_t>(stream);
+    // the LoD image sits right after the single descriptor in the context scratch
+    const auto* lod_dev = reinterpret_cast<const unsigned long long*>(
+        ctx->scratch + align_up(sizeof(ctrfe::SlotDev), 16));
+    const long long total = n_seg * width;
+    const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+    const char* xc = static_cast<const char*>(x);
+    switch (dtype) {
+      case CTRFE_F32: ctrfe::max_index_kernel<CTRFE_F32><<<blocks, 256, 0, st>>>(xc, lod_dev, n_seg, (int)width, max_index); break;
+      case CTRFE_F16: ctrfe::max_index_kernel<CTRFE_F16><<<blocks, 256, 0, st>>>(xc, lod_dev, n_seg, (int)width, max_index); break;
+      default: ctrfe::max_index_kernel<CTRFE_BF16><<<blocks, 256, 0, st>>>(xc, lod_dev, n_seg, (int)width, max_index); break;
+    }
+    CU(cudaGetLastError());
+  }
+  return CTRFE_OK;
+}
+
+int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_t width, int32_t use_cvm,
+              void* y, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "cvm: null ctx");
+  if (dtype != CTRFE_F32 && dtype != CTRFE_F16 && dtype != CTRFE_BF16)
+    return fail(CTRFE_ERR_UNSUPPORTED, "cvm: dtype %d not supported (f32, f16, bf16)", dtype);
+  if (width < 2) return fail(CTRFE_ERR_ARG, "cvm: Input(X) needs at least the show and click columns (width=%lld)", (long long)width);
+  if (rows < 0) return fail(CTRFE_ERR_ARG, "cvm: negative rows");
+  const long long wo = use_cvm ? width : width - 2;
+  const long long total = rows * wo;
+  if (total == 0) return CTRFE_OK;
+  if (!x || !y) return fail(CTRFE_ERR_ARG, "cvm: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  const char* xc = static_cast<const char*>(x);
+  char* yc = static_cast<char*>(y);
+  switch (dtype) {
+    case CTRFE_F32: ctrfe::cvm_kernel<CTRFE_F32><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
+    case CTRFE_F16: ctrfe::cvm_kernel<CTRFE_F16><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
+    default: ctrfe::cvm_kernel<CTRFE_BF16><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
+  }
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,469 @@
+"""Host-side mirrors of the reference operator interfaces for the CTR sparse front end.
+
+Same op names, argument names/meaning and error behaviour as the reference operators;
+each function marshals into the C ABI (include/ctrfe.h) and launches sm_100a kernels.
+torch is used only for what it is good at here: device memory and streams.
+
+    lookup_table_v2            paddle/fluid/operators/lookup_table_v2_op.cc:26-104
+    sequence_pool              paddle/fluid/operators/sequence_ops/sequence_pool_op.{cc,h}
+    cvm                        paddle/fluid/operators/cvm_op.{cc,h}
+    fused_seqpool_cvm          paddle/fluid/operators/fused/fused_seqpool_cvm_op.{cc,cu}
+    fusion_seqpool_cvm_concat  paddle/fluid/operators/fused/fusion_seqpool_cvm_concat_op.cc
+    fused_embedding_seq_pool   paddle/fluid/operators/fused/fused_embedding_seq_pool_op.{cc,h}
+    ctr_fused_emb_seqpool_cvm  NEW: the whole front end in one launch (SURVEY.md section 8b,
+                               route 1 -- Paddle's custom-op loader refuses to re-register a
+                               built-in name, framework/custom_operator.cc:722-725)
+
+LoD arguments are offset-based lists of levels, as LoDTensor::lod() returns them
+(see paddle_infer_b200.lod for the length-based conversion the Python API uses).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from collections import namedtuple
+from typing import List, Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib as B
+from .lod import check_lod
+
+_DT = {torch.float32: B.F32, torch.float16: B.F16, torch.bfloat16: B.BF16, torch.float64: B.F64}
+_IDT = {torch.int64: B.I64, torch.int32: B.I32}
+
+
+class InvalidArgument(ValueError):
+    """platform::errors::InvalidArgument of the reference's enforce checks."""
+
+
+class Unimplemented(NotImplementedError):
+    """platform::errors::Unimplemented."""
+
+
+# ------------------------------------------------------------------------------------------
+# context plumbing
+# ------------------------------------------------------------------------------------------
+class Context:
+    """One ctrfe_ctx per CUDA device (pinned staging ring, device scratch, bad-id flag)."""
+
+    def __init__(self, device: Union[int, torch.device, None] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("paddle_infer_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        h = C.c_void_p()
+        B.check(B.lib().ctrfe_ctx_create(dev.index, C.byref(h)))
+        self.handle = h
+
+    def stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def check_ids(self) -> None:
+        """Raise BadIdError if any launch since the last check met an id outside the table
+        (what EmbeddingCPUFunctor enforces, phi/kernels/cpu/embedding_kernel.cc:59-76)."""
+        s, p, i = C.c_int64(-1), C.c_int64(-1), C.c_int64(-1)
+        rc = B.lib().ctrfe_check_ids(self.handle, self.stream(), C.byref(s), C.byref(p), C.byref(i))
+        if rc == B.ERR_BAD_ID:
+            raise B.BadIdError(B.lib().ctrfe_last_error().decode(), s.value, p.value, i.value)
+        B.check(rc)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            B.lib().ctrfe_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_ctxs = {}
+
+
+def default_context(device=None) -> Context:
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    if idx not in _ctxs:
+        _ctxs[idx] = Context(torch.device("cuda", idx))
+    return _ctxs[idx]
+
+
+def _need_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must live on the GPU: this op has no CPU kernel (no CPU fallback)")
+
+
+def _last_level(lod, name="X") -> List[int]:
+    if lod is None or len(lod) == 0:
+        raise InvalidArgument(f"Input({name}) Tensor of SequencePoolOp does not contain LoD information.")
+    if len(lod) > 2:
+        raise InvalidArgument(f"The lod level of input shall be no more than 2.Received lod level is {len(lod)}.")
+    if len(lod) == 2 and lod[0][-1] != len(lod[1]) - 1:
+        raise InvalidArgument("The input lod information is illegal.")
+    return lod[-1]
+
+
+def _lod_np(level: Sequence[int]) -> np.ndarray:
+    a = np.ascontiguousarray(np.asarray(level, dtype=np.uint64))
+    if a.ndim != 1 or a.size < 1:
+        raise InvalidArgument("a LoD level needs at least one offset")
+    return a
+
+
+# ------------------------------------------------------------------------------------------
+# lookup_table_v2
+# ------------------------------------------------------------------------------------------
+def lookup_table_v2(W: torch.Tensor, Ids: torch.Tensor, padding_idx: int = -1, *, check: bool = True,
+                    ctx: Optional[Context] = None) -> torch.Tensor:
+    """Out = W[Ids] with a zero row where Ids == padding_idx; Out.shape = Ids.shape + [D]
+    (lookup_table_v2_op.cc:45-66).  Out shares Ids' LoD (the caller keeps carrying it).
+    check=True synchronises and raises BadIdError for ids outside [0, N), as the reference
+    CPU kernel does; pass check=False in a serving loop and call ctx.check_ids() at will."""
+    _need_cuda(W, "W"), _need_cuda(Ids, "Ids")
+    if W.dim() != 2:
+        raise InvalidArgument(f"ShapeError: The dimensions of the 'lookup table' must be 2. But received "
+                              f"lookup table's dimensions = {W.dim()}.")
+    if Ids.dtype not in _IDT:
+        raise Unimplemented("emebdding input only support int32 and int64")
+    ctx = ctx or default_context(W.device)
+    W = W.contiguous()
+    ids = Ids.contiguous()
+    out = torch.empty(tuple(Ids.shape) + (W.shape[1],), dtype=W.dtype, device=W.device)
+    B.check(B.lib().ctrfe_embedding(ctx.handle, W.data_ptr(), W.shape[0], W.shape[1] * W.element_size(),
+                                    ids.data_ptr(), _IDT[ids.dtype], ids.numel(), int(padding_idx),
+                                    out.data_ptr(), ctx.stream()))
+    if check:
+        ctx.check_ids()
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+# sequence_pool
+# ------------------------------------------------------------------------------------------
+SeqPoolOut = namedtuple("SeqPoolOut", ["Out", "MaxIndex", "lod"])
+
+
+def sequence_pool(X: torch.Tensor, lod, pooltype: str = "AVERAGE", pad_value: float = 0.0,
+                  is_test: bool = False, *, ctx: Optional[Context] = None) -> SeqPoolOut:
+    """Pools each sequence of the LAST LoD level of X ([K, ...]) into one row.
+    Out: [num_seq, ...]; Out's LoD is lod[0] when X has two levels, else none
+    (sequence_pool_op.h:42-72).  MaxIndex (int32, Out's shape) is produced for MAX unless
+    is_test (the reference skips it for is_test on CPU, sequence_pool_op.h:79-87).
+    Empty sequences yield pad_value."""
+    _need_cuda(X, "X")
+    if pooltype not in B.POOLTYPES:
+        raise InvalidArgument(f"unsupported pooling pooltype: {pooltype}. Only support \"AVERAGE\", \"SUM\", "
+                              "\"SQRT\", \"LAST\", \"FIRST\" and \"MAX\"")
+    if X.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise Unimplemented(f"sequence_pool: dtype {X.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    last = _last_level(lod)
+    n_seq = len(last) - 1
+    if X.shape[0] < n_seq:
+        raise InvalidArgument("The first dimension of Input(X) must be large than batch size."
+                              f"But received first dimension of Input(X) is {X.shape[0]}, while batch"
+                              f"size is {n_seq}.")
+    if last[-1] > X.shape[0]:
+        raise InvalidArgument(f"The last LoD offset ({last[-1]}) exceeds the first dimension of Input(X) "
+                              f"({X.shape[0]}).")
+    ctx = ctx or default_context(X.device)
+    X = X.contiguous()
+    width = int(np.prod(X.shape[1:])) if X.dim() > 1 else 1
+    out = torch.empty((n_seq,) + tuple(X.shape[1:]), dtype=X.dtype, device=X.device)
+    want_index = pooltype == "MAX" and not is_test
+    index = torch.empty(out.shape, dtype=torch.int32, device=X.device) if want_index else None
+    lod_a = _lod_np(last)
+    B.check(B.lib().ctrfe_sequence_pool(ctx.handle, X.data_ptr(), _DT[X.dtype], width, lod_a.ctypes.data, n_seq,
+                                        B.POOLTYPES[pooltype], float(pad_value), out.data_ptr(),
+                                        index.data_ptr() if want_index else None, ctx.stream()))
+    out_lod = [list(lod[0])] if len(lod) == 2 else []
+    return SeqPoolOut(out, index, out_lod)
+
+
+# ------------------------------------------------------------------------------------------
+# cvm
+# ------------------------------------------------------------------------------------------
+def cvm(X: torch.Tensor, CVM: Optional[torch.Tensor] = None, use_cvm: bool = True, *,
+        ctx: Optional[Context] = None) -> torch.Tensor:
+    """Y[:,0] = log(X[:,0]+1), Y[:,1] = log(X[:,1]+1) - Y[:,0], rest copied (use_cvm=True);
+    or X[:, 2:] (use_cvm=False).  X must be rank 2 (cvm_op.cc:34-38).  The CVM input is
+    accepted for signature parity and, as in the reference forward, never read
+    (cvm_op.h:60-99).  Y shares X's LoD."""
+    _need_cuda(X, "X")
+    if X.dim() != 2:
+        raise InvalidArgument(f"Input(X)'s rank should be 2, but got {X.dim()}")
+    if X.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise Unimplemented(f"cvm: dtype {X.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    ctx = ctx or default_context(X.device)
+    X = X.contiguous()
+    rows, w = X.shape
+    if w < 2:
+        raise InvalidArgument("Input(X) of cvm needs at least the show and click columns")
+    y = torch.empty((rows, w if use_cvm else w - 2), dtype=X.dtype, device=X.device)
+    B.check(B.lib().ctrfe_cvm(ctx.handle, X.data_ptr(), _DT[X.dtype], rows, w, int(bool(use_cvm)), y.data_ptr(),
+                              ctx.stream()))
+    return y
+
+
+# ------------------------------------------------------------------------------------------
+# the fused front end
+# ------------------------------------------------------------------------------------------
+def _as_list(x, n):
+    return list(x) if isinstance(x, (list, tuple)) else [x] * n
+
+
+class FusedPlan:
+    """A prepared batch: descriptors + LoD resident on the device; launch() enqueues ONE
+    kernel for all slots.  Keeps the tensors it names alive."""
+
+    def __init__(self, ctx: Context, handle, outs, keep):
+        self.ctx, self.handle, self.outs, self._keep = ctx, handle, outs, keep
+
+    def launch(self) -> None:
+        B.check(B.lib().ctrfe_plan_launch(self.handle, self.ctx.stream()))
+
+    def num_kernels(self) -> int:
+        return B.lib().ctrfe_plan_num_kernels(self.handle)
+
+    def close(self):
+        if self.handle:
+            B.lib().ctrfe_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_value, padding_idx, cvm_mode,
+                cvm_offset, scale_mode, init_mode, lod_on_device):
+    S = len(lods)
+    slots = (B.Slot * S)()
+    keep = []
+    for s in range(S):
+        t = tables[s]
+        if lod_on_device:
+            lod_ptr, n_seg = lods[s].data_ptr(), lods[s].numel() - 1
+            keep.append(lods[s])
+        else:
+            a = _lod_np(lods[s])
+            keep.append(a)
+            lod_ptr, n_seg = a.ctypes.data, a.size - 1
+        i = ids[s]
+        slots[s] = B.Slot(t.data_ptr(), t.shape[0], i.data_ptr() if i is not None else None, lod_ptr, n_seg,
+                          outs[s].data_ptr(), out_ld, B.POOLTYPES[pooltypes[s]],
+                          _IDT[i.dtype] if i is not None else B.I64)
+    desc = B.FusedDesc(S, dtype, slots, dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset, scale_mode,
+                       init_mode, B.LOD_DEVICE if lod_on_device else B.LOD_HOST, 0)
+    keep.append(slots)
+    return desc, keep
+
+
+def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, pooltype="SUM", *,
+                              pad_value: float = 0.0, padding_idx: int = -1, use_cvm: Optional[bool] = True,
+                              cvm_offset: int = 2, concat: bool = False, scale_mode: int = B.SCALE_DIVIDE,
+                              init_mode: int = B.INIT_ZERO, check: bool = True, plan_only: bool = False,
+                              out: Optional[torch.Tensor] = None, ctx: Optional[Context] = None):
+    """lookup_table_v2 -> sequence_pool -> cvm for every slot of a CTR batch in one launch.
+
+    W         one table [N, D] shared by all slots, or a list with one table per slot
+    Ids       per slot: 1-D int64/int32 ids, LoD-packed
+    lods      per slot: offsets of the last LoD level -- a host sequence / numpy array, or a
+              CUDA uint64-as-int64 tensor when the offsets are already on the device
+    pooltype  one name or one per slot
+    use_cvm   True: cvm(use_cvm=True); False: cvm(use_cvm=False) (drops cvm_offset columns);
+              None: no cvm op after the pool
+    concat    write all slots into one [B, S*D_out] tensor (concat(axis=1) fused, as
+              fusion_seqpool_cvm_concat does)
+    Returns a list of [B_s, D_out] tensors, or the [B, S*D_out] tensor when concat=True;
+    with plan_only=True returns a FusedPlan instead (nothing launched yet).
+    """
+    S = len(Ids)
+    tables = _as_list(W, S)
+    if len(tables) != S:
+        raise InvalidArgument("W must be one table or one per slot")
+    pools = _as_list(pooltype, S)
+    for p in pools:
+        if p not in B.POOLTYPES:
+            raise InvalidArgument(f"unsupported pooling pooltype: {p}")
+    t0 = tables[0]
+    _need_cuda(t0, "W")
+    if t0.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise Unimplemented(f"dtype {t0.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    dim = t0.shape[1]
+    for t in tables:
+        if t.dim() != 2 or t.shape[1] != dim or t.dtype != t0.dtype or not t.is_contiguous():
+            raise InvalidArgument("all tables must be contiguous [N, D] with equal D and dtype")
+    for i in Ids:
+        _need_cuda(i, "Ids")
+        if i.dtype not in _IDT:
+            raise Unimplemented("emebdding input only support int32 and int64")
+    ctx = ctx or default_context(t0.device)
+    cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
+    d_out = dim - cvm_offset if cvm_mode == B.CVM_STRIP else dim
+    lod_on_device = isinstance(lods[0], torch.Tensor)
+    n_segs = [(l.numel() if lod_on_device else len(l)) - 1 for l in lods]
+    ids_c = [i.contiguous().view(-1) for i in Ids]
+    if concat:
+        if len(set(n_segs)) != 1:
+            raise InvalidArgument("Batchsize of all inputs should be equal.")
+        if out is None:
+            out = torch.empty((n_segs[0], S * d_out), dtype=t0.dtype, device=t0.device)
+        outs = [out[:, s * d_out:(s + 1) * d_out] for s in range(S)]
+        ld = S * d_out
+    else:
+        outs = [torch.empty((n, d_out), dtype=t0.dtype, device=t0.device) for n in n_segs]
+        ld = d_out
+    desc, keep = _build_desc(tables, ids_c, lods, pools, outs, ld, dim=dim, dtype=_DT[t0.dtype],
+                             pad_value=pad_value, padding_idx=padding_idx, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
+                             scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device)
+    result = out if concat else outs
+    if plan_only:
+        h = C.c_void_p()
+        B.check(B.lib().ctrfe_plan_create(ctx.handle, C.byref(desc), ctx.stream(), C.byref(h)))
+        return FusedPlan(ctx, h, result, (tables, ids_c, outs, out, keep))
+    B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
+    if check:
+        ctx.check_ids()
+    return result
+
+
+def _dense_slots(Xs, lods):
+    for x in Xs:
+        _need_cuda(x, "X")
+    w = Xs[0].shape[1] if Xs[0].dim() == 2 else int(np.prod(Xs[0].shape[1:]))
+    flat = [x.contiguous().view(x.shape[0], -1) for x in Xs]
+    for f in flat:
+        if f.shape[1] != w:
+            raise InvalidArgument("Width of all inputs should be equal.")
+    lasts = [_last_level(l) for l in lods]
+    for f, l in zip(flat, lasts):
+        if l[-1] > f.shape[0]:
+            raise InvalidArgument("The last LoD offset exceeds the first dimension of Input(X).")
+    return flat, lasts, w
+
+
+def fused_seqpool_cvm(X: Sequence[torch.Tensor], lods: Sequence, CVM: Optional[torch.Tensor] = None,
+                      pooltype: str = "SUM", pad_value: float = 0.0, use_cvm: bool = True, cvm_offset: int = 2,
+                      *, ctx: Optional[Context] = None) -> List[torch.Tensor]:
+    """PaddleBox's multi-slot op over PRE-PULLED values (fused/fused_seqpool_cvm_op.cc:120-150):
+    X is a list of [K_s, D] LoD tensors, one per slot; SUM only; the accumulator STARTS at
+    pad_value (fused_seqpool_cvm_op.cu:49), so an empty sequence yields pad_value too;
+    use_cvm=False drops cvm_offset leading columns.  One launch instead of the reference's
+    two kernels + intermediate buffer."""
+    if pooltype != "SUM":
+        raise InvalidArgument("fused_seqpool_cvm only supports pooltype SUM")  # op maker InEnum({"SUM"})
+    flat, lasts, w = _dense_slots(X, lods)
+    if not flat:
+        return []
+    if flat[0].dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise Unimplemented("fused_seqpool_cvm: float32/float16/bfloat16 only")
+    ctx = ctx or default_context(flat[0].device)
+    S = len(flat)
+    cvm_mode = B.CVM_USE if use_cvm else B.CVM_STRIP
+    d_out = w if use_cvm else w - cvm_offset
+    outs = [torch.empty((len(l) - 1, d_out), dtype=flat[0].dtype, device=flat[0].device) for l in lasts]
+    desc, keep = _build_desc(flat, [None] * S, lasts, ["SUM"] * S, outs, d_out, dim=w, dtype=_DT[flat[0].dtype],
+                             pad_value=pad_value, padding_idx=-1, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
+                             scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_PAD, lod_on_device=False)
+    B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
+    return outs
+
+
+def fusion_seqpool_cvm_concat(X: Sequence[torch.Tensor], lods: Sequence, CVM: Optional[torch.Tensor] = None,
+                              pooltype: str = "SUM", use_cvm: bool = True, axis: int = 1, *,
+                              ctx: Optional[Context] = None) -> torch.Tensor:
+    """The CPU predictor's fused op (fused/fusion_seqpool_cvm_concat_op.cc:97-159): per slot
+    sequence_pool (SUM / AVERAGE / SQRT, jit kernel: scale by reciprocal) -> cvm(use_cvm=True)
+    -> written at column s*w of Out [B, S*w].  axis must be 1, use_cvm must be True, as the
+    reference enforces (:58-70)."""
+    if axis != 1:
+        raise InvalidArgument("fusion_seqpool_cvm_concat only supports concat axis=1 yet.")
+    if not use_cvm:
+        raise InvalidArgument("fusion_seqpool_cvm_concat only supports use_cvm is true yet.")
+    if pooltype not in ("SUM", "AVERAGE", "SQRT"):
+        raise InvalidArgument(f"fusion_seqpool_cvm_concat: unsupported pooltype {pooltype}")
+    flat, lasts, w = _dense_slots(X, lods)
+    S = len(flat)
+    bs = len(lasts[0]) - 1
+    for l in lasts:
+        if len(l) - 1 != bs:
+            raise InvalidArgument("Batchsize of all inputs should be equal.")
+    ctx = ctx or default_context(flat[0].device)
+    out = torch.empty((bs, S * w), dtype=flat[0].dtype, device=flat[0].device)
+    outs = [out[:, s * w:(s + 1) * w] for s in range(S)]
+    desc, keep = _build_desc(flat, [None] * S, lasts, [pooltype] * S, outs, S * w, dim=w, dtype=_DT[flat[0].dtype],
+                             pad_value=0.0, padding_idx=-1, cvm_mode=B.CVM_USE, cvm_offset=2,
+                             scale_mode=B.SCALE_RECIPROCAL, init_mode=B.INIT_ZERO, lod_on_device=False)
+    B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
+    return out
+
+
+def fused_embedding_seq_pool(W: torch.Tensor, Ids: torch.Tensor, lod, combiner: str = "sum",
+                             padding_idx: int = -1, is_sparse: bool = False, *, check: bool = True,
+                             ctx: Optional[Context] = None) -> torch.Tensor:
+    """Gather + SUM per sequence (fused/fused_embedding_seq_pool_op.h:84-127, the EmbSeqPool
+    route: first row copied, the rest added in id order).  Ids: [K, 1] int64 with one LoD
+    level; Out: [num_seq, D]."""
+    if combiner != "sum":
+        raise Unimplemented("fused_embedding_seq_pool only supports combiner 'sum'")
+    if Ids.dim() == 2 and Ids.shape[1] != 1:
+        raise Unimplemented("fused_embedding_seq_pool: ids last dimension > 1 is not supported here")
+    if len(lod) != 1:
+        raise InvalidArgument("The LoD level of Input(Ids) should be 1.")
+    return ctr_fused_emb_seqpool_cvm(W, [Ids.reshape(-1)], [lod[0]], "SUM", padding_idx=padding_idx, use_cvm=None,
+                                     init_mode=B.INIT_FIRST_ROW, check=check, ctx=ctx)[0]
+
+
+# ------------------------------------------------------------------------------------------
+# host-buffer doorway (what a predictor feeding from CPU memory calls)
+# ------------------------------------------------------------------------------------------
+class HostFrontEnd:
+    """The fused front end with HOST inputs and outputs: per-slot id arrays and LoD offsets in
+    (pinned) host memory in, the pooled [B, S*D_out] block in pinned host memory out.  This is
+    the shape of the reference's feed path -- ZeroCopyTensor::CopyFromCpu + SetLoD per slot,
+    CopyToCpu on the result (inference/api/details/zero_copy_tensor.cc) -- around one fused
+    launch.  Device staging is allocated once and reused; run() is synchronous on return."""
+
+    def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
+                 padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2,
+                 ctx: Optional[Context] = None):
+        tables = _as_list(W, n_slots)
+        t0 = tables[0]
+        _need_cuda(t0, "W")
+        self.tables, self.S, self.B = tables, n_slots, batch
+        self.pools = _as_list(pooltype, n_slots)
+        self.kw = dict(pad_value=pad_value, padding_idx=padding_idx, use_cvm=use_cvm, cvm_offset=cvm_offset)
+        self.ctx = ctx or default_context(t0.device)
+        d_out = t0.shape[1] - (cvm_offset if use_cvm is False else 0)
+        self.dev_ids = [torch.empty(max_ids_per_slot, dtype=torch.int64, device=t0.device) for _ in range(n_slots)]
+        self.dev_out = torch.empty((batch, n_slots * d_out), dtype=t0.dtype, device=t0.device)
+        self.host_out = torch.empty((batch, n_slots * d_out), dtype=t0.dtype, pin_memory=True)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run(self, ids_host: Sequence[torch.Tensor], lods_host: Sequence[np.ndarray], check: bool = False):
+        ids_dev = []
+        h2d = 0
+        for s in range(self.S):
+            n = ids_host[s].numel()
+            d = self.dev_ids[s][:n]
+            d.copy_(ids_host[s], non_blocking=True)
+            ids_dev.append(d)
+            h2d += n * 8 + lods_host[s].size * 8
+        ctr_fused_emb_seqpool_cvm(self.tables if len(self.tables) > 1 else self.tables[0], ids_dev, lods_host,
+                                  self.pools, concat=True, out=self.dev_out, check=False, ctx=self.ctx, **self.kw)
+        self.host_out.copy_(self.dev_out, non_blocking=True)
+        if check:
+            self.ctx.check_ids()  # synchronises
+        else:
+            torch.cuda.current_stream(self.dev_out.device).synchronize()
+        self.h2d_bytes, self.d2h_bytes = h2d, self.host_out.numel() * self.host_out.element_size()
+        return self.host_out

@@ -1,0 +1,430 @@
+"""GPU parity tests proper: the sm_100a kernels, called through the C ABI (via the ctypes
+host mirror), against the CPU oracle on identical inputs and against the committed golden
+fixtures.  Bars (BASELINE.json north_star):
+  * gathered rows and MAX/LAST/FIRST pooling: bit-exact;
+  * SUM/AVERAGE/SQRT in fp32: bit-exact (summation order is preserved), asserted as such;
+  * CVM column 0: <= 1 ulp of the oracle's double-log (rtol 2e-7); column 1 (a cancellation):
+    rtol 1e-6 + atol 1e-6 (the reference's own tests use atol 1e-5, op_test.py:1776);
+  * fp16/bf16: rtol 1e-2 required, bit-exact observed (single rounding, same order).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def env():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import __graft_entry__ as g
+    g.build()
+    from oracle import oracle as O
+    from paddle_infer_b200 import _lib as B
+    from paddle_infer_b200 import ops
+    # the native library must be the thing that runs
+    assert B.lib().ctrfe_version() >= 100
+    return ops, O, B, torch.device("cuda:0")
+
+
+def _t(a, dev, bf16=False):
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    return t.view(torch.bfloat16) if bf16 else t
+
+
+def _np(t):
+    if t.dtype == torch.bfloat16:
+        return t.view(torch.int16).cpu().numpy().view(np.uint16)
+    return t.cpu().numpy()
+
+
+def _assert_cvm_close(got, want, use_cvm, exact_tail=True):
+    got, want = np.asarray(got, np.float32), np.asarray(want, np.float32)
+    if use_cvm:
+        np.testing.assert_allclose(got[..., 0], want[..., 0], rtol=2e-7, atol=0)
+        np.testing.assert_allclose(got[..., 1], want[..., 1], rtol=1e-6, atol=1e-6)
+        np.testing.assert_array_equal(got[..., 2:], want[..., 2:])
+    else:
+        np.testing.assert_array_equal(got, want)
+
+
+# ------------------------------------------------------------------ golden fixtures on the GPU
+def test_golden_lookup_table_v2(env, golden):
+    ops, O, B, dev = env
+    arrays, meta = golden["lookup_table_v2"]
+    for name, m in meta.items():
+        table, ids = arrays[f"{name}/table"], arrays[f"{name}/ids"]
+        out = ops.lookup_table_v2(_t(table, dev), _t(ids, dev), m["padding_idx"])
+        assert tuple(out.shape) == ids.shape + (31,)
+        np.testing.assert_array_equal(out.cpu().numpy(), arrays[f"{name}/out"], err_msg=name)
+
+
+def test_golden_sequence_pool(env, golden):
+    ops, O, B, dev = env
+    arrays, meta = golden["sequence_pool"]
+    for cls, m in meta.items():
+        x, want = arrays[f"{cls}/x"], arrays[f"{cls}/out"]
+        a = m["attrs"]
+        r = ops.sequence_pool(_t(x, dev), m["offsets"], a["pooltype"], a["pad_value"], is_test=a.get("is_test", False))
+        got = r.Out.cpu().numpy()
+        assert got.shape == want.shape, cls
+        # vs the reference's numpy formula at the reference's tolerance
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5, err_msg=cls)
+        # vs the oracle: bit-exact
+        np.testing.assert_array_equal(got, O.sequence_pool(x, m["offsets"][-1], a["pooltype"], a["pad_value"]), err_msg=cls)
+        # two-level LoD: Out carries level 0 (sequence_pool_op.h:62-70)
+        assert r.lod == ([m["offsets"][0]] if len(m["offsets"]) == 2 else [])
+        if a["pooltype"] == "MAX" and not a.get("is_test", False):
+            _, idx = O.sequence_pool(x, m["offsets"][-1], "MAX", a["pad_value"], is_test=False)
+            np.testing.assert_array_equal(r.MaxIndex.cpu().numpy(), idx, err_msg=cls)
+        else:
+            assert r.MaxIndex is None
+
+
+def test_golden_cvm(env, golden):
+    ops, O, B, dev = env
+    arrays, meta = golden["cvm"]
+    for name, m in meta.items():
+        x, want = arrays[f"{name}/x"], arrays[f"{name}/y"]
+        got = ops.cvm(_t(x, dev), None, m["use_cvm"]).cpu().numpy()
+        assert got.shape == want.shape
+        _assert_cvm_close(got, want, m["use_cvm"])
+        _assert_cvm_close(got, O.cvm(x, m["use_cvm"]), m["use_cvm"])
+
+
+def test_golden_fusion_seqpool_cvm_concat(env, golden):
+    ops, O, B, dev = env
+    arrays, meta = golden["fusion_seqpool_cvm_concat"]
+    for key, m in meta.items():
+        S = m["n_slots"]
+        from paddle_infer_b200.lod import lengths_to_offsets
+        lods = [lengths_to_offsets(l) for l in m["lods_lengths"]]
+        xs = [arrays[f"{key}/x{i}"] for i in range(S)]
+        got = ops.fusion_seqpool_cvm_concat([_t(x, dev) for x in xs], lods, None, m["pooltype"]).cpu().numpy()
+        want = arrays[f"{key}/out"]
+        assert got.shape == want.shape
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5, err_msg=key)
+        ids = [np.arange(x.shape[0], dtype=np.int64) for x in xs]
+        orc = O.fused_forward(xs, ids, [l[0] for l in lods], [m["pooltype"]] * S, cvm_mode=O.CVM_USE, concat=True,
+                              scale_mode=O.SCALE_RECIPROCAL)
+        w = m["w"]
+        _assert_cvm_close(got.reshape(-1, S, w), orc.reshape(-1, S, w), True)
+
+
+# ------------------------------------------------------------------ the fused path, swept
+def _random_case(rng, S, Bsz, N, D, max_len, dtype, empty_frac=0.15):
+    if dtype == "f32":
+        table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+    elif dtype == "f16":
+        table = rng.uniform(-1, 1, (N, D)).astype(np.float16)
+    else:
+        from oracle import oracle as O
+        table = O.f32_to_bf16_bits(rng.uniform(-1, 1, (N, D)).astype(np.float32))
+    if D >= 2:  # show / click columns: small non-negative integers, click <= show
+        show = rng.integers(0, 16, N)
+        click = rng.integers(0, show + 1)
+        if dtype == "bf16":
+            from oracle import oracle as O
+            table[:, 0] = O.f32_to_bf16_bits(show.astype(np.float32))
+            table[:, 1] = O.f32_to_bf16_bits(click.astype(np.float32))
+        else:
+            table[:, 0], table[:, 1] = show, click
+    lods, ids = [], []
+    for _ in range(S):
+        l = rng.integers(0, max_len + 1, Bsz)
+        l[rng.random(Bsz) < empty_frac] = 0
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        lods.append(lod)
+        ids.append(rng.integers(0, N, int(lod[-1])).astype(np.int64))
+    return table, ids, lods
+
+
+POOLS = ["SUM", "AVERAGE", "SQRT", "MAX", "LAST", "FIRST"]
+
+
+@pytest.mark.parametrize("dtype", ["f32", "f16", "bf16"])
+@pytest.mark.parametrize("D", [8, 16, 64, 128, 11, 3, 200, 1000])
+def test_fused_matches_oracle(env, dtype, D):
+    """All pooltypes x cvm modes; D covers 128-bit lanes (8..128), the scalar fallback
+    (11, 3: the reference fixtures' widths), multi-tile rows (200, 1000)."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng({"f32": 1, "f16": 2, "bf16": 3}[dtype] * 10007 + D)
+    S, Bsz, N = 6, 97, 500
+    table, ids, lods = _random_case(rng, S, Bsz, N, D, 9, dtype)
+    bf16 = dtype == "bf16"
+    tt = _t(table, dev, bf16)
+    ids_t = [_t(i, dev) for i in ids]
+    pad_idx = int(ids[0][0])
+    for use_cvm, cvm_mode in ((None, O.CVM_NONE), (True, O.CVM_USE), (False, O.CVM_STRIP)):
+        got = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods, POOLS, pad_value=0.1, padding_idx=pad_idx,
+                                            use_cvm=use_cvm)
+        want = O.fused_forward([table], ids, lods, POOLS, pad_value=0.1, padding_idx=pad_idx, cvm_mode=cvm_mode,
+                               bf16=bf16)
+        for s in range(S):
+            g, w = _np(got[s]), want[s]
+            assert g.shape == w.shape
+            if dtype == "f32":
+                _assert_cvm_close(g, w, use_cvm is True)
+            else:
+                gf = O.bf16_bits_to_f32(g) if bf16 else g.astype(np.float32)
+                wf = O.bf16_bits_to_f32(w) if bf16 else w.astype(np.float32)
+                np.testing.assert_allclose(gf, wf, rtol=1e-2, atol=1e-3)       # the stated bar
+                tail = slice(2, None) if use_cvm is True else slice(None)
+                np.testing.assert_array_equal(g[:, tail], w[:, tail])            # observed: bit-exact
+                if POOLS[s] in ("MAX", "LAST", "FIRST"):
+                    np.testing.assert_array_equal(g[:, tail], w[:, tail])
+
+
+def test_fused_concat_int32_ids_and_per_slot_tables(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(123)
+    S, Bsz, N, D = 5, 64, 300, 16
+    tabs, ids, lods = [], [], []
+    for s in range(S):
+        t, i, l = _random_case(rng, 1, Bsz, N + s, D, 7, "f32")
+        tabs.append(t), ids.append(i[0].astype(np.int32)), lods.append(l[0])
+    got = ops.ctr_fused_emb_seqpool_cvm([_t(t, dev) for t in tabs], [_t(i, dev) for i in ids], lods,
+                                        ["SUM", "SQRT", "AVERAGE", "MAX", "SUM"], use_cvm=True, concat=True)
+    want = O.fused_forward(tabs, ids, lods, ["SUM", "SQRT", "AVERAGE", "MAX", "SUM"], cvm_mode=O.CVM_USE, concat=True)
+    _assert_cvm_close(got.cpu().numpy().reshape(Bsz, S, D), want.reshape(Bsz, S, D), True)
+
+
+def test_fused_modes_reciprocal_firstrow_padinit(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(77)
+    table, ids, lods = _random_case(rng, 3, 50, 200, 16, 12, "f32", empty_frac=0.0)
+    tt, ids_t = _t(table, dev), [_t(i, dev) for i in ids]
+    for kw_gpu, kw_orc in (
+        (dict(scale_mode=B.SCALE_RECIPROCAL), dict(scale_mode=O.SCALE_RECIPROCAL)),
+        (dict(init_mode=B.INIT_PAD, pad_value=0.25), dict(init_mode=O.INIT_PAD, pad_value=0.25)),
+    ):
+        got = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods, ["SUM", "AVERAGE", "SQRT"], use_cvm=None, **kw_gpu)
+        want = O.fused_forward([table], ids, lods, ["SUM", "AVERAGE", "SQRT"], **kw_orc)
+        for g, w in zip(got, want):
+            np.testing.assert_array_equal(g.cpu().numpy(), w)
+    # first-row init (EmbSeqPool order, refer.h:513-528) on non-empty sequences, incl. a -0.0 row
+    table2 = table.copy()
+    table2[5] = -0.0
+    lens = rng.integers(1, 6, 40)
+    lod = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    idv = rng.integers(0, 200, int(lod[-1])).astype(np.int64)
+    idv[lod[:-1].astype(np.int64)] = 5  # every sequence starts with the -0.0 row
+    out = ops.fused_embedding_seq_pool(_t(table2, dev), _t(idv, dev).reshape(-1, 1), [lod])
+    want = O.fused_forward([table2], [idv], [lod], ["SUM"], init_mode=O.INIT_FIRST_ROW)[0]
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    R = O.ref_lib()
+    if R is not None:  # and the reference's own EmbSeqPool agrees to the bit
+        ref = np.empty_like(want)
+        assert R.ref_embseqpool_lod_f32(table2.ctypes.data, 200, 16, idv.ctypes.data, lod.ctypes.data, 40,
+                                        ref.ctypes.data, 16) == 0
+        np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+
+
+def test_fused_seqpool_cvm_paddlebox(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(31)
+    xs, lods = [], []
+    for s in range(4):
+        lens = rng.integers(0, 6, 33)
+        lod = [0] + list(np.cumsum(lens))
+        x = rng.uniform(0, 2, (int(lod[-1]), 12)).astype(np.float32)
+        xs.append(x), lods.append([lod])
+    for use_cvm in (True, False):
+        got = ops.fused_seqpool_cvm([_t(x, dev) for x in xs], lods, None, "SUM", 0.5, use_cvm, 2)
+        for x, l, g in zip(xs, lods, got):
+            want = O.fused_seqpool_cvm(x, l[0], 0.5, use_cvm, 2, log_mode=O.LOG_DOUBLE)
+            _assert_cvm_close(g.cpu().numpy(), want, use_cvm)
+            # and within 1e-6 of the float-log variant the reference GPU kernel computes
+            wf = O.fused_seqpool_cvm(x, l[0], 0.5, use_cvm, 2, log_mode=O.LOG_FLOAT)
+            np.testing.assert_allclose(g.cpu().numpy(), wf, rtol=1e-6, atol=1e-6)
+
+
+# ------------------------------------------------------------------ edge cases
+def test_edge_cases(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(5)
+    table = rng.uniform(-1, 1, (64, 16)).astype(np.float32)
+    tt = _t(table, dev)
+    # all sequences empty
+    lod = np.zeros(10, np.uint64)
+    out = ops.ctr_fused_emb_seqpool_cvm(tt, [torch.empty(0, dtype=torch.int64, device=dev)], [lod], "SUM",
+                                        pad_value=0.3, use_cvm=None)[0]
+    assert (out.cpu().numpy() == np.float32(0.3)).all()
+    # one long sequence (many id batches), one sequence of one row, trailing empties
+    k = 3000
+    ids = rng.integers(0, 64, k + 1).astype(np.int64)
+    lod = np.array([0, k, k + 1, k + 1, k + 1], np.uint64)
+    for pool in POOLS:
+        got = ops.ctr_fused_emb_seqpool_cvm(tt, [_t(ids, dev)], [lod], pool, use_cvm=None)[0].cpu().numpy()
+        want = O.fused_forward([table], [ids], [lod], [pool])[0]
+        np.testing.assert_array_equal(got, want, err_msg=pool)
+    # NaN / inf / -0.0 / denormal rows: MAX keeps the reference's "first row, then strictly greater"
+    t2 = table.copy()
+    t2[0, :] = np.nan
+    t2[1, :] = -np.inf
+    t2[2, :] = -0.0
+    t2[3, :] = 0.0
+    t2[4, :] = 1e-40  # denormal: flushed in arithmetic, compared as zero (FTZ/DAZ)
+    ids = np.array([0, 7, 1, 1, 2, 3, 3, 2, 8, 0, 4, 3, 4, 4], np.int64)
+    lod = np.array([0, 2, 4, 6, 8, 10, 12, 14], np.uint64)
+    for pool in ("MAX", "SUM", "FIRST", "LAST"):
+        got = ops.ctr_fused_emb_seqpool_cvm(_t(t2, dev), [_t(ids, dev)], [lod], pool, use_cvm=None)[0].cpu().numpy()
+        want = O.fused_forward([t2], [ids], [lod], [pool])[0]
+        np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32), err_msg=pool)
+
+
+def test_bad_ids_raise_like_the_reference(env):
+    ops, O, B, dev = env
+    table = torch.ones(32, 8, device=dev)
+    for bad in (32, -1, 1 << 40):
+        ids = torch.tensor([1, 2, bad, 3], dtype=torch.int64, device=dev)
+        with pytest.raises(B.BadIdError) as e:
+            ops.lookup_table_v2(table, ids)
+        assert e.value.position == 2 and e.value.id_value == bad
+        assert "expected >= 0 and <" in str(e.value)
+        with pytest.raises(ValueError) as e:
+            ops.ctr_fused_emb_seqpool_cvm(table, [ids[:2], ids], [[0, 1, 2], [0, 2, 4]], "SUM", use_cvm=None)
+        assert e.value.slot == 1 and e.value.position == 2
+    # padding_idx is honoured before the range check, and the flag is clear again
+    ids = torch.tensor([1, 99], dtype=torch.int64, device=dev)
+    out = ops.lookup_table_v2(table, ids, padding_idx=99)
+    assert out[0].eq(1).all() and out[1].eq(0).all()
+    # host-side argument checks mirror the reference's enforce messages
+    with pytest.raises(ops.InvalidArgument, match="does not contain LoD"):
+        ops.sequence_pool(table, [], "SUM")
+    with pytest.raises(ops.InvalidArgument, match="no more than 2"):
+        ops.sequence_pool(table, [[0, 1], [0, 1], [0, 32]], "SUM")
+    with pytest.raises(ops.InvalidArgument, match="illegal"):
+        ops.sequence_pool(table, [[0, 3], [0, 32]], "SUM")
+    with pytest.raises(ops.InvalidArgument, match="rank should be 2"):
+        ops.cvm(torch.ones(2, 3, 4, device=dev))
+    with pytest.raises(Exception, match="non-decreasing"):
+        ops.sequence_pool(table, [[0, 5, 3, 32]], "SUM")
+
+
+def test_unfused_chain_equals_fused(env):
+    """lookup_table_v2 -> sequence_pool -> cvm as three launches equals the fused launch (fp32)."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(2)
+    table, ids, lods = _random_case(rng, 2, 300, 1000, 16, 8, "f32")
+    tt = _t(table, dev)
+    for s, pool in enumerate(("SUM", "MAX")):
+        rows = ops.lookup_table_v2(tt, _t(ids[s], dev))
+        np.testing.assert_array_equal(rows.cpu().numpy(), table[ids[s]])
+        pooled = ops.sequence_pool(rows, [list(lods[s])], pool, 0.0, is_test=True).Out
+        y = ops.cvm(pooled, None, True)
+        fused = ops.ctr_fused_emb_seqpool_cvm(tt, [_t(ids[s], dev)], [lods[s]], pool, use_cvm=True)[0]
+        np.testing.assert_array_equal(y.cpu().numpy(), fused.cpu().numpy())
+
+
+def test_plan_reuse_and_device_lod(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(9)
+    table, ids, lods = _random_case(rng, 4, 128, 2000, 16, 8, "f32")
+    tt, ids_t = _t(table, dev), [_t(i, dev) for i in ids]
+    lods_dev = [torch.from_numpy(l.astype(np.int64)).to(dev) for l in lods]
+    plan = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods_dev, "SUM", use_cvm=True, concat=True, plan_only=True)
+    assert plan.num_kernels() == 1
+    want = O.fused_forward([table], ids, lods, ["SUM"] * 4, cvm_mode=O.CVM_USE, concat=True)
+    for _ in range(3):
+        plan.outs.zero_()
+        plan.launch()
+        torch.cuda.synchronize()
+        _assert_cvm_close(plan.outs.cpu().numpy().reshape(128, 4, 16), want.reshape(128, 4, 16), True)
+    plan.ctx.check_ids()
+    plan.close()
+
+
+# ------------------------------------------------------------------ BASELINE configs
+def _run_config(env, cfg, batch=None, rows=None, slots=None, sample=None):
+    """Run one synthetic config on the GPU; check a sample of sequences against the oracle
+    fed with exactly the table rows the sample touches (regenerated on the host)."""
+    ops, O, B, dev = env
+    from benchtools import synth
+    b = synth.draw_batch(cfg, 0, batch, slots, rows)
+    N = cfg.rows if rows is None else rows
+    S = len(b.ids)
+    Bsz = b.lods[0].size - 1
+    tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
+    n_tab = 1 if cfg.shared_table else S
+    tabs = []
+    for t in range(n_tab):
+        tab = torch.empty((N, cfg.dim), dtype=tdt, device=dev)
+        synth.fill_table(tab, cfg.seed + 1000 * t, cvm_cols=cfg.use_cvm is not None)
+        tabs.append(tab)
+    ids_t = [torch.from_numpy(i).to(dev) for i in b.ids]
+    out = ops.ctr_fused_emb_seqpool_cvm(tabs if n_tab > 1 else tabs[0], ids_t, b.lods, cfg.pooltypes[:S],
+                                        use_cvm=cfg.use_cvm, concat=True)
+    torch.cuda.synchronize()
+    got = _np(out).reshape(Bsz, S, cfg.d_out)
+    # oracle on a sample of sequences, with a compact table of just the rows they need
+    rng = np.random.default_rng(1)
+    pick = np.arange(Bsz) if sample is None or sample >= Bsz else np.sort(rng.choice(Bsz, sample, replace=False))
+    cvm_mode = O.CVM_NONE if cfg.use_cvm is None else (O.CVM_USE if cfg.use_cvm else O.CVM_STRIP)
+    for s in range(S):
+        lod = b.lods[s].astype(np.int64)
+        seg_ids = [b.ids[s][lod[i]:lod[i + 1]] for i in pick]
+        flat = np.concatenate(seg_ids) if seg_ids else np.empty(0, np.int64)
+        uniq, inv = np.unique(flat, return_inverse=True)
+        compact = synth.table_rows_numpy(cfg.seed + (1000 * s if n_tab > 1 else 0), uniq, cfg.dim, cfg.dtype,
+                                         cvm_cols=cfg.use_cvm is not None)
+        if uniq.size == 0:
+            compact = np.zeros((1, cfg.dim), compact.dtype)
+        sub_lod = np.concatenate([[0], np.cumsum([len(x) for x in seg_ids])]).astype(np.uint64)
+        want = O.fused_forward([compact], [inv.astype(np.int64)], [sub_lod], [cfg.pooltypes[s]], cvm_mode=cvm_mode,
+                               bf16=cfg.dtype == "bf16")[0]
+        g = got[pick, s, :]
+        if cfg.dtype == "f32":
+            _assert_cvm_close(g, want, cfg.use_cvm is True)
+        else:
+            np.testing.assert_array_equal(g, want)
+    return got, b
+
+
+def test_config1_full(env):
+    from benchtools import synth
+    _run_config(env, synth.configs()["cfg1"])
+
+
+def test_config2_full_size_sampled(env):
+    """DeepFM: 39 slots x 8192, one shared 1e8 x 16 fp32 table (6.4 GB), Zipf ids."""
+    from benchtools import synth
+    cfg = synth.configs()["cfg2"]
+    got, b = _run_config(env, cfg, sample=512)
+    # size-independent property on the full output: column 2.. of an empty sequence is pad_value (0)
+    for s in (0, 17, 38):
+        empty = np.diff(b.lods[s].astype(np.int64)) == 0
+        assert empty.any() and (got[empty, s, 2:] == 0).all()
+
+
+def test_config3_reduced_rows(env):
+    """DLRM: 26 tables, bf16 D=64, mixed SUM/AVERAGE/SQRT, no CVM; rows cut to 1e6 per table
+    and batch to 4096 so 26 tables fit beside the other tests (full size runs in bench.py)."""
+    from benchtools import synth
+    _run_config(env, synth.configs()["cfg3"], batch=4096, rows=1_000_000, sample=256)
+
+
+def test_config5_long_sequences(env):
+    """8 slots x avg 200 ids, D=128 fp16, MAX and SQRT; rows cut to 2e6 per table."""
+    from benchtools import synth
+    _run_config(env, synth.configs()["cfg5"], batch=512, rows=2_000_000, sample=128)
+
+
+def test_linearity_property_full_batch(env):
+    """SUM pooling is linear in the table: pool(2*T) == 2*pool(T) exactly (power-of-two scale),
+    checked on every output of a cfg2-shaped batch without the oracle."""
+    ops, O, B, dev = env
+    from benchtools import synth
+    cfg = synth.configs()["cfg2"]
+    b = synth.draw_batch(cfg, 3, batch=8192, slots=8, rows=1_000_000)
+    tab = torch.empty((1_000_000, 16), dtype=torch.float32, device=dev)
+    synth.fill_table(tab, cfg.seed)
+    ids_t = [torch.from_numpy(i).to(dev) for i in b.ids]
+    a = ops.ctr_fused_emb_seqpool_cvm(tab, ids_t, b.lods, "SUM", use_cvm=None, concat=True)
+    c = ops.ctr_fused_emb_seqpool_cvm(tab * 2, ids_t, b.lods, "SUM", use_cvm=None, concat=True)
+    assert torch.equal(a * 2, c)
+    # checksum of checksums: sum over all pooled rows == sum over all gathered rows (fp64)
+    total_rows = sum(tab[i].double().sum().item() for i in ids_t)
+    assert abs(a.double().sum().item() - total_rows) <= 1e-6 * max(1.0, abs(total_rows))
