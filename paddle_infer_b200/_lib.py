@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libctrfe.so")
+LIB_PATH = os.environ.get("CTRFE_LIB") or os.path.join(_HERE, "libctrfe.so")  # CTRFE_LIB: tuning builds
 
 # enums of include/ctrfe.h
 OK, ERR_BAD_ID, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED, ERR_NCCL = range(6)

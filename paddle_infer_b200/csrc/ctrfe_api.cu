@@ -1,11 +1,12 @@
 // ctrfe_api.cu -- the C ABI declared in include/ctrfe.h: argument checking (mirroring the
-// reference's enforce checks), one-copy LoD/descriptor upload, kernel launches.
+// reference's enforce checks), one-copy LoD upload, kernel launches.
 // No CPU compute path exists in this file: every entry point launches sm_100a kernels.
 #include <cuda_runtime.h>
 
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <utility>
 #include <vector>
 
 #include "ctrfe_kernels.cuh"
@@ -49,24 +50,31 @@ struct IdSource {  // what ctrfe_check_ids needs to fetch the offending id value
 struct ctrfe_ctx {
   int device = 0;
   unsigned long long* err_dev = nullptr;   // [1]
-  unsigned long long* err_host = nullptr;  // pinned [2]: flag, id value
+  unsigned long long* err_host = nullptr;  // pinned [2]
   Staging ring[kRing];
   int ring_next = 0;
-  // scratch of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
+  // LoD image of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
   char* scratch = nullptr;
   size_t scratch_cap = 0;
+  // zeros that a padding_idx / out-of-range id reads instead of a table row
+  char* zero_row = nullptr;
+  size_t zero_cap = 0;
   std::vector<IdSource> last_ids;  // slots of the most recent fused launch
+  const void* last_ids_owner = nullptr;  // identity tag only (never dereferenced): skip re-copying
   int sm_count = 148;
 };
 
 struct ctrfe_plan {
   ctrfe_ctx* ctx = nullptr;
-  char* dev = nullptr;       // descriptors + LoD (owned unless borrowed)
+  char* dev = nullptr;  // LoD image when the offsets came from the host
   bool owns_dev = false;
-  ctrfe::FusedParams params{};
+  std::vector<ctrfe::KParams> chunks;  // <= kMaxSlotsPerLaunch slots each: one launch per chunk
+  std::vector<dim3> grids;
+  std::vector<int> modes;                      // kernel MODE of each chunk
+  std::vector<std::pair<int, int>> where;      // caller slot -> (chunk, index in chunk)
   int dtype = 0;
   bool vect = false;
-  dim3 grid{};
+  int g_shift = 0;
   std::vector<IdSource> id_src;
 };
 
@@ -94,6 +102,8 @@ int elem_size(int dtype) {
   }
 }
 
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
 int stage_acquire(ctrfe_ctx* ctx, size_t bytes, Staging** out) {
   Staging& s = ctx->ring[ctx->ring_next];
   ctx->ring_next = (ctx->ring_next + 1) % kRing;
@@ -116,8 +126,7 @@ int stage_acquire(ctrfe_ctx* ctx, size_t bytes, Staging** out) {
 int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
   if (ctx->scratch_cap >= bytes) return CTRFE_OK;
   if (ctx->scratch) {
-    // work already enqueued may still read the old buffer
-    CU(cudaStreamSynchronize(stream));
+    CU(cudaStreamSynchronize(stream));  // work already enqueued may still read the old buffer
     CU(cudaFree(ctx->scratch));
     ctx->scratch = nullptr;
   }
@@ -127,14 +136,25 @@ int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
   return CTRFE_OK;
 }
 
-size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+int zero_row_reserve(ctrfe_ctx* ctx, size_t row_bytes) {
+  if (ctx->zero_cap >= row_bytes) return CTRFE_OK;
+  if (ctx->zero_row) {
+    CU(cudaDeviceSynchronize());
+    CU(cudaFree(ctx->zero_row));
+    ctx->zero_row = nullptr;
+  }
+  size_t cap = row_bytes < (1u << 16) ? (1u << 16) : align_up(row_bytes, 256);
+  CU(cudaMalloc(reinterpret_cast<void**>(&ctx->zero_row), cap));
+  CU(cudaMemset(ctx->zero_row, 0, cap));
+  ctx->zero_cap = cap;
+  return CTRFE_OK;
+}
 
-// Validates a descriptor the way the reference ops' InferShape/Compute do, and derives the
-// launch geometry.  Returns the bytes needed for descriptors + (host) LoDs.
-int plan_geometry(const ctrfe_fused_desc* d, ctrfe::FusedParams* p, bool* vect, dim3* grid,
-                  size_t* bytes_needed) {
+// Validates a descriptor the way the reference ops' InferShape/Compute do, derives the launch
+// geometry and fills everything of the plan that does not depend on where the LoD lives.
+// *lod_bytes = device bytes needed for the host LoDs (0 when they are already on the device).
+int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, size_t* lod_bytes) {
   if (!d || !d->slots || d->n_slots <= 0) return fail(CTRFE_ERR_ARG, "fused: no slots");
-  if (d->n_slots > 65535) return fail(CTRFE_ERR_ARG, "fused: at most 65535 slots per call (got %d)", d->n_slots);
   if (d->dtype != CTRFE_F32 && d->dtype != CTRFE_F16 && d->dtype != CTRFE_BF16)
     return fail(CTRFE_ERR_UNSUPPORTED, "fused: dtype %d not supported (f32, f16, bf16)", d->dtype);
   if (d->dim <= 0 || d->dim > (1 << 20)) return fail(CTRFE_ERR_ARG, "fused: bad dim %lld", (long long)d->dim);
@@ -155,11 +175,10 @@ int plan_geometry(const ctrfe_fused_desc* d, ctrfe::FusedParams* p, bool* vect, 
   const long long row_bytes = d->dim * es;
   const int d_out = static_cast<int>(d->dim) - (d->cvm_mode == CTRFE_CVM_STRIP ? d->cvm_offset : 0);
   bool v = (row_bytes % 16) == 0;
-  long long max_seg = 0;
-  size_t lod_bytes = 0;
+  size_t lb = 0;
   for (int s = 0; s < d->n_slots; ++s) {
     const ctrfe_slot& sl = d->slots[s];
-    if (sl.n_seg < 0) return fail(CTRFE_ERR_ARG, "slot %d: negative n_seg", s);
+    if (sl.n_seg < 0 || sl.n_seg > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "slot %d: n_seg %lld outside [0, 2^31)", s, (long long)sl.n_seg);
     if (sl.n_seg > 0 && (!sl.table || !sl.lod || !sl.out))
       return fail(CTRFE_ERR_ARG, "slot %d: null table / lod / out", s);
     if (sl.pooltype < CTRFE_POOL_AVERAGE || sl.pooltype > CTRFE_POOL_MAX)
@@ -170,58 +189,92 @@ int plan_geometry(const ctrfe_fused_desc* d, ctrfe::FusedParams* p, bool* vect, 
       return fail(CTRFE_ERR_UNSUPPORTED, "slot %d: ids must be int32 or int64", s);
     if (sl.out_ld < d_out) return fail(CTRFE_ERR_ARG, "slot %d: out_ld %lld < output width %d", s,
                                        (long long)sl.out_ld, d_out);
-    if (sl.table_rows < 0) return fail(CTRFE_ERR_ARG, "slot %d: negative table_rows", s);
+    if (sl.table_rows < 0 || sl.table_rows >= 0xfffffffeLL)
+      return fail(CTRFE_ERR_UNSUPPORTED, "slot %d: table_rows %lld outside [0, 2^32 - 2)", s, (long long)sl.table_rows);
     if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
-    if (sl.n_seg > max_seg) max_seg = sl.n_seg;
-    lod_bytes += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+    lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
+  int rc = zero_row_reserve(ctx, static_cast<size_t>(row_bytes));
+  if (rc) return rc;
 
-  p->padding_idx = d->padding_idx;
-  p->dim = static_cast<int>(d->dim);
-  p->row_bytes = static_cast<int>(row_bytes);
   const long long units = v ? row_bytes / 16 : d->dim;  // lane-sized pieces per row
-  int g_shift = 0;
-  while ((1 << g_shift) < units && g_shift < 5) ++g_shift;
-  p->g_shift = g_shift;
-  p->tiles = static_cast<int>((units + (1 << g_shift) - 1) >> g_shift);
-  p->cvm_mode = d->cvm_mode;
-  p->cvm_offset = d->cvm_offset;
-  p->scale_mode = d->scale_mode;
-  p->init_mode = d->init_mode;
-  p->pad_value = d->pad_value;
-  *vect = v;
-  const long long items = max_seg * p->tiles;
-  const long long gx = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
-  if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "fused: batch too large for one launch");
-  *grid = dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(d->n_slots), 1);
-  *bytes_needed = align_up(sizeof(ctrfe::SlotDev) * d->n_slots, 16) +
-                  (d->lod_location == CTRFE_LOD_HOST ? lod_bytes : 0);
+  int g_shift = 5;                                      // the scalar fallback always uses whole warps
+  if (v) { g_shift = 0; while ((1 << g_shift) < units && g_shift < 5) ++g_shift; }
+  const int tiles = static_cast<int>((units + (1 << g_shift) - 1) >> g_shift);
+  plan->ctx = ctx;
+  plan->dtype = d->dtype;
+  plan->vect = v;
+  plan->g_shift = g_shift;
+  plan->chunks.clear();
+  plan->grids.clear();
+  plan->modes.clear();
+  plan->where.assign(d->n_slots, std::make_pair(-1, -1));
+  // Slots are grouped by kernel mode (accumulating vs selecting pools) into launches of at
+  // most kMaxSlotsPerLaunch descriptors; a CTR batch with one pooltype family is ONE launch.
+  int open_chunk[2] = {-1, -1};
+  std::vector<long long> max_seg;
+  for (int s = 0; s < d->n_slots; ++s) {
+    const ctrfe_slot& sl = d->slots[s];
+    const int mode = sl.pooltype >= CTRFE_POOL_LAST ? ctrfe::kModeSelect : ctrfe::kModeAdd;
+    int c = open_chunk[mode];
+    if (c < 0 || plan->chunks[c].n_slots == ctrfe::kMaxSlotsPerLaunch) {
+      plan->chunks.emplace_back();
+      c = static_cast<int>(plan->chunks.size()) - 1;
+      open_chunk[mode] = c;
+      plan->modes.push_back(mode);
+      max_seg.push_back(0);
+      ctrfe::KParams& k = plan->chunks[c];
+      memset(&k, 0, sizeof(k));
+      k.err = ctx->err_dev;
+      k.zero_row = ctx->zero_row;
+      k.padding_idx = d->padding_idx;
+      k.dim = static_cast<int>(d->dim);
+      k.row_bytes = static_cast<int>(row_bytes);
+      k.tiles = tiles;
+      k.cvm_mode = d->cvm_mode;
+      k.cvm_offset = d->cvm_offset;
+      k.scale_mode = d->scale_mode;
+      k.init_mode = d->init_mode;
+      k.pad_value = d->pad_value;
+      k.n_slots = 0;
+    }
+    ctrfe::KParams& k = plan->chunks[c];
+    ctrfe::SlotK& o = k.slots[k.n_slots];
+    plan->where[s] = std::make_pair(c, k.n_slots);
+    ++k.n_slots;
+    o.table = static_cast<const char*>(sl.table);
+    o.ids = sl.ids;
+    o.lod = reinterpret_cast<const unsigned long long*>(sl.lod);  // re-pointed for host LoDs
+    o.out = static_cast<char*>(sl.out);
+    o.out_ld_bytes = sl.out_ld * es;
+    o.table_rows = static_cast<unsigned>(sl.table_rows);
+    o.n_seg = static_cast<unsigned>(sl.n_seg);
+    o.pooltype = static_cast<short>(sl.pooltype);
+    o.id_kind = static_cast<short>(sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2);
+    o.slot_index = s;
+    if (sl.n_seg > max_seg[c]) max_seg[c] = sl.n_seg;
+  }
+  for (size_t c = 0; c < plan->chunks.size(); ++c) {
+    const long long items = max_seg[c] * tiles;
+    const long long gx = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
+    if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "fused: batch too large for one launch");
+    plan->grids.push_back(dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(plan->chunks[c].n_slots), 1));
+  }
+  plan->id_src.resize(d->n_slots);
+  for (int s = 0; s < d->n_slots; ++s)
+    plan->id_src[s] = IdSource{d->slots[s].ids, d->slots[s].ids_dtype == CTRFE_I32};
+  *lod_bytes = d->lod_location == CTRFE_LOD_HOST ? lb : 0;
   return CTRFE_OK;
 }
 
-// Fills the staging image (descriptors, then host LoDs) and validates the LoDs in the same
-// pass: non-decreasing offsets (framework CheckLoD, lod_tensor.h:74-104) and, for dense
-// rows, lod.back() <= rows (sequence_pool_op.h:52-60).
-int plan_stage(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, std::vector<IdSource>* id_src) {
-  auto* sd = reinterpret_cast<ctrfe::SlotDev*>(host_img);
-  size_t off = align_up(sizeof(ctrfe::SlotDev) * d->n_slots, 16);
-  id_src->resize(d->n_slots);
+// Copies the host LoDs into one pinned image, validating them in the same pass:
+// non-decreasing offsets (framework CheckLoD, lod_tensor.h:74-104) and, for dense rows,
+// lod.back() <= rows (sequence_pool_op.h:52-60); re-points the descriptors at the device image.
+int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, ctrfe_plan* plan) {
+  size_t off = 0;
   for (int s = 0; s < d->n_slots; ++s) {
     const ctrfe_slot& sl = d->slots[s];
-    ctrfe::SlotDev& o = sd[s];
-    o.table = static_cast<const char*>(sl.table);
-    o.ids = sl.ids;
-    o.out = static_cast<char*>(sl.out);
-    o.table_rows = sl.table_rows;
-    o.out_ld = sl.out_ld;
-    o.n_seg = sl.n_seg;
-    o.pooltype = sl.pooltype;
-    o.ids_i32 = sl.ids_dtype == CTRFE_I32;
-    (*id_src)[s] = IdSource{sl.ids, o.ids_i32};
-    if (d->lod_location == CTRFE_LOD_DEVICE) {
-      o.lod = reinterpret_cast<const unsigned long long*>(sl.lod);
-      continue;
-    }
+    ctrfe::SlotK& o = plan->chunks[plan->where[s].first].slots[plan->where[s].second];
     auto* dst = reinterpret_cast<uint64_t*>(host_img + off);
     o.lod = reinterpret_cast<const unsigned long long*>(dev_img + off);
     if (sl.n_seg == 0) {
@@ -249,37 +302,51 @@ int plan_stage(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, s
   return CTRFE_OK;
 }
 
-template <int DT>
-void launch_fused_t(bool vect, dim3 grid, cudaStream_t st, const ctrfe::FusedParams& p) {
-  if (vect) ctrfe::fused_pool_kernel<DT, true><<<grid, ctrfe::kThreads, 0, st>>>(p);
-  else ctrfe::fused_pool_kernel<DT, false><<<grid, ctrfe::kThreads, 0, st>>>(p);
+template <int DT, int MODE>
+void launch_fused_tm(bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  using namespace ctrfe;
+  if (!vect) { fused_pool_kernel<DT, false, 5, MODE><<<grid, kThreads, 0, st>>>(p); return; }
+  switch (gs) {
+    case 0: fused_pool_kernel<DT, true, 0, MODE><<<grid, kThreads, 0, st>>>(p); break;
+    case 1: fused_pool_kernel<DT, true, 1, MODE><<<grid, kThreads, 0, st>>>(p); break;
+    case 2: fused_pool_kernel<DT, true, 2, MODE><<<grid, kThreads, 0, st>>>(p); break;
+    case 3: fused_pool_kernel<DT, true, 3, MODE><<<grid, kThreads, 0, st>>>(p); break;
+    case 4: fused_pool_kernel<DT, true, 4, MODE><<<grid, kThreads, 0, st>>>(p); break;
+    default: fused_pool_kernel<DT, true, 5, MODE><<<grid, kThreads, 0, st>>>(p); break;
+  }
 }
 
-int launch_fused(int dtype, bool vect, dim3 grid, cudaStream_t st, const ctrfe::FusedParams& p) {
-  switch (dtype) {
-    case CTRFE_F32: launch_fused_t<CTRFE_F32>(vect, grid, st, p); break;
-    case CTRFE_F16: launch_fused_t<CTRFE_F16>(vect, grid, st, p); break;
-    default: launch_fused_t<CTRFE_BF16>(vect, grid, st, p); break;
+template <int DT>
+void launch_fused_t(int mode, bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  if (mode == ctrfe::kModeSelect) launch_fused_tm<DT, ctrfe::kModeSelect>(vect, gs, grid, st, p);
+  else launch_fused_tm<DT, ctrfe::kModeAdd>(vect, gs, grid, st, p);
+}
+
+int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
+  for (size_t c = 0; c < plan.chunks.size(); ++c) {
+    const int m = plan.modes[c];
+    switch (plan.dtype) {
+      case CTRFE_F32: launch_fused_t<CTRFE_F32>(m, plan.vect, plan.g_shift, plan.grids[c], st, plan.chunks[c]); break;
+      case CTRFE_F16: launch_fused_t<CTRFE_F16>(m, plan.vect, plan.g_shift, plan.grids[c], st, plan.chunks[c]); break;
+      default: launch_fused_t<CTRFE_BF16>(m, plan.vect, plan.g_shift, plan.grids[c], st, plan.chunks[c]); break;
+    }
   }
   CU(cudaGetLastError());
   return CTRFE_OK;
 }
 
-// Builds a plan image in `dev` (capacity checked by the caller) via a pinned staging slot.
-int plan_build(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, cudaStream_t st, char* dev, size_t bytes,
-               ctrfe_plan* plan) {
+// Uploads the host LoDs (if any) into `dev` through a pinned staging slot.
+int plan_upload(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, cudaStream_t st, char* dev, size_t bytes,
+                ctrfe_plan* plan) {
+  if (bytes == 0) return CTRFE_OK;
   Staging* sg = nullptr;
   int rc = stage_acquire(ctx, bytes, &sg);
   if (rc) return rc;
-  rc = plan_stage(d, sg->host, dev, &plan->id_src);
+  rc = plan_stage_lods(d, sg->host, dev, plan);
   if (rc) return rc;
   CU(cudaMemcpyAsync(dev, sg->host, bytes, cudaMemcpyHostToDevice, st));
   CU(cudaEventRecord(sg->done, st));
   sg->pending = true;
-  plan->params.slots = reinterpret_cast<const ctrfe::SlotDev*>(dev);
-  plan->params.err = ctx->err_dev;
-  plan->dtype = d->dtype;
-  plan->ctx = ctx;
   plan->dev = dev;
   return CTRFE_OK;
 }
@@ -326,6 +393,7 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
     if (s.host) cudaFreeHost(s.host);
   }
   if (c->scratch) cudaFree(c->scratch);
+  if (c->zero_row) cudaFree(c->zero_row);
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
   delete c;
@@ -370,14 +438,19 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
   DeviceGuard g(ctx->device);
   auto* plan = new ctrfe_plan();
   size_t bytes = 0;
-  int rc = plan_geometry(desc, &plan->params, &plan->vect, &plan->grid, &bytes);
+  int rc = plan_geometry(ctx, desc, plan, &bytes);
   if (rc) { delete plan; return rc; }
-  char* dev = nullptr;
-  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
-  if (e != cudaSuccess) { delete plan; return fail(CTRFE_ERR_CUDA, "plan_create: cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); }
-  plan->owns_dev = true;
-  rc = plan_build(ctx, desc, static_cast<cudaStream_t>(stream), dev, bytes, plan);
-  if (rc) { cudaFree(dev); delete plan; return rc; }
+  if (bytes) {
+    char* dev = nullptr;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
+    if (e != cudaSuccess) {
+      delete plan;
+      return fail(CTRFE_ERR_CUDA, "plan_create: cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+    }
+    plan->owns_dev = true;
+    rc = plan_upload(ctx, desc, static_cast<cudaStream_t>(stream), dev, bytes, plan);
+    if (rc) { cudaFree(dev); delete plan; return rc; }
+  }
   *out = plan;
   return CTRFE_OK;
 }
@@ -385,13 +458,17 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
 int ctrfe_plan_launch(ctrfe_plan* plan, void* stream) {
   if (!plan) return fail(CTRFE_ERR_ARG, "plan_launch: null plan");
   DeviceGuard g(plan->ctx->device);
-  plan->ctx->last_ids = plan->id_src;
-  return launch_fused(plan->dtype, plan->vect, plan->grid, static_cast<cudaStream_t>(stream), plan->params);
+  if (plan->ctx->last_ids_owner != plan) {
+    plan->ctx->last_ids = plan->id_src;
+    plan->ctx->last_ids_owner = plan;
+  }
+  return launch_plan(*plan, static_cast<cudaStream_t>(stream));
 }
 
 int ctrfe_plan_destroy(ctrfe_plan* plan) {
   if (!plan) return CTRFE_OK;
   DeviceGuard g(plan->ctx->device);
+  if (plan->ctx->last_ids_owner == plan) plan->ctx->last_ids_owner = nullptr;
   if (plan->owns_dev && plan->dev) {
     cudaDeviceSynchronize();
     cudaFree(plan->dev);
@@ -400,7 +477,7 @@ int ctrfe_plan_destroy(ctrfe_plan* plan) {
   return CTRFE_OK;
 }
 
-int ctrfe_plan_num_kernels(const ctrfe_plan*) { return 1; }
+int ctrfe_plan_num_kernels(const ctrfe_plan* plan) { return plan ? static_cast<int>(plan->chunks.size()) : 0; }
 
 int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream) {
   if (!ctx) return fail(CTRFE_ERR_ARG, "fused_forward: null ctx");
@@ -408,14 +485,15 @@ int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stre
   auto st = static_cast<cudaStream_t>(stream);
   ctrfe_plan plan;
   size_t bytes = 0;
-  int rc = plan_geometry(desc, &plan.params, &plan.vect, &plan.grid, &bytes);
+  int rc = plan_geometry(ctx, desc, &plan, &bytes);
   if (rc) return rc;
   rc = scratch_reserve(ctx, bytes, st);
   if (rc) return rc;
-  rc = plan_build(ctx, desc, st, ctx->scratch, bytes, &plan);
+  rc = plan_upload(ctx, desc, st, ctx->scratch, bytes, &plan);
   if (rc) return rc;
   ctx->last_ids.swap(plan.id_src);
-  return launch_fused(plan.dtype, plan.vect, plan.grid, st, plan.params);
+  ctx->last_ids_owner = nullptr;
+  return launch_plan(plan, st);
 }
 
 int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes, const void* ids,
@@ -439,6 +517,7 @@ int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   ctx->last_ids.assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
+  ctx->last_ids_owner = nullptr;
   const char* t = static_cast<const char*>(table);
   char* o = static_cast<char*>(out);
   const int i32 = ids_dtype == CTRFE_I32;
@@ -491,9 +570,8 @@ int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t wi
   if (max_index && pooltype == CTRFE_POOL_MAX) {
     DeviceGuard g(ctx->device);
     auto st = static_cast<cudaStream_t>(stream);
-    // the LoD image sits right after the single descriptor in the context scratch
-    const auto* lod_dev = reinterpret_cast<const unsigned long long*>(
-        ctx->scratch + align_up(sizeof(ctrfe::SlotDev), 16));
+    // the single slot's LoD image sits at the start of the context scratch
+    const auto* lod_dev = reinterpret_cast<const unsigned long long*>(ctx->scratch);
     const long long total = n_seg * width;
     const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
     const char* xc = static_cast<const char*>(x);

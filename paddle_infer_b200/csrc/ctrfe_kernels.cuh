@@ -22,39 +22,57 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "../../include/ctrfe.h"
 
 namespace ctrfe {
 
-constexpr int kThreads = 256;  // threads per CTA of the pooling kernel
-constexpr int kUnroll = 4;     // row loads in flight per lane
+// Resident CTAs per SM the register allocator must leave room for (tuned on B200 with ncu;
+// overridable at build time for experiments).
+#ifndef CTRFE_MINB32
+#define CTRFE_MINB32 6
+#endif
+#ifndef CTRFE_MINB16
+#define CTRFE_MINB16 4
+#endif
 
-// Device-resident slot descriptor (built on the host by ctrfe_plan_create).
-struct SlotDev {
-  const char* table;               // [table_rows, dim] or dense X when ids == nullptr
-  const void* ids;                 // int64 / int32, or nullptr
+constexpr int kThreads = 256;          // threads per CTA of the pooling kernel
+constexpr int kUnroll = 4;             // row loads in flight per lane
+constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters
+constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequence: no load, no add
+constexpr uint32_t kZero = 0xfffffffeu;  // padding_idx / out-of-range id: contributes a zero row
+
+// Slot descriptor, passed BY VALUE in the kernel parameter block (constant bank): a CTA
+// reads its slot's pointers without a dependent global load.
+struct SlotK {
+  const char* table;               // [table_rows, dim] or dense X when id_kind == 2
+  const void* ids;                 // int64 / int32
   const unsigned long long* lod;   // device offsets [n_seg + 1]
   char* out;
-  long long table_rows;
-  long long out_ld;                // elements
-  long long n_seg;
-  int pooltype;
-  int ids_i32;
+  long long out_ld_bytes;          // bytes between consecutive output rows
+  unsigned int table_rows;         // < 2^32 - 2
+  unsigned int n_seg;
+  short pooltype;
+  short id_kind;                   // 0 int64, 1 int32, 2 dense (row index = position)
+  int slot_index;                  // position in the caller's slot array (bad-id report)
 };
 
-struct FusedParams {
-  const SlotDev* slots;
-  unsigned long long* err;  // [0]: min over (slot << 44 | position) of bad ids, ~0 = none
+struct KParams {
+  unsigned long long* err;   // [0]: min over (slot << 44 | position) of bad ids, ~0 = none
+  const char* zero_row;      // >= row_bytes of zeros: what a padding / bad id reads
   long long padding_idx;
   int dim;
   int row_bytes;
-  int g_shift;     // log2(lanes per group)
-  int tiles;       // column tiles per row (1 unless a row is wider than one warp covers)
+  int tiles;                 // column tiles per row (1 unless a row is wider than one group covers)
   int cvm_mode;
   int cvm_offset;
   int scale_mode;
   int init_mode;
+  int reserved;
   float pad_value;
+  int n_slots;
+  SlotK slots[kMaxSlotsPerLaunch];
 };
 
 __device__ __forceinline__ uint4 ldg128(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
@@ -103,154 +121,233 @@ struct Lane {
     if constexpr (ES == 4) return w[e];
     else return (w[e >> 1] >> ((e & 1) * 16)) & 0xffffu;
   }
+  // both halves of word r as floats (16-bit types)
+  __device__ __forceinline__ static float2 unpack2(uint32_t w) {
+    if constexpr (DT == CTRFE_F16) {
+      return __half22float2(*reinterpret_cast<const __half2*>(&w));
+    } else {
+      return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+    }
+  }
 };
 
+enum { kModeAdd = 0, kModeSelect = 1 };
+
+// log(x + 1) as the reference CPU kernel evaluates it: the add in fp32, the log in fp64.
+__device__ __forceinline__ double cvm_log1(float x) { return log(static_cast<double>(x + 1.0f)); }
+
+// Pin a value in a register: stops ptxas from re-deriving it from the (dynamically indexed)
+// parameter bank inside the row loop.
+#define CTRFE_KEEP64(x) asm volatile("" : "+l"(x))
+#define CTRFE_KEEP32(x) asm volatile("" : "+r"(x))
+
 // ---------------------------------------------------------------------------------------
-// fused gather + segmented pool + CVM.  grid = (ceil(max_items*G / kThreads), n_slots).
+// fused gather + segmented pool + CVM.
+// grid = (ceil(max_items * G / kThreads), slots in this launch); G = 1 << GS lanes per item.
+// MODE: kModeAdd for SUM / AVERAGE / SQRT slots, kModeSelect for MAX / LAST / FIRST slots
+// (the host puts slots of different modes into different launches).
 // ---------------------------------------------------------------------------------------
-template <int DT, bool VECT>
-__global__ void __launch_bounds__(kThreads) fused_pool_kernel(const FusedParams p) {
+template <int DT, bool VECT, int GS, int MODE>
+__global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
+fused_pool_kernel(const __grid_constant__ KParams kp) {
   using L = Lane<DT, VECT>;
   constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
+  constexpr int G = 1 << GS;
+  constexpr int U = kUnroll;
+  constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
+  constexpr int R = G * NI;               // rows consumed per step of the sequence loop
+  constexpr bool selecting = MODE == kModeSelect;
 
-  const SlotDev* __restrict__ sd = p.slots + blockIdx.y;
-  const long long n_seg = sd->n_seg;
-  const int g_shift = p.g_shift;
-  const int G = 1 << g_shift;
-  const int tiles = p.tiles;
-  const long long first_item = (static_cast<long long>(blockIdx.x) * kThreads) >> g_shift;
-  if (first_item >= n_seg * tiles) return;  // whole CTA past this slot's work
+  const SlotK* const slp = &kp.slots[blockIdx.y];
+  const unsigned n_seg = slp->n_seg;
+  const int tiles = kp.tiles;
+  const unsigned long long first_item = (static_cast<unsigned long long>(blockIdx.x) * kThreads) >> GS;
+  if (first_item >= static_cast<unsigned long long>(n_seg) * tiles) return;  // CTA past this slot's work
 
-  const char* __restrict__ table = sd->table;
-  const void* __restrict__ ids = sd->ids;
-  const unsigned long long* __restrict__ lod = sd->lod;
-  const long long table_rows = sd->table_rows;
-  const int pooltype = sd->pooltype;
-  const bool ids_i32 = sd->ids_i32 != 0;
-  const long long row_bytes = p.row_bytes;
-  const long long padding_idx = p.padding_idx;
-
+  const int pooltype = slp->pooltype;
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1);
-  const long long item = (static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x) >> g_shift;
-  long long seg = item;
+  const unsigned long long item = (static_cast<unsigned long long>(blockIdx.x) * kThreads + threadIdx.x) >> GS;
+  unsigned seg = static_cast<unsigned>(item);
   int tile = 0;
-  if (tiles > 1) { seg = item / tiles; tile = static_cast<int>(item - seg * tiles); }
+  if (tiles > 1) { seg = static_cast<unsigned>(item / tiles); tile = static_cast<int>(item - static_cast<unsigned long long>(seg) * tiles); }
   const bool seg_ok = seg < n_seg;
   const int col0 = (tile * G + gl) * VEC;
-  const bool col_ok = col0 < p.dim;
+  const bool col_ok = col0 < kp.dim;
 
   long long start = 0, end = 0;
   if (seg_ok) {
+    const unsigned long long* __restrict__ lod = slp->lod;
     start = static_cast<long long>(__ldg(lod + seg));
     end = static_cast<long long>(__ldg(lod + seg + 1));
   }
   const int seg_len = static_cast<int>(end - start);  // rows of the sequence (for the scale)
-  // LAST / FIRST read exactly one row: narrow the range and reuse the copy-first path.
-  const bool selecting = pooltype == CTRFE_POOL_MAX || pooltype == CTRFE_POOL_LAST ||
-                         pooltype == CTRFE_POOL_FIRST;
-  if (seg_len > 0) {
+  if (selecting && seg_len > 0) {  // LAST / FIRST read exactly one row
     if (pooltype == CTRFE_POOL_FIRST) end = start + 1;
     else if (pooltype == CTRFE_POOL_LAST) start = end - 1;
   }
   const int len = static_cast<int>(end - start);
-  const bool copy_first = selecting || p.init_mode == CTRFE_INIT_FIRST_ROW;
   const int maxlen = __reduce_max_sync(kFull, len);
 
+  // this CTA's slot, copied out of the parameter bank once
+  unsigned long long lane_base = reinterpret_cast<unsigned long long>(slp->table) + static_cast<unsigned>(col0 * ES);
+  unsigned table_rows = slp->table_rows;
+  unsigned row_bytes = kp.row_bytes;
+  int id_kind = slp->id_kind;
+  // address of this lane's first id (dense rows: the position itself)
+  unsigned long long idp = id_kind == 2 ? static_cast<unsigned long long>(start + gl)
+                                        : reinterpret_cast<unsigned long long>(slp->ids) +
+                                              static_cast<unsigned long long>(start + gl) * (id_kind == 1 ? 4u : 8u);
+  const unsigned id_step = id_kind == 2 ? 1u : (id_kind == 1 ? 4u : 8u);
+  const bool pad_on = kp.padding_idx != -1;
+  const uint32_t pad_lo = static_cast<uint32_t>(kp.padding_idx);
+  const uint32_t pad_hi = static_cast<uint32_t>(static_cast<unsigned long long>(kp.padding_idx) >> 32);
+  CTRFE_KEEP64(lane_base);
+  CTRFE_KEEP32(table_rows);
+  CTRFE_KEEP32(row_bytes);
+  CTRFE_KEEP32(id_kind);
+
+  // Row index of the id at address `a` (sequence position `off`): kSkip past the end; kZero
+  // for a row that reads as zeros -- padding_idx (tested before the range check, as
+  // embedding_kernel.cc:56-57 does) or an out-of-range id, which is also flagged for the
+  // host to raise so that the kernel itself never faults.
+  auto fetch_rid = [&](unsigned long long a, int off) -> uint32_t {
+    if (off >= len) return kSkip;
+    long long id;
+    if (id_kind == 0) id = __ldg(reinterpret_cast<const long long*>(a));
+    else if (id_kind == 1) id = static_cast<long long>(__ldg(reinterpret_cast<const int*>(a)));
+    else id = static_cast<long long>(a);
+    const uint32_t lo = static_cast<uint32_t>(id), hi = static_cast<uint32_t>(static_cast<unsigned long long>(id) >> 32);
+    const bool in_range = hi == 0u && lo < table_rows;  // table_rows < 2^32 - 2
+    const bool is_pad = pad_on && lo == pad_lo && hi == pad_hi;
+    if (!in_range && !is_pad && tile == 0) {
+      atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) |
+                            static_cast<unsigned long long>(start + off));
+    }
+    return (in_range && !is_pad) ? lo : kZero;
+  };
+
   float acc[VEC];
-  uint32_t sel[RW];  // raw bits of the selected elements (selection pools on 16-bit types)
+  uint32_t sel[RW];  // selection pools on 16-bit types: raw bits of the selected elements
   {
-    const float init = p.init_mode == CTRFE_INIT_PAD ? p.pad_value : 0.0f;
+    const float init = kp.init_mode == CTRFE_INIT_PAD ? kp.pad_value : 0.0f;
 #pragma unroll
     for (int e = 0; e < VEC; ++e) acc[e] = init;
 #pragma unroll
     for (int r = 0; r < RW; ++r) sel[r] = 0u;
   }
+  // SELECT copies the first row; ADD does so only in EmbSeqPool order (CTRFE_INIT_FIRST_ROW)
+  const bool copy_first = selecting || kp.init_mode == CTRFE_INIT_FIRST_ROW;
 
-  auto load_id = [&](long long pos) -> long long {
-    if (ids == nullptr) return pos;  // dense rows: sequence_pool over a materialised X
-    return ids_i32 ? static_cast<long long>(__ldg(reinterpret_cast<const int*>(ids) + pos))
-                   : __ldg(reinterpret_cast<const long long*>(ids) + pos);
-  };
-  auto flag_if_bad = [&](long long id, long long pos) {
-    if (id != padding_idx || padding_idx == -1) {
-      if (static_cast<unsigned long long>(id) >= static_cast<unsigned long long>(table_rows)) {
-        atomicMin(p.err, (static_cast<unsigned long long>(blockIdx.y) << 44) |
-                             static_cast<unsigned long long>(pos));
-      }
-    }
-  };
-
-  long long cur_id = 0;
-  if (gl < len) {
-    cur_id = load_id(start + gl);
-    if (tile == 0) flag_if_bad(cur_id, start + gl);
-  }
-
-  for (int base = 0; base < maxlen; base += G) {
-    // prefetch the next batch of ids before touching this batch's rows
-    long long nxt_id = 0;
-    if (base + G + gl < len) {
-      nxt_id = load_id(start + base + G + gl);
-      if (tile == 0) flag_if_bad(nxt_id, start + base + G + gl);
-    }
-    for (int j0 = 0; j0 < G && base + j0 < maxlen; j0 += kUnroll) {
-      uint32_t raw[kUnroll][RW];
-      bool valid[kUnroll];
+  uint32_t cur[NI];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int j = j0 + u;
-        const long long id = __shfl_sync(kFull, cur_id, j & (G - 1), G);
-        valid[u] = (j < G) && (base + j < len) && col_ok;
-        const bool fetch = valid[u] && !(padding_idx != -1 && id == padding_idx) &&
-                           static_cast<unsigned long long>(id) < static_cast<unsigned long long>(table_rows);
+  for (int i = 0; i < NI; ++i) cur[i] = fetch_rid(idp + static_cast<unsigned long long>(i * G) * id_step, i * G + gl);
+  for (int base = 0; base < maxlen; base += R) {
+    idp += static_cast<unsigned long long>(R) * id_step;
+    uint32_t nxt[NI];  // next step's ids are requested before this step's rows
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+      nxt[i] = fetch_rid(idp + static_cast<unsigned long long>(i * G) * id_step, base + R + i * G + gl);
+#pragma unroll
+    for (int c = 0; c < R / U; ++c) {
+      if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
+      uint32_t raw[U][RW];
+      bool ok[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = c * U + u;
+        const uint32_t rid = __shfl_sync(kFull, cur[j / G], j % G, G);
+        ok[u] = (rid != kSkip) && col_ok;
+        // a kZero row (padding_idx / bad id) is added as zeros without touching memory
 #pragma unroll
         for (int r = 0; r < RW; ++r) raw[u][r] = 0u;
-        if (fetch) L::load(table + id * row_bytes + static_cast<long long>(col0) * ES, raw[u]);
+        if (rid < kZero && col_ok)
+          L::load(reinterpret_cast<const char*>(lane_base + static_cast<unsigned long long>(rid) * row_bytes), raw[u]);
       }
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        if (!valid[u]) continue;
-        const bool first = copy_first && (base + j0 + u == 0);
-        if (pooltype == CTRFE_POOL_MAX || pooltype == CTRFE_POOL_LAST || pooltype == CTRFE_POOL_FIRST) {
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        const bool first = copy_first && (c == 0 && u == 0) && (base == 0);
+        if constexpr (MODE == kModeSelect) {
           // out = row0; then strictly-greater replaces (math/sequence_pooling.cc:166-174)
-          uint32_t take_mask[RW];
+          if constexpr (DT == CTRFE_F16) {
+            // packed half compare: same order as the fp32 compare (the conversion is exact and
+            // monotone, half subnormals are normal floats); NaN never replaces; row 0 sticks
 #pragma unroll
-          for (int r = 0; r < RW; ++r) take_mask[r] = 0u;
-#pragma unroll
-          for (int e = 0; e < VEC; ++e) {
-            const float x = elem_to_float<DT>(L::bits(raw[u], e));
-            if (first || x > acc[e]) {
-              acc[e] = x;
-              if constexpr (ES == 4) take_mask[e] = 0xffffffffu;
-              else take_mask[e >> 1] |= 0xffffu << ((e & 1) * 16);
+            for (int r = 0; r < RW; ++r) {
+              const __half2 x2 = *reinterpret_cast<const __half2*>(&raw[u][r]);
+              const __half2 a2 = *reinterpret_cast<const __half2*>(&sel[r]);
+              const unsigned m = first ? 0xffffffffu : __hgt2_mask(x2, a2);
+              sel[r] = (sel[r] & ~m) | (raw[u][r] & m);
             }
+          } else if constexpr (ES == 4) {
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+              const float x = __uint_as_float(raw[u][e]);
+              if (first || x > acc[e]) acc[e] = x;
+            }
+          } else {
+            uint32_t take[RW];
+#pragma unroll
+            for (int r = 0; r < RW; ++r) take[r] = 0u;
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+              const float x = elem_to_float<DT>(L::bits(raw[u], e));
+              if (first || x > acc[e]) {
+                acc[e] = x;
+                take[e >> 1] |= 0xffffu << ((e & 1) * 16);
+              }
+            }
+#pragma unroll
+            for (int r = 0; r < RW; ++r) sel[r] = (sel[r] & ~take[r]) | (raw[u][r] & take[r]);
           }
-#pragma unroll
-          for (int r = 0; r < RW; ++r) sel[r] = (sel[r] & ~take_mask[r]) | (raw[u][r] & take_mask[r]);
         } else {
+          if constexpr (ES == 4) {
 #pragma unroll
-          for (int e = 0; e < VEC; ++e) {
-            const float x = elem_to_float<DT>(L::bits(raw[u], e));
-            acc[e] = first ? x : acc[e] + x;
+            for (int e = 0; e < VEC; ++e) {
+              const float x = __uint_as_float(raw[u][e]);
+              acc[e] = first ? x : acc[e] + x;
+            }
+          } else if constexpr (VECT) {
+#pragma unroll
+            for (int r = 0; r < RW; ++r) {
+              const float2 x = L::unpack2(raw[u][r]);
+              acc[2 * r] = first ? x.x : acc[2 * r] + x.x;
+              acc[2 * r + 1] = first ? x.y : acc[2 * r + 1] + x.y;
+            }
+          } else {
+            const float x = elem_to_float<DT>(raw[u][0]);
+            acc[0] = first ? x : acc[0] + x;
           }
         }
       }
     }
-    cur_id = nxt_id;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
   }
 
   // ---- epilogue: pad / scale / CVM / store -------------------------------------------
   bool use_sel = selecting && ES == 2;  // 16-bit selection pools store the selected bits
-  if (seg_len == 0 && p.init_mode != CTRFE_INIT_PAD) {
+  if (selecting && DT == CTRFE_F16 && kp.cvm_mode == CTRFE_CVM_USE && tile == 0 && gl == 0) {
+    // the half-compare path kept no float copy: the CVM columns need one
+    if constexpr (VECT && DT == CTRFE_F16) {
+      const float2 x = L::unpack2(sel[0]);
+      acc[0] = x.x;
+      acc[1] = x.y;
+    }
+  }
+  if constexpr (!VECT && DT == CTRFE_F16) {
+    if (selecting) acc[0] = elem_to_float<DT>(sel[0]);
+  }
+  if (seg_len == 0 && kp.init_mode != CTRFE_INIT_PAD) {
     // empty sequence -> pad_value for every pooltype (sequence_pooling.cc:93-98,160-165,395-398)
 #pragma unroll
-    for (int e = 0; e < VEC; ++e) acc[e] = p.pad_value;
+    for (int e = 0; e < VEC; ++e) acc[e] = kp.pad_value;
     use_sel = false;
   } else if (seg_len > 0 && (pooltype == CTRFE_POOL_AVERAGE || pooltype == CTRFE_POOL_SQRT)) {
     const float h = static_cast<float>(seg_len);
-    if (p.scale_mode == CTRFE_SCALE_DIVIDE) {
+    if (kp.scale_mode == CTRFE_SCALE_DIVIDE) {
       const float d = pooltype == CTRFE_POOL_AVERAGE ? h : sqrtf(h);
 #pragma unroll
       for (int e = 0; e < VEC; ++e) acc[e] = acc[e] / d;
@@ -262,33 +359,40 @@ __global__ void __launch_bounds__(kThreads) fused_pool_kernel(const FusedParams 
     }
   }
 
-  bool cvm_cols[2] = {false, false};  // which of this lane's elements were CVM-transformed
-  if (p.cvm_mode == CTRFE_CVM_USE) {
-    // y0 = log(x0 + 1); y1 = log(x1 + 1) - y0   (cvm_op.h:34-37).  The float add happens in
-    // fp32, the log in fp64 narrowed to fp32, and the subtraction uses the rounded y0.
-    if constexpr (VEC >= 2) {
-      if (tile == 0 && gl == 0) {
-        const float y0 = static_cast<float>(log(static_cast<double>(acc[0] + 1.0f)));
-        const float y1 = static_cast<float>(log(static_cast<double>(acc[1] + 1.0f)) - static_cast<double>(y0));
+  bool cvm_cols[2] = {false, false};  // which of this lane's leading elements were CVM-transformed
+  if (kp.cvm_mode == CTRFE_CVM_USE) {
+    // y0 = log(x0 + 1); y1 = log(x1 + 1) - y0   (cvm_op.h:34-37): the add in fp32, the log in
+    // fp64 narrowed to fp32, the subtraction against the ROUNDED y0.  The two logs run on two
+    // lanes at once (lane 1 borrows x1), halving the fp64 instruction stream.
+    const bool head = tile == 0;
+    if constexpr (VEC >= 2 && G >= 2) {
+      const float x1 = __shfl_sync(kFull, acc[1], 0, G);
+      double lg = 0.0;
+      if (head && gl < 2) lg = cvm_log1(gl == 0 ? acc[0] : x1);
+      const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);
+      float y1 = 0.0f;
+      if (head && gl == 1) y1 = static_cast<float>(lg - static_cast<double>(y0));
+      y1 = __shfl_sync(kFull, y1, 1, G);
+      if (head && gl == 0) { acc[0] = y0; acc[1] = y1; cvm_cols[0] = cvm_cols[1] = true; }
+    } else if constexpr (VEC >= 2) {
+      if (head) {
+        const float y0 = static_cast<float>(cvm_log1(acc[0]));
+        acc[1] = static_cast<float>(cvm_log1(acc[1]) - static_cast<double>(y0));
         acc[0] = y0;
-        acc[1] = y1;
         cvm_cols[0] = cvm_cols[1] = true;
       }
     } else {
-      float y0 = 0.0f;
-      if (tile == 0 && gl == 0) y0 = static_cast<float>(log(static_cast<double>(acc[0] + 1.0f)));
-      const float y0b = __shfl_sync(kFull, y0, 0, G);  // column 1 lives on the next lane
-      if (tile == 0 && gl == 0) { acc[0] = y0; cvm_cols[0] = true; }
-      if (tile == 0 && gl == 1) {
-        acc[0] = static_cast<float>(log(static_cast<double>(acc[0] + 1.0f)) - static_cast<double>(y0b));
-        cvm_cols[0] = true;
-      }
+      double lg = 0.0;
+      if (head && gl < 2) lg = cvm_log1(acc[0]);
+      const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);  // column 1 lives on lane 1
+      if (head && gl == 0) { acc[0] = y0; cvm_cols[0] = true; }
+      if (head && gl == 1) { acc[0] = static_cast<float>(lg - static_cast<double>(y0)); cvm_cols[0] = true; }
     }
   }
 
   if (!(seg_ok && col_ok)) return;
-  const int skip = p.cvm_mode == CTRFE_CVM_STRIP ? p.cvm_offset : 0;
-  char* orow = sd->out + seg * sd->out_ld * ES;
+  const int skip = kp.cvm_mode == CTRFE_CVM_STRIP ? kp.cvm_offset : 0;
+  char* orow = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes;
 
   uint32_t packed[RW];
 #pragma unroll

@@ -1,0 +1,289 @@
+// ctrfe_paddle_ops.cc -- Paddle custom-operator shim over the ctrfe C ABI.
+//
+// Built by a Paddle maintainer against an installed Paddle (paddle/extension.h) and linked
+// with libctrfe.so; loaded with paddle.utils.cpp_extension.load / LoadCustomOperatorLib.
+// It cannot be loaded on the authoring box (Paddle is not installed there); it is
+// syntax-checked against the reference headers by paddle_shim/check_syntax.sh.
+//
+// Why the op names differ from the built-ins: the custom-op loader skips a name that is
+// already registered (framework/custom_operator.cc:722-725), so `lookup_table_v2`,
+// `sequence_pool`, `cvm` cannot be re-registered through the public API.  This file
+// registers
+//     ctr_fused_emb_seqpool_cvm   W, Ids@VECTOR -> Out@VECTOR      (the fused front end)
+//     b200_lookup_table_v2        W, Ids -> Out                    (1:1 clone)
+//     b200_sequence_pool          X -> Out, MaxIndex               (1:1 clone)
+//     b200_cvm                    X, CVM -> Y                      (1:1 clone)
+// with the reference ops' input/output/attribute names, and paddle_infer_b200/rewrite.py
+// retargets a loaded program's op types (the saved model on disk is untouched).
+//
+// LoD: paddle::Tensor has no LoD accessor; the DenseTensor behind it carries it
+// (custom_operator.cc:159,173 copy meta incl. lod; phi/core/tensor_meta.h:72).
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "paddle/extension.h"
+#include "paddle/phi/core/dense_tensor.h"
+
+#include "ctrfe.h"
+
+namespace {
+
+const phi::LoD& LodOf(const paddle::Tensor& t) {
+  auto* dense = static_cast<phi::DenseTensor*>(t.impl().get());
+  PD_CHECK(dense != nullptr, "ctrfe: input is not a DenseTensor");
+  return dense->lod();
+}
+
+// Untyped device pointers: paddle::Tensor::data<T>() is typed; the DenseTensor behind it
+// hands out void*.
+const void* Raw(const paddle::Tensor& t) {
+  return static_cast<const phi::DenseTensor*>(t.impl().get())->data();
+}
+void* RawMut(paddle::Tensor& t) {  // NOLINT
+  return static_cast<phi::DenseTensor*>(t.impl().get())->data();
+}
+
+int DtypeCode(paddle::DataType dt) {
+  switch (dt) {
+    case paddle::DataType::FLOAT32: return CTRFE_F32;
+    case paddle::DataType::FLOAT16: return CTRFE_F16;
+    case paddle::DataType::BFLOAT16: return CTRFE_BF16;
+    default: PD_THROW("ctrfe: only float32 / float16 / bfloat16 tables have sm_100a kernels");
+  }
+  return -1;
+}
+
+int IdCode(paddle::DataType dt) {
+  if (dt == paddle::DataType::INT64) return CTRFE_I64;
+  if (dt == paddle::DataType::INT32) return CTRFE_I32;
+  PD_THROW("emebdding input only support int32 and int64");
+  return -1;
+}
+
+int PoolCode(const std::string& p) {
+  if (p == "AVERAGE") return CTRFE_POOL_AVERAGE;
+  if (p == "SUM") return CTRFE_POOL_SUM;
+  if (p == "SQRT") return CTRFE_POOL_SQRT;
+  if (p == "LAST") return CTRFE_POOL_LAST;
+  if (p == "FIRST") return CTRFE_POOL_FIRST;
+  if (p == "MAX") return CTRFE_POOL_MAX;
+  PD_THROW("unsupported pooling pooltype: ", p);
+  return -1;
+}
+
+// One context per device for the process (the C core is re-entrant across contexts; a
+// predictor and its clones run one thread each, so guard the lazy creation only).
+ctrfe_ctx* CtxFor(const paddle::Tensor& t) {
+  static ctrfe_ctx* ctxs[64] = {nullptr};
+  const int dev = t.place().GetDeviceId();
+  PD_CHECK(dev >= 0 && dev < 64, "ctrfe: bad device id");
+  if (ctxs[dev] == nullptr) {
+    PD_CHECK(ctrfe_ctx_create(dev, &ctxs[dev]) == CTRFE_OK, ctrfe_last_error());
+  }
+  return ctxs[dev];
+}
+
+void Check(int rc) { PD_CHECK(rc == CTRFE_OK, ctrfe_last_error()); }
+
+void NeedGpu(const paddle::Tensor& t, const char* what) {
+  PD_CHECK(t.is_gpu(), what, " must be on a CUDAPlace: the ctrfe ops have no CPU kernel");
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// ctr_fused_emb_seqpool_cvm
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> CtrFusedForward(const paddle::Tensor& w, const std::vector<paddle::Tensor>& ids,
+                                            const std::string& pooltype, float pad_value, int64_t padding_idx,
+                                            bool use_cvm, int cvm_offset) {
+  NeedGpu(w, "W");
+  const auto wshape = w.shape();
+  PD_CHECK(wshape.size() == 2, "ShapeError: The dimensions of the 'lookup table' must be 2.");
+  const int64_t dim = wshape[1];
+  const int64_t d_out = use_cvm ? dim : dim - cvm_offset;
+  const int pool = PoolCode(pooltype);
+  std::vector<ctrfe_slot> slots(ids.size());
+  std::vector<paddle::Tensor> outs;
+  outs.reserve(ids.size());
+  for (size_t s = 0; s < ids.size(); ++s) {
+    NeedGpu(ids[s], "Ids");
+    const auto& lod = LodOf(ids[s]);
+    PD_CHECK(!lod.empty() && lod.size() <= 2, "Input(Ids) must carry 1 or 2 LoD levels");
+    const auto& last = lod.back();
+    const int64_t n_seg = static_cast<int64_t>(last.size()) - 1;
+    outs.emplace_back(paddle::empty({n_seg, d_out}, w.dtype(), w.place()));
+    ctrfe_slot& sl = slots[s];
+    sl.table = Raw(w);
+    sl.table_rows = wshape[0];
+    sl.ids = Raw(ids[s]);
+    sl.lod = reinterpret_cast<const uint64_t*>(last.data());  // size_t offsets, host
+    sl.n_seg = n_seg;
+    sl.out = RawMut(outs.back());
+    sl.out_ld = d_out;
+    sl.pooltype = pool;
+    sl.ids_dtype = IdCode(ids[s].dtype());
+  }
+  ctrfe_fused_desc d{};
+  d.n_slots = static_cast<int32_t>(slots.size());
+  d.dtype = DtypeCode(w.dtype());
+  d.slots = slots.data();
+  d.dim = dim;
+  d.padding_idx = padding_idx;
+  d.pad_value = pad_value;
+  d.cvm_mode = use_cvm ? CTRFE_CVM_USE : CTRFE_CVM_STRIP;
+  d.cvm_offset = cvm_offset;
+  d.scale_mode = CTRFE_SCALE_DIVIDE;
+  d.init_mode = CTRFE_INIT_ZERO;
+  d.lod_location = CTRFE_LOD_HOST;
+  Check(ctrfe_fused_forward(CtxFor(w), &d, w.stream()));
+  return outs;
+}
+
+std::vector<std::vector<int64_t>> CtrFusedInferShape(const std::vector<int64_t>& w_shape,
+                                                     const std::vector<std::vector<int64_t>>& ids_shapes,
+                                                     const std::string& pooltype, float pad_value,
+                                                     int64_t padding_idx, bool use_cvm, int cvm_offset) {
+  // batch is only known from the LoD at run time, as in fused_seqpool_cvm_op.cc:82-91
+  std::vector<std::vector<int64_t>> out;
+  for (size_t i = 0; i < ids_shapes.size(); ++i) out.push_back({-1, use_cvm ? w_shape[1] : w_shape[1] - cvm_offset});
+  return out;
+}
+
+std::vector<paddle::DataType> CtrFusedInferDtype(const paddle::DataType& w_dtype,
+                                                 const std::vector<paddle::DataType>& ids_dtypes) {
+  return std::vector<paddle::DataType>(ids_dtypes.size(), w_dtype);
+}
+
+PD_BUILD_OP(ctr_fused_emb_seqpool_cvm)
+    .Inputs({"W", paddle::Vec("Ids")})
+    .Outputs({paddle::Vec("Out")})
+    .Attrs({"pooltype: std::string", "pad_value: float", "padding_idx: int64_t", "use_cvm: bool",
+            "cvm_offset: int"})
+    .SetKernelFn(PD_KERNEL(CtrFusedForward))
+    .SetInferShapeFn(PD_INFER_SHAPE(CtrFusedInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(CtrFusedInferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_lookup_table_v2  (LookupTableV2OpMaker, lookup_table_v2_op.cc:69-104)
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200LookupTableV2(const paddle::Tensor& w, const paddle::Tensor& ids,
+                                              int64_t padding_idx) {
+  NeedGpu(w, "W");
+  NeedGpu(ids, "Ids");
+  const auto wshape = w.shape();
+  PD_CHECK(wshape.size() == 2, "ShapeError: The dimensions of the 'lookup table' must be 2.");
+  auto oshape = ids.shape();
+  oshape.push_back(wshape[1]);
+  auto out = paddle::empty(oshape, w.dtype(), w.place());
+  const int64_t es = static_cast<int64_t>(paddle::experimental::SizeOf(w.dtype()));
+  ctrfe_ctx* ctx = CtxFor(w);
+  Check(ctrfe_embedding(ctx, Raw(w), wshape[0], wshape[1] * es, Raw(ids), IdCode(ids.dtype()), ids.numel(),
+                        padding_idx, RawMut(out), w.stream()));
+  // the reference CPU kernel throws on an out-of-range id; keep that behaviour
+  int64_t slot = -1, pos = -1, bad = -1;
+  Check(ctrfe_check_ids(ctx, w.stream(), &slot, &pos, &bad));
+  return {out};
+}
+
+std::vector<std::vector<int64_t>> B200LookupTableV2InferShape(const std::vector<int64_t>& w_shape,
+                                                              const std::vector<int64_t>& ids_shape,
+                                                              int64_t padding_idx) {
+  auto o = ids_shape;
+  o.push_back(w_shape[1]);
+  return {o};
+}
+
+std::vector<paddle::DataType> B200LookupTableV2InferDtype(const paddle::DataType& w_dtype,
+                                                          const paddle::DataType& ids_dtype) {
+  return {w_dtype};
+}
+
+PD_BUILD_OP(b200_lookup_table_v2)
+    .Inputs({"W", "Ids"})
+    .Outputs({"Out"})
+    .Attrs({"padding_idx: int64_t"})
+    .SetKernelFn(PD_KERNEL(B200LookupTableV2))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200LookupTableV2InferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200LookupTableV2InferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_sequence_pool  (SequencePoolOpMaker, sequence_pool_op.cc:45-112).  The custom-op
+// maker has no "intermediate" marker, so MaxIndex is a plain second output: int32 indices
+// for MAX when !is_test, else a 0-size tensor.
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200SequencePool(const paddle::Tensor& x, const std::string& pooltype, float pad_value,
+                                             bool is_test) {
+  NeedGpu(x, "X");
+  const auto& lod = LodOf(x);
+  PD_CHECK(!lod.empty(), "Input(X) Tensor of SequencePoolOp does not contain LoD information.");
+  PD_CHECK(lod.size() <= 2, "The lod level of input shall be no more than 2.");
+  if (lod.size() == 2) PD_CHECK(lod[0].back() == lod[1].size() - 1, "The input lod information is illegal.");
+  const auto& last = lod.back();
+  const int64_t n_seg = static_cast<int64_t>(last.size()) - 1;
+  auto shape = x.shape();
+  PD_CHECK(shape[0] >= n_seg, "The first dimension of Input(X) must be large than batch size.");
+  int64_t width = 1;
+  for (size_t i = 1; i < shape.size(); ++i) width *= shape[i];
+  shape[0] = n_seg;
+  auto out = paddle::empty(shape, x.dtype(), x.place());
+  const bool want_index = pooltype == "MAX" && !is_test;
+  auto index = want_index ? paddle::empty(shape, paddle::DataType::INT32, x.place())
+                          : paddle::empty({0}, paddle::DataType::INT32, x.place());
+  Check(ctrfe_sequence_pool(CtxFor(x), Raw(x), DtypeCode(x.dtype()), width,
+                            reinterpret_cast<const uint64_t*>(last.data()), n_seg, PoolCode(pooltype), pad_value,
+                            RawMut(out), want_index ? index.data<int32_t>() : nullptr, x.stream()));
+  return {out, index};
+}
+
+std::vector<std::vector<int64_t>> B200SequencePoolInferShape(const std::vector<int64_t>& x_shape,
+                                                             const std::string& pooltype, float pad_value,
+                                                             bool is_test) {
+  auto o = x_shape;
+  o[0] = -1;
+  return {o, o};
+}
+
+std::vector<paddle::DataType> B200SequencePoolInferDtype(const paddle::DataType& x_dtype) {
+  return {x_dtype, paddle::DataType::INT32};
+}
+
+PD_BUILD_OP(b200_sequence_pool)
+    .Inputs({"X"})
+    .Outputs({"Out", "MaxIndex"})
+    .Attrs({"pooltype: std::string", "pad_value: float", "is_test: bool"})
+    .SetKernelFn(PD_KERNEL(B200SequencePool))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200SequencePoolInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200SequencePoolInferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_cvm  (CVMOpMaker, cvm_op.cc:127-150).  The CVM input is declared because the
+// reference op has it; forward never reads it (cvm_op.h:60-99).
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200Cvm(const paddle::Tensor& x, const paddle::Tensor& cvm, bool use_cvm) {
+  NeedGpu(x, "X");
+  const auto shape = x.shape();
+  PD_CHECK(shape.size() == 2, "Input(X)'s rank should be 2, but got ", shape.size());
+  auto y = paddle::empty({shape[0], use_cvm ? shape[1] : shape[1] - 2}, x.dtype(), x.place());
+  Check(ctrfe_cvm(CtxFor(x), Raw(x), DtypeCode(x.dtype()), shape[0], shape[1], use_cvm ? 1 : 0, RawMut(y),
+                  x.stream()));
+  return {y};
+}
+
+std::vector<std::vector<int64_t>> B200CvmInferShape(const std::vector<int64_t>& x_shape,
+                                                    const std::vector<int64_t>& cvm_shape, bool use_cvm) {
+  return {{x_shape[0], use_cvm ? x_shape[1] : x_shape[1] - 2}};
+}
+
+std::vector<paddle::DataType> B200CvmInferDtype(const paddle::DataType& x_dtype, const paddle::DataType& cvm_dtype) {
+  return {x_dtype};
+}
+
+PD_BUILD_OP(b200_cvm)
+    .Inputs({"X", "CVM"})
+    .Outputs({"Y"})
+    .Attrs({"use_cvm: bool"})
+    .SetKernelFn(PD_KERNEL(B200Cvm))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200CvmInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200CvmInferDtype));
