@@ -5,6 +5,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <utility>
 #include <vector>
@@ -56,6 +57,9 @@ struct ctrfe_ctx {
   // LoD image of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
   char* scratch = nullptr;
   size_t scratch_cap = 0;
+  // zeros that a padding_idx / out-of-range id reads instead of a table row
+  char* zero_row = nullptr;
+  size_t zero_cap = 0;
   std::vector<IdSource> last_ids;  // slots of the most recent fused launch
   const void* last_ids_owner = nullptr;  // identity tag only (never dereferenced): skip re-copying
   int sm_count = 148;
@@ -68,11 +72,11 @@ struct ctrfe_plan {
   std::vector<ctrfe::KParams> chunks;  // <= kMaxSlotsPerLaunch slots each: one launch per chunk
   std::vector<dim3> grids;
   std::vector<int> modes;                      // kernel MODE of each chunk
-  std::vector<const void*> kernels;            // kernel instantiation of each chunk
   std::vector<std::pair<int, int>> where;      // caller slot -> (chunk, index in chunk)
   int dtype = 0;
   bool vect = false;
   int g_shift = 0;
+  int chunk_bytes = 16;  // bytes of a row one lane holds (32: 256-bit loads, fp32 only)
   std::vector<IdSource> id_src;
 };
 
@@ -134,28 +138,18 @@ int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
   return CTRFE_OK;
 }
 
-// The kernel instantiation for (dtype, 128-bit lanes?, log2 lanes per item, pool mode).
-template <int DT, int MODE>
-const void* fused_kernel_tm(bool vect, int gs) {
-  using namespace ctrfe;
-  if (!vect) return reinterpret_cast<const void*>(&fused_pool_kernel<DT, false, 5, MODE>);
-  switch (gs) {
-    case 0: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 0, MODE>);
-    case 1: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 1, MODE>);
-    case 2: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 2, MODE>);
-    case 3: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 3, MODE>);
-    case 4: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 4, MODE>);
-    default: return reinterpret_cast<const void*>(&fused_pool_kernel<DT, true, 5, MODE>);
+int zero_row_reserve(ctrfe_ctx* ctx, size_t row_bytes) {
+  if (ctx->zero_cap >= row_bytes) return CTRFE_OK;
+  if (ctx->zero_row) {
+    CU(cudaDeviceSynchronize());
+    CU(cudaFree(ctx->zero_row));
+    ctx->zero_row = nullptr;
   }
-}
-
-const void* fused_kernel(int dtype, int mode, bool vect, int gs) {
-  const bool sel = mode == ctrfe::kModeSelect;
-  switch (dtype) {
-    case CTRFE_F32: return sel ? fused_kernel_tm<CTRFE_F32, ctrfe::kModeSelect>(vect, gs) : fused_kernel_tm<CTRFE_F32, ctrfe::kModeAdd>(vect, gs);
-    case CTRFE_F16: return sel ? fused_kernel_tm<CTRFE_F16, ctrfe::kModeSelect>(vect, gs) : fused_kernel_tm<CTRFE_F16, ctrfe::kModeAdd>(vect, gs);
-    default: return sel ? fused_kernel_tm<CTRFE_BF16, ctrfe::kModeSelect>(vect, gs) : fused_kernel_tm<CTRFE_BF16, ctrfe::kModeAdd>(vect, gs);
-  }
+  size_t cap = row_bytes < (1u << 16) ? (1u << 16) : align_up(row_bytes, 256);
+  CU(cudaMalloc(reinterpret_cast<void**>(&ctx->zero_row), cap));
+  CU(cudaMemset(ctx->zero_row, 0, cap));
+  ctx->zero_cap = cap;
+  return CTRFE_OK;
 }
 
 // Validates a descriptor the way the reference ops' InferShape/Compute do, derives the launch
@@ -202,7 +196,21 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
-  const long long units = v ? row_bytes / 16 : d->dim;  // lane-sized pieces per row
+  int rc = zero_row_reserve(ctx, static_cast<size_t>(row_bytes));
+  if (rc) return rc;
+
+  // lane chunk: 32 bytes (one 256-bit load) for fp32 rows that allow it, else 16, else one element
+  int cb = 16;
+  // 256-bit lanes halve the instruction count but also the warps in flight; on B200 the
+  // 128-bit mapping measured faster for short sequences (profiles/), so 32-byte lanes are opt-in.
+  const char* use256 = getenv("CTRFE_LDG256");
+  if (v && d->dtype == CTRFE_F32 && row_bytes % 32 == 0 && use256 && use256[0] == '1') {
+    cb = 32;
+    for (int s = 0; s < d->n_slots; ++s)
+      if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
+  }
+  plan->chunk_bytes = cb;
+  const long long units = v ? row_bytes / cb : d->dim;  // lane-sized pieces per row
   int g_shift = 5;                                      // the scalar fallback always uses whole warps
   if (v) { g_shift = 0; while ((1 << g_shift) < units && g_shift < 5) ++g_shift; }
   const int tiles = static_cast<int>((units + (1 << g_shift) - 1) >> g_shift);
@@ -231,6 +239,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       ctrfe::KParams& k = plan->chunks[c];
       memset(&k, 0, sizeof(k));
       k.err = ctx->err_dev;
+      k.zero_row = ctx->zero_row;
       k.padding_idx = d->padding_idx;
       k.dim = static_cast<int>(d->dim);
       k.row_bytes = static_cast<int>(row_bytes);
@@ -258,24 +267,11 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     o.slot_index = s;
     if (sl.n_seg > max_seg[c]) max_seg[c] = sl.n_seg;
   }
-  // Persistent grid: as many CTAs as the device keeps resident at once (SMs x occupancy of
-  // this instantiation), split evenly over the launch's slots; each group then strides over
-  // its slot's segments (never more CTAs than there is work).
-  plan->kernels.clear();
   for (size_t c = 0; c < plan->chunks.size(); ++c) {
     const long long items = max_seg[c] * tiles;
-    if (items >= 0xffffffffLL) return fail(CTRFE_ERR_ARG, "fused: n_seg * column tiles must stay below 2^32");
-    const void* fn = fused_kernel(d->dtype, plan->modes[c], v, g_shift);
-    int occ = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, ctrfe::kThreads, 0));
-    if (occ < 1) occ = 1;
-    const long long need = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
-    const int ns = plan->chunks[c].n_slots;
-    long long per_slot = (static_cast<long long>(ctx->sm_count) * occ) / ns;
-    if (per_slot < 1) per_slot = 1;
-    const long long gx = need < per_slot ? need : per_slot;
-    plan->kernels.push_back(fn);
-    plan->grids.push_back(dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(ns), 1));
+    const long long gx = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
+    if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "fused: batch too large for one launch");
+    plan->grids.push_back(dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(plan->chunks[c].n_slots), 1));
   }
   plan->id_src.resize(d->n_slots);
   for (int s = 0; s < d->n_slots; ++s)
@@ -307,8 +303,8 @@ int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_i
         prev = v;
       }
       if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
-      if (prev >= (1ull << 32)) return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu: a slot holds < 2^32 ids", s,
-                                            (unsigned long long)prev);
+      if (prev > (1ull << 43)) return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large", s,
+                                           (unsigned long long)prev);
       if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows)
         return fail(CTRFE_ERR_ARG,
                     "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)",
@@ -319,11 +315,43 @@ int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_i
   return CTRFE_OK;
 }
 
+template <int DT, int MODE, int CB>
+void launch_fused_tm(bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  using namespace ctrfe;
+  if (!vect) { fused_pool_kernel<DT, false, 5, MODE, 16><<<grid, kThreads, 0, st>>>(p); return; }
+  switch (gs) {
+    case 0: fused_pool_kernel<DT, true, 0, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    case 1: fused_pool_kernel<DT, true, 1, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    case 2: fused_pool_kernel<DT, true, 2, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    case 3: fused_pool_kernel<DT, true, 3, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    case 4: fused_pool_kernel<DT, true, 4, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    default: fused_pool_kernel<DT, true, 5, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+  }
+}
+
+template <int DT>
+void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  if constexpr (DT == CTRFE_F32) {
+    if (cb == 32) {  // 256-bit lanes exist for fp32 rows only
+      if (mode == ctrfe::kModeSelect) launch_fused_tm<DT, ctrfe::kModeSelect, 32>(vect, gs, grid, st, p);
+      else launch_fused_tm<DT, ctrfe::kModeAdd, 32>(vect, gs, grid, st, p);
+      return;
+    }
+  }
+  if (mode == ctrfe::kModeSelect) launch_fused_tm<DT, ctrfe::kModeSelect, 16>(vect, gs, grid, st, p);
+  else launch_fused_tm<DT, ctrfe::kModeAdd, 16>(vect, gs, grid, st, p);
+}
+
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
-    void* args[] = {const_cast<ctrfe::KParams*>(&plan.chunks[c])};
-    CU(cudaLaunchKernel(plan.kernels[c], plan.grids[c], dim3(ctrfe::kThreads), args, 0, st));
+    const int m = plan.modes[c];
+    switch (plan.dtype) {
+      case CTRFE_F32: launch_fused_t<CTRFE_F32>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
+      case CTRFE_F16: launch_fused_t<CTRFE_F16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
+      default: launch_fused_t<CTRFE_BF16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
+    }
   }
+  CU(cudaGetLastError());
   return CTRFE_OK;
 }
 
@@ -385,6 +413,7 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
     if (s.host) cudaFreeHost(s.host);
   }
   if (c->scratch) cudaFree(c->scratch);
+  if (c->zero_row) cudaFree(c->zero_row);
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
   delete c;

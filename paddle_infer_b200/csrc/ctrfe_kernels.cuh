@@ -5,20 +5,14 @@
 // per column, apply the CVM transform, and store the pooled row once.  Nothing is
 // materialised in between (the reference writes and re-reads [K,D] and [B,D]).
 //
-// Mapping: a "group" of G = 2^GS adjacent lanes owns one (segment, column-tile) work
-// item at a time; each lane owns one 16-byte chunk of the row (VECT) or one element
-// (scalar fallback for widths/alignments that do not allow 128-bit access).  Lanes of a
-// group load consecutive ids with one coalesced request and broadcast them with warp
-// shuffles; the U row loads of a batch are all issued before the first dependent add, so
-// each lane keeps U independent 128-bit loads in flight while the adds stay strictly
-// sequential per column (bit-exact with the reference's order: jit/refer/refer.h:372-380,
-// math/sequence_pooling.cu:93-97).
-//
-// The grid is persistent: a group walks its slot's segments with a fixed stride and runs a
-// three-deep software pipeline over them -- while the rows of segment i are in flight, the
-// ids of segment i+1 and the LoD offsets of segment i+2 have already been requested.  The
-// dependent chain LoD -> ids -> rows, which costs three DRAM latencies when every segment
-// starts cold, is paid once per group instead of once per segment.
+// Mapping: a "group" of G = 2^g_shift adjacent lanes owns one (segment, column-tile)
+// work item; each lane owns one 16-byte chunk of the row (VECT) or one element
+// (scalar fallback for widths/alignments that do not allow 128-bit access).  Lanes of
+// a group load G consecutive ids with one coalesced request and broadcast them with
+// warp shuffles; the U row loads of a batch are all issued before the first dependent
+// add, so each lane keeps U independent 128-bit loads in flight while the adds stay
+// strictly sequential per column (bit-exact with the reference's order:
+// jit/refer/refer.h:372-380, math/sequence_pooling.cu:93-97).
 //
 // Compiled with -ftz=true -fmad=false: the reference CPU executor runs under FTZ+DAZ
 // (framework/naive_executor.cc:66) and never contracts a*b+c on this path.
@@ -28,6 +22,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "../../include/ctrfe.h"
 
 namespace ctrfe {
@@ -35,24 +31,24 @@ namespace ctrfe {
 // Resident CTAs per SM the register allocator must leave room for (tuned on B200 with ncu;
 // overridable at build time for experiments).
 #ifndef CTRFE_MINB32
-#define CTRFE_MINB32 5
+#define CTRFE_MINB32 8
 #endif
 #ifndef CTRFE_MINB16
 #define CTRFE_MINB16 4
 #endif
 
-constexpr int kThreads = 256;             // threads per CTA of the pooling kernel
-constexpr int kUnroll = 4;                // row loads in flight per lane
-constexpr int kMaxSlotsPerLaunch = 64;    // slot descriptors carried in the kernel parameters
-constexpr uint32_t kSkip = 0xffffffffu;   // row slot past the end of the sequence: no load, no add
-constexpr uint32_t kZero = 0xfffffffeu;   // padding_idx / out-of-range id: contributes a zero row
+constexpr int kThreads = 256;          // threads per CTA of the pooling kernel
+constexpr int kUnroll = 4;             // row loads in flight per lane
+constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters
+constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequence: no load, no add
+constexpr uint32_t kZero = 0xfffffffeu;  // padding_idx / out-of-range id: contributes a zero row
 
 // Slot descriptor, passed BY VALUE in the kernel parameter block (constant bank): a CTA
 // reads its slot's pointers without a dependent global load.
 struct SlotK {
   const char* table;               // [table_rows, dim] or dense X when id_kind == 2
   const void* ids;                 // int64 / int32
-  const unsigned long long* lod;   // device offsets [n_seg + 1]; every offset < 2^32
+  const unsigned long long* lod;   // device offsets [n_seg + 1]
   char* out;
   long long out_ld_bytes;          // bytes between consecutive output rows
   unsigned int table_rows;         // < 2^32 - 2
@@ -64,6 +60,7 @@ struct SlotK {
 
 struct KParams {
   unsigned long long* err;   // [0]: min over (slot << 44 | position) of bad ids, ~0 = none
+  const char* zero_row;      // >= row_bytes of zeros: what a padding / bad id reads
   long long padding_idx;
   int dim;
   int row_bytes;
@@ -72,9 +69,9 @@ struct KParams {
   int cvm_offset;
   int scale_mode;
   int init_mode;
+  int reserved;
   float pad_value;
   int n_slots;
-  int reserved;
   SlotK slots[kMaxSlotsPerLaunch];
 };
 
@@ -102,15 +99,22 @@ __device__ __forceinline__ uint32_t float_to_elem(float v) {
   }
 }
 
-// A lane's slice of one row: RW raw 32-bit words holding VEC elements.
-template <int DT, bool VECT>
+// A lane's slice of one row: CB bytes = RW raw 32-bit words holding VEC elements.  CB is 16
+// (one 128-bit load) or, for fp32 rows that are a multiple of 32 bytes, 32 (one 256-bit
+// load, LDG.E.256 on sm_100): half as many lanes per row, so half as many instructions per
+// byte on a path that ncu shows to be issue-bound.
+template <int DT, bool VECT, int CB = 16>
 struct Lane {
   static constexpr int ES = (DT == CTRFE_F32) ? 4 : 2;
-  static constexpr int VEC = VECT ? 16 / ES : 1;
-  static constexpr int RW = VECT ? 4 : 1;
+  static constexpr int VEC = VECT ? CB / ES : 1;
+  static constexpr int RW = VECT ? CB / 4 : 1;
 
   __device__ __forceinline__ static void load(const char* p, uint32_t (&w)[RW]) {
-    if constexpr (VECT) {
+    if constexpr (VECT && CB == 32) {
+      asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                   : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                   : "l"(p));
+    } else if constexpr (VECT) {
       uint4 v = ldg128(p);
       w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
     } else if constexpr (ES == 4) {
@@ -124,7 +128,7 @@ struct Lane {
     if constexpr (ES == 4) return w[e];
     else return (w[e >> 1] >> ((e & 1) * 16)) & 0xffffu;
   }
-  // both halves of a word as floats (16-bit types)
+  // both halves of word r as floats (16-bit types)
   __device__ __forceinline__ static float2 unpack2(uint32_t w) {
     if constexpr (DT == CTRFE_F16) {
       return __half22float2(*reinterpret_cast<const __half2*>(&w));
@@ -136,6 +140,16 @@ struct Lane {
 
 enum { kModeAdd = 0, kModeSelect = 1 };
 
+// (a0, a1) += (x0, x1): sm_100's packed fp32 add -- two independent IEEE round-to-nearest,
+// flush-to-zero adds in one instruction, so the per-column order and rounding are unchanged.
+__device__ __forceinline__ void add_f32x2(float& a0, float& a1, float x0, float x1) {
+  unsigned long long a, x;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "f"(x0), "f"(x1));
+  asm("add.rn.ftz.f32x2 %0, %0, %1;" : "+l"(a) : "l"(x));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(a));
+}
+
 // log(x + 1) as the reference CPU kernel evaluates it: the add in fp32, the log in fp64.
 __device__ __forceinline__ double cvm_log1(float x) { return log(static_cast<double>(x + 1.0f)); }
 
@@ -146,331 +160,300 @@ __device__ __forceinline__ double cvm_log1(float x) { return log(static_cast<dou
 
 // ---------------------------------------------------------------------------------------
 // fused gather + segmented pool + CVM.
-// grid = (CTAs per slot, slots in this launch); G = 1 << GS lanes per item.
+// grid = (ceil(max_items * G / kThreads), slots in this launch); G = 1 << GS lanes per item.
 // MODE: kModeAdd for SUM / AVERAGE / SQRT slots, kModeSelect for MAX / LAST / FIRST slots
 // (the host puts slots of different modes into different launches).
 // ---------------------------------------------------------------------------------------
-template <int DT, bool VECT, int GS, int MODE>
+template <int DT, bool VECT, int GS, int MODE, int CB>
 __global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
 fused_pool_kernel(const __grid_constant__ KParams kp) {
-  using L = Lane<DT, VECT>;
+  using L = Lane<DT, VECT, CB>;
   constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
-  constexpr int U = kUnroll;
-  constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
-  constexpr int R = G * NI;               // rows consumed per step of the sequence loop
+  constexpr int U = kUnroll * 16 / CB;               // row loads in flight per lane (same bytes)
+  constexpr int NI = G >= kUnroll ? 1 : kUnroll / G;  // ids held per lane
+  constexpr int R = G * NI;                           // rows consumed per step of the sequence loop
   constexpr bool selecting = MODE == kModeSelect;
-  constexpr unsigned GPC = kThreads >> GS;  // groups (work items in flight) per CTA
 
   const SlotK* const slp = &kp.slots[blockIdx.y];
+  const unsigned n_seg = slp->n_seg;
   const int tiles = kp.tiles;
-  const unsigned n_items = slp->n_seg * static_cast<unsigned>(tiles);  // host: < 2^32
-  if (blockIdx.x * GPC >= n_items) return;  // CTA past this slot's work
-  const unsigned stride = gridDim.x * GPC;
+  const unsigned long long first_item = (static_cast<unsigned long long>(blockIdx.x) * kThreads) >> GS;
+  if (first_item >= static_cast<unsigned long long>(n_seg) * tiles) return;  // CTA past this slot's work
 
+  const int pooltype = slp->pooltype;
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1);
-  unsigned item = blockIdx.x * GPC + (threadIdx.x >> GS);
-  unsigned warp_item = blockIdx.x * GPC + ((threadIdx.x & ~31u) >> GS);  // warp-uniform loop key
+  const unsigned long long item = (static_cast<unsigned long long>(blockIdx.x) * kThreads + threadIdx.x) >> GS;
+  unsigned seg = static_cast<unsigned>(item);
+  int tile = 0;
+  if (tiles > 1) { seg = static_cast<unsigned>(item / tiles); tile = static_cast<int>(item - static_cast<unsigned long long>(seg) * tiles); }
+  const bool seg_ok = seg < n_seg;
+  const int col0 = (tile * G + gl) * VEC;
+  const bool col_ok = col0 < kp.dim;
+
+  long long start = 0, end = 0;
+  if (seg_ok) {
+    const unsigned long long* __restrict__ lod = slp->lod;
+    start = static_cast<long long>(__ldg(lod + seg));
+    end = static_cast<long long>(__ldg(lod + seg + 1));
+  }
+  const int seg_len = static_cast<int>(end - start);  // rows of the sequence (for the scale)
+  if (selecting && seg_len > 0) {  // LAST / FIRST read exactly one row
+    if (pooltype == CTRFE_POOL_FIRST) end = start + 1;
+    else if (pooltype == CTRFE_POOL_LAST) start = end - 1;
+  }
+  const int len = static_cast<int>(end - start);
+  const int maxlen = __reduce_max_sync(kFull, len);
 
   // this CTA's slot, copied out of the parameter bank once
-  const int pooltype = slp->pooltype;
-  unsigned long long table = reinterpret_cast<unsigned long long>(slp->table);
-  unsigned long long lodp = reinterpret_cast<unsigned long long>(slp->lod);
-  unsigned long long idsp = reinterpret_cast<unsigned long long>(slp->ids);
+  unsigned long long lane_base = reinterpret_cast<unsigned long long>(slp->table) + static_cast<unsigned>(col0 * ES);
   unsigned table_rows = slp->table_rows;
   unsigned row_bytes = kp.row_bytes;
   int id_kind = slp->id_kind;
+  // address of this lane's first id (dense rows: the position itself)
+  unsigned long long idp = id_kind == 2 ? static_cast<unsigned long long>(start + gl)
+                                        : reinterpret_cast<unsigned long long>(slp->ids) +
+                                              static_cast<unsigned long long>(start + gl) * (id_kind == 1 ? 4u : 8u);
   const unsigned id_step = id_kind == 2 ? 1u : (id_kind == 1 ? 4u : 8u);
-  if (id_kind == 2) idsp = 0;
   const bool pad_on = kp.padding_idx != -1;
   const uint32_t pad_lo = static_cast<uint32_t>(kp.padding_idx);
   const uint32_t pad_hi = static_cast<uint32_t>(static_cast<unsigned long long>(kp.padding_idx) >> 32);
-  // SELECT copies the first row; ADD does so only in EmbSeqPool order (CTRFE_INIT_FIRST_ROW)
-  const bool copy_first = selecting || kp.init_mode == CTRFE_INIT_FIRST_ROW;
-  CTRFE_KEEP64(table);
-  CTRFE_KEEP64(lodp);
-  CTRFE_KEEP64(idsp);
+  CTRFE_KEEP64(lane_base);
   CTRFE_KEEP32(table_rows);
   CTRFE_KEEP32(row_bytes);
   CTRFE_KEEP32(id_kind);
 
-  // ---- pipeline stage 1: request the two LoD offsets of an item (low words: < 2^32) ----
-  auto issue_lod = [&](unsigned it, uint32_t& s_lo, uint32_t& e_lo) {
-    s_lo = 0u;
-    e_lo = 0u;
-    if (it < n_items) {
-      const unsigned seg = tiles > 1 ? it / static_cast<unsigned>(tiles) : it;
-      const unsigned* w = reinterpret_cast<const unsigned*>(lodp + static_cast<unsigned long long>(seg) * 8u);
-      s_lo = __ldg(w);
-      e_lo = __ldg(w + 2);
-    }
-  };
-
-  // Row index of the id at sequence position `off` of a segment starting at `start`: kSkip
-  // past the end; kZero for a row that reads as zeros -- padding_idx (tested before the
-  // range check, as embedding_kernel.cc:56-57 does) or an out-of-range id, which is also
-  // flagged for the host to raise so that the kernel itself never faults.
-  auto fetch_rid = [&](uint32_t start, int len, int off, bool report) -> uint32_t {
+  // Row index of the id at address `a` (sequence position `off`): kSkip past the end; kZero
+  // for a row that reads as zeros -- padding_idx (tested before the range check, as
+  // embedding_kernel.cc:56-57 does) or an out-of-range id, which is also flagged for the
+  // host to raise so that the kernel itself never faults.
+  auto fetch_rid = [&](unsigned long long a, int off) -> uint32_t {
     if (off >= len) return kSkip;
-    const unsigned long long pos = static_cast<unsigned long long>(start) + static_cast<unsigned>(off);
-    const unsigned long long a = idsp + pos * id_step;
     long long id;
     if (id_kind == 0) id = __ldg(reinterpret_cast<const long long*>(a));
     else if (id_kind == 1) id = static_cast<long long>(__ldg(reinterpret_cast<const int*>(a)));
-    else id = static_cast<long long>(pos);
+    else id = static_cast<long long>(a);
     const uint32_t lo = static_cast<uint32_t>(id), hi = static_cast<uint32_t>(static_cast<unsigned long long>(id) >> 32);
     const bool in_range = hi == 0u && lo < table_rows;  // table_rows < 2^32 - 2
     const bool is_pad = pad_on && lo == pad_lo && hi == pad_hi;
-    if (!in_range && !is_pad && report)
-      atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) | pos);
+    if (!in_range && !is_pad && tile == 0) {
+      atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) |
+                            static_cast<unsigned long long>(start + off));
+    }
     return (in_range && !is_pad) ? lo : kZero;
   };
 
-  // ---- pipeline stage 2: consume the offsets, request the first ids -------------------
-  struct Seg {
-    uint32_t start;   // first row position this item reads
-    int len;          // rows it reads (1 for LAST / FIRST)
-    int seg_len;      // rows of the sequence (the AVERAGE / SQRT divisor)
-    uint32_t cur[NI];
-  };
-  auto open_seg = [&](unsigned it, uint32_t s_lo, uint32_t e_lo, Seg& s) {
-    s.start = s_lo;
-    s.seg_len = static_cast<int>(e_lo - s_lo);
-    s.len = s.seg_len;
-    if (selecting && s.seg_len > 0) {  // LAST / FIRST read exactly one row
-      if (pooltype == CTRFE_POOL_FIRST) s.len = 1;
-      else if (pooltype == CTRFE_POOL_LAST) { s.start = e_lo - 1u; s.len = 1; }
+  float acc[VEC];
+  uint32_t sel[RW];  // selection pools on 16-bit types: raw bits of the selected elements
+  {
+    const float init = kp.init_mode == CTRFE_INIT_PAD ? kp.pad_value : 0.0f;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = init;
+#pragma unroll
+    for (int r = 0; r < RW; ++r) sel[r] = 0u;
+  }
+  // SELECT copies the first row; ADD does so only in EmbSeqPool order (CTRFE_INIT_FIRST_ROW)
+  const bool copy_first = selecting || kp.init_mode == CTRFE_INIT_FIRST_ROW;
+
+  uint32_t cur[NI];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) cur[i] = fetch_rid(idp + static_cast<unsigned long long>(i * G) * id_step, i * G + gl);
+  for (int base = 0; base < maxlen; base += R) {
+    idp += static_cast<unsigned long long>(R) * id_step;
+    uint32_t nxt[NI];  // next step's ids are requested before this step's rows
+#pragma unroll
+    for (int i = 0; i < NI; ++i) nxt[i] = kSkip;
+    if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
+#pragma unroll
+      for (int i = 0; i < NI; ++i)
+        nxt[i] = fetch_rid(idp + static_cast<unsigned long long>(i * G) * id_step, base + R + i * G + gl);
     }
-    const bool report = tiles == 1 || (it % static_cast<unsigned>(tiles)) == 0;
 #pragma unroll
-    for (int i = 0; i < NI; ++i) s.cur[i] = fetch_rid(s.start, s.len, i * G + gl, report);
-  };
-
-  // ---- pipeline stage 3: rows, reduction, epilogue, store ------------------------------
-  auto process = [&](unsigned it, Seg& sg) {
-    unsigned seg = it;
-    int tile = 0;
-    if (tiles > 1) { seg = it / static_cast<unsigned>(tiles); tile = static_cast<int>(it - seg * static_cast<unsigned>(tiles)); }
-    const bool seg_ok = it < n_items;
-    const int col0 = (tile * G + gl) * VEC;
-    const bool col_ok = col0 < kp.dim;
-    const unsigned long long lane_base = table + static_cast<unsigned>(col0 * ES);
-    const int len = sg.len;
-    const int maxlen = __reduce_max_sync(kFull, len);
-
-    float acc[VEC];
-    uint32_t sel[RW];  // selection pools on 16-bit types: raw bits of the selected elements
-    {
-      const float init = kp.init_mode == CTRFE_INIT_PAD ? kp.pad_value : 0.0f;
+    for (int c = 0; c < R / U; ++c) {
+      if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
+      uint32_t raw[U][RW];
+      bool ok[U];
 #pragma unroll
-      for (int e = 0; e < VEC; ++e) acc[e] = init;
+      for (int u = 0; u < U; ++u) {
+        const int j = c * U + u;
+        const uint32_t rid = __shfl_sync(kFull, cur[j / G], j % G, G);
+        ok[u] = (rid != kSkip) && col_ok;
+        // a kZero row (padding_idx / bad id) is added as zeros without touching memory
 #pragma unroll
-      for (int r = 0; r < RW; ++r) sel[r] = 0u;
-    }
-
-    for (int base = 0; base < maxlen; base += R) {
-      uint32_t nxt[NI];  // the next step's ids are requested before this step's rows
+        for (int r = 0; r < RW; ++r) raw[u][r] = 0u;
+        if (rid < kZero && col_ok)
+          L::load(reinterpret_cast<const char*>(lane_base + static_cast<unsigned long long>(rid) * row_bytes), raw[u]);
+      }
 #pragma unroll
-      for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(sg.start, len, base + R + i * G + gl, tile == 0);
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        const bool first = copy_first && (c == 0 && u == 0) && (base == 0);
+        if constexpr (MODE == kModeSelect) {
+          // out = row0; then strictly-greater replaces (math/sequence_pooling.cc:166-174)
+          if constexpr (DT == CTRFE_F16) {
+            // packed half compare: same order as the fp32 compare (the conversion is exact and
+            // monotone, half subnormals are normal floats); NaN never replaces; row 0 sticks
 #pragma unroll
-      for (int c = 0; c < R / U; ++c) {
-        if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
-        uint32_t raw[U][RW];
-        bool ok[U];
+            for (int r = 0; r < RW; ++r) {
+              const __half2 x2 = *reinterpret_cast<const __half2*>(&raw[u][r]);
+              const __half2 a2 = *reinterpret_cast<const __half2*>(&sel[r]);
+              const unsigned m = first ? 0xffffffffu : __hgt2_mask(x2, a2);
+              sel[r] = (sel[r] & ~m) | (raw[u][r] & m);
+            }
+          } else if constexpr (ES == 4) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int j = c * U + u;
-          const uint32_t rid = __shfl_sync(kFull, sg.cur[j / G], j % G, G);
-          ok[u] = (rid != kSkip) && col_ok;
-          // a kZero row (padding_idx / bad id) is added as zeros without touching memory
-#pragma unroll
-          for (int r = 0; r < RW; ++r) raw[u][r] = 0u;
-          if (rid < kZero && col_ok)
-            L::load(reinterpret_cast<const char*>(lane_base + static_cast<unsigned long long>(rid) * row_bytes), raw[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (!ok[u]) continue;
-          const bool first = copy_first && (c == 0 && u == 0) && (base == 0);
-          if constexpr (MODE == kModeSelect) {
-            // out = row0; then strictly-greater replaces (math/sequence_pooling.cc:166-174)
-            if constexpr (DT == CTRFE_F16) {
-              // packed half compare: same order as the fp32 compare (the conversion is exact and
-              // monotone, half subnormals are normal floats); NaN never replaces; row 0 sticks
-#pragma unroll
-              for (int r = 0; r < RW; ++r) {
-                const __half2 x2 = *reinterpret_cast<const __half2*>(&raw[u][r]);
-                const __half2 a2 = *reinterpret_cast<const __half2*>(&sel[r]);
-                const unsigned m = first ? 0xffffffffu : __hgt2_mask(x2, a2);
-                sel[r] = (sel[r] & ~m) | (raw[u][r] & m);
-              }
-            } else if constexpr (ES == 4) {
-#pragma unroll
-              for (int e = 0; e < VEC; ++e) {
-                const float x = __uint_as_float(raw[u][e]);
-                if (first || x > acc[e]) acc[e] = x;
-              }
-            } else {
-              uint32_t take[RW];
-#pragma unroll
-              for (int r = 0; r < RW; ++r) take[r] = 0u;
-#pragma unroll
-              for (int e = 0; e < VEC; ++e) {
-                const float x = elem_to_float<DT>(L::bits(raw[u], e));
-                if (first || x > acc[e]) {
-                  acc[e] = x;
-                  take[e >> 1] |= 0xffffu << ((e & 1) * 16);
-                }
-              }
-#pragma unroll
-              for (int r = 0; r < RW; ++r) sel[r] = (sel[r] & ~take[r]) | (raw[u][r] & take[r]);
+            for (int e = 0; e < VEC; ++e) {
+              const float x = __uint_as_float(raw[u][e]);
+              if (first || x > acc[e]) acc[e] = x;
             }
           } else {
-            if constexpr (ES == 4) {
+            uint32_t take[RW];
 #pragma unroll
-              for (int e = 0; e < VEC; ++e) {
-                const float x = __uint_as_float(raw[u][e]);
-                acc[e] = first ? x : acc[e] + x;
-              }
-            } else if constexpr (VECT) {
+            for (int r = 0; r < RW; ++r) take[r] = 0u;
 #pragma unroll
-              for (int r = 0; r < RW; ++r) {
-                const float2 x = L::unpack2(raw[u][r]);
-                acc[2 * r] = first ? x.x : acc[2 * r] + x.x;
-                acc[2 * r + 1] = first ? x.y : acc[2 * r + 1] + x.y;
+            for (int e = 0; e < VEC; ++e) {
+              const float x = elem_to_float<DT>(L::bits(raw[u], e));
+              if (first || x > acc[e]) {
+                acc[e] = x;
+                take[e >> 1] |= 0xffffu << ((e & 1) * 16);
               }
-            } else {
-              const float x = elem_to_float<DT>(raw[u][0]);
-              acc[0] = first ? x : acc[0] + x;
             }
+#pragma unroll
+            for (int r = 0; r < RW; ++r) sel[r] = (sel[r] & ~take[r]) | (raw[u][r] & take[r]);
+          }
+        } else {
+          if constexpr (ES == 4 && VECT) {
+            if (first) {
+#pragma unroll
+              for (int e = 0; e < VEC; ++e) acc[e] = __uint_as_float(raw[u][e]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < VEC; e += 2)  // two independent fp32 adds per instruction (FADD2)
+                add_f32x2(acc[e], acc[e + 1], __uint_as_float(raw[u][e]), __uint_as_float(raw[u][e + 1]));
+            }
+          } else if constexpr (ES == 4) {
+            const float x = __uint_as_float(raw[u][0]);
+            acc[0] = first ? x : acc[0] + x;
+          } else if constexpr (VECT) {
+#pragma unroll
+            for (int r = 0; r < RW; ++r) {
+              const float2 x = L::unpack2(raw[u][r]);
+              if (first) { acc[2 * r] = x.x; acc[2 * r + 1] = x.y; }
+              else add_f32x2(acc[2 * r], acc[2 * r + 1], x.x, x.y);
+            }
+          } else {
+            const float x = elem_to_float<DT>(raw[u][0]);
+            acc[0] = first ? x : acc[0] + x;
           }
         }
       }
-#pragma unroll
-      for (int i = 0; i < NI; ++i) sg.cur[i] = nxt[i];
     }
+#pragma unroll
+    for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
+  }
 
-    // ---- epilogue: pad / scale / CVM / store -----------------------------------------
-    const int seg_len = sg.seg_len;
-    bool use_sel = selecting && ES == 2;  // 16-bit selection pools store the selected bits
-    if (selecting && DT == CTRFE_F16 && kp.cvm_mode == CTRFE_CVM_USE && tile == 0 && gl == 0) {
-      // the half-compare path kept no float copy: the CVM columns need one
-      if constexpr (VECT && DT == CTRFE_F16) {
-        const float2 x = L::unpack2(sel[0]);
-        acc[0] = x.x;
-        acc[1] = x.y;
-      }
+  // ---- epilogue: pad / scale / CVM / store -------------------------------------------
+  bool use_sel = selecting && ES == 2;  // 16-bit selection pools store the selected bits
+  if (selecting && DT == CTRFE_F16 && kp.cvm_mode == CTRFE_CVM_USE && tile == 0 && gl == 0) {
+    // the half-compare path kept no float copy: the CVM columns need one
+    if constexpr (VECT && DT == CTRFE_F16) {
+      const float2 x = L::unpack2(sel[0]);
+      acc[0] = x.x;
+      acc[1] = x.y;
     }
-    if constexpr (!VECT && DT == CTRFE_F16) {
-      if (selecting) acc[0] = elem_to_float<DT>(sel[0]);
+  }
+  if constexpr (!VECT && DT == CTRFE_F16) {
+    if (selecting) acc[0] = elem_to_float<DT>(sel[0]);
+  }
+  if (seg_len == 0 && kp.init_mode != CTRFE_INIT_PAD) {
+    // empty sequence -> pad_value for every pooltype (sequence_pooling.cc:93-98,160-165,395-398)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = kp.pad_value;
+    use_sel = false;
+  } else if (seg_len > 0 && (pooltype == CTRFE_POOL_AVERAGE || pooltype == CTRFE_POOL_SQRT)) {
+    const float h = static_cast<float>(seg_len);
+    if (kp.scale_mode == CTRFE_SCALE_DIVIDE) {
+      const float d = pooltype == CTRFE_POOL_AVERAGE ? h : sqrtf(h);
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) acc[e] = acc[e] / d;
+    } else {
+      float s = 1.0f;
+      s = pooltype == CTRFE_POOL_AVERAGE ? s / h : s / sqrtf(h);
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) acc[e] = s * acc[e];
     }
-    if (seg_len == 0 && kp.init_mode != CTRFE_INIT_PAD) {
-      // empty sequence -> pad_value for every pooltype (sequence_pooling.cc:93-98,160-165,395-398)
-#pragma unroll
-      for (int e = 0; e < VEC; ++e) acc[e] = kp.pad_value;
-      use_sel = false;
-    } else if (seg_len > 0 && (pooltype == CTRFE_POOL_AVERAGE || pooltype == CTRFE_POOL_SQRT)) {
-      const float h = static_cast<float>(seg_len);
-      if (kp.scale_mode == CTRFE_SCALE_DIVIDE) {
-        const float d = pooltype == CTRFE_POOL_AVERAGE ? h : sqrtf(h);
-#pragma unroll
-        for (int e = 0; e < VEC; ++e) acc[e] = acc[e] / d;
-      } else {
-        float s = 1.0f;
-        s = pooltype == CTRFE_POOL_AVERAGE ? s / h : s / sqrtf(h);
-#pragma unroll
-        for (int e = 0; e < VEC; ++e) acc[e] = s * acc[e];
-      }
-    }
+  }
 
-    bool cvm_cols[2] = {false, false};  // which of this lane's leading elements were CVM-transformed
-    if (kp.cvm_mode == CTRFE_CVM_USE) {
-      // y0 = log(x0 + 1); y1 = log(x1 + 1) - y0   (cvm_op.h:34-37): the add in fp32, the log in
-      // fp64 narrowed to fp32, the subtraction against the ROUNDED y0.  The two logs run on two
-      // lanes at once (lane 1 borrows x1), halving the fp64 instruction stream.
-      const bool head = tile == 0;
-      if constexpr (VEC >= 2 && G >= 2) {
-        const float x1 = __shfl_sync(kFull, acc[1], 0, G);
-        double lg = 0.0;
-        if (head && gl < 2) lg = cvm_log1(gl == 0 ? acc[0] : x1);
-        const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);
-        float y1 = 0.0f;
-        if (head && gl == 1) y1 = static_cast<float>(lg - static_cast<double>(y0));
-        y1 = __shfl_sync(kFull, y1, 1, G);
-        if (head && gl == 0) { acc[0] = y0; acc[1] = y1; cvm_cols[0] = cvm_cols[1] = true; }
-      } else if constexpr (VEC >= 2) {
-        if (head) {
-          const float y0 = static_cast<float>(cvm_log1(acc[0]));
-          acc[1] = static_cast<float>(cvm_log1(acc[1]) - static_cast<double>(y0));
-          acc[0] = y0;
-          cvm_cols[0] = cvm_cols[1] = true;
-        }
-      } else {
-        double lg = 0.0;
-        if (head && gl < 2) lg = cvm_log1(acc[0]);
-        const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);  // column 1 lives on lane 1
-        if (head && gl == 0) { acc[0] = y0; cvm_cols[0] = true; }
-        if (head && gl == 1) { acc[0] = static_cast<float>(lg - static_cast<double>(y0)); cvm_cols[0] = true; }
-      }
-    }
-
-    if (!(seg_ok && col_ok)) return;
-    const int skip = kp.cvm_mode == CTRFE_CVM_STRIP ? kp.cvm_offset : 0;
-    char* orow = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes;
-
-    uint32_t packed[RW];
-#pragma unroll
-    for (int r = 0; r < RW; ++r) packed[r] = 0u;
-#pragma unroll
-    for (int e = 0; e < VEC; ++e) {
-      uint32_t b;
-      if (use_sel && !(e < 2 && cvm_cols[e & 1])) b = L::bits(sel, e);
-      else b = float_to_elem<DT>(acc[e]);
-      if constexpr (ES == 4) packed[e] = b;
-      else packed[e >> 1] |= b << ((e & 1) * 16);
-    }
-
-    if constexpr (VECT) {
-      char* dst = orow + static_cast<long long>(col0 - skip) * ES;
-      if (skip == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
-        *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-      } else {
-#pragma unroll
-        for (int e = 0; e < VEC; ++e) {
-          if (col0 + e < skip) continue;
-          const uint32_t b = L::bits(packed, e);
-          if constexpr (ES == 4) reinterpret_cast<uint32_t*>(dst)[e] = b;
-          else reinterpret_cast<unsigned short*>(dst)[e] = static_cast<unsigned short>(b);
-        }
+  bool cvm_cols[2] = {false, false};  // which of this lane's leading elements were CVM-transformed
+  if (kp.cvm_mode == CTRFE_CVM_USE) {
+    // y0 = log(x0 + 1); y1 = log(x1 + 1) - y0   (cvm_op.h:34-37): the add in fp32, the log in
+    // fp64 narrowed to fp32, the subtraction against the ROUNDED y0.  The two logs run on two
+    // lanes at once (lane 1 borrows x1), halving the fp64 instruction stream.
+    const bool head = tile == 0;
+    if constexpr (VEC >= 2 && G >= 2) {
+      const float x1 = __shfl_sync(kFull, acc[1], 0, G);
+      double lg = 0.0;
+      if (head && gl < 2) lg = cvm_log1(gl == 0 ? acc[0] : x1);
+      const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);
+      float y1 = 0.0f;
+      if (head && gl == 1) y1 = static_cast<float>(lg - static_cast<double>(y0));
+      y1 = __shfl_sync(kFull, y1, 1, G);
+      if (head && gl == 0) { acc[0] = y0; acc[1] = y1; cvm_cols[0] = cvm_cols[1] = true; }
+    } else if constexpr (VEC >= 2) {
+      if (head) {
+        const float y0 = static_cast<float>(cvm_log1(acc[0]));
+        acc[1] = static_cast<float>(cvm_log1(acc[1]) - static_cast<double>(y0));
+        acc[0] = y0;
+        cvm_cols[0] = cvm_cols[1] = true;
       }
     } else {
-      if (col0 >= skip) {
-        char* dst = orow + static_cast<long long>(col0 - skip) * ES;
-        if constexpr (ES == 4) *reinterpret_cast<uint32_t*>(dst) = packed[0];
-        else *reinterpret_cast<unsigned short*>(dst) = static_cast<unsigned short>(packed[0]);
+      double lg = 0.0;
+      if (head && gl < 2) lg = cvm_log1(acc[0]);
+      const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);  // column 1 lives on lane 1
+      if (head && gl == 0) { acc[0] = y0; cvm_cols[0] = true; }
+      if (head && gl == 1) { acc[0] = static_cast<float>(lg - static_cast<double>(y0)); cvm_cols[0] = true; }
+    }
+  }
+
+  if (!(seg_ok && col_ok)) return;
+  const int skip = kp.cvm_mode == CTRFE_CVM_STRIP ? kp.cvm_offset : 0;
+  char* orow = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes;
+
+  uint32_t packed[RW];
+#pragma unroll
+  for (int r = 0; r < RW; ++r) packed[r] = 0u;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) {
+    uint32_t b;
+    if (use_sel && !(e < 2 && cvm_cols[e & 1])) b = L::bits(sel, e);
+    else b = float_to_elem<DT>(acc[e]);
+    if constexpr (ES == 4) packed[e] = b;
+    else packed[e >> 1] |= b << ((e & 1) * 16);
+  }
+
+  if constexpr (VECT) {
+    char* dst = orow + static_cast<long long>(col0 - skip) * ES;
+    if (skip == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+#pragma unroll
+      for (int q = 0; q < RW / 4; ++q)
+        reinterpret_cast<uint4*>(dst)[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        if (col0 + e < skip) continue;
+        const uint32_t b = L::bits(packed, e);
+        if constexpr (ES == 4) reinterpret_cast<uint32_t*>(dst)[e] = b;
+        else reinterpret_cast<unsigned short*>(dst)[e] = static_cast<unsigned short>(b);
       }
     }
-  };
-
-  // ---- the pipeline ---------------------------------------------------------------------
-  uint32_t a_s, a_e, b_s, b_e;
-  issue_lod(item, a_s, a_e);
-  issue_lod(item + stride, b_s, b_e);
-  Seg s0;
-  open_seg(item, a_s, a_e, s0);
-  while (warp_item < n_items) {
-    uint32_t c_s, c_e;
-    issue_lod(item + 2u * stride, c_s, c_e);       // LoD of the item after next
-    Seg s1;
-    open_seg(item + stride, b_s, b_e, s1);         // ids of the next item
-    process(item, s0);                             // rows of this item
-    s0 = s1;
-    b_s = c_s;
-    b_e = c_e;
-    item += stride;
-    warp_item += stride;
+  } else {
+    if (col0 >= skip) {
+      char* dst = orow + static_cast<long long>(col0 - skip) * ES;
+      if constexpr (ES == 4) *reinterpret_cast<uint32_t*>(dst) = packed[0];
+      else *reinterpret_cast<unsigned short*>(dst) = static_cast<unsigned short>(packed[0]);
+    }
   }
 }
 
