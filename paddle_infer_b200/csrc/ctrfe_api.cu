@@ -57,9 +57,6 @@ struct ctrfe_ctx {
   // LoD image of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
   char* scratch = nullptr;
   size_t scratch_cap = 0;
-  // zeros that a padding_idx / out-of-range id reads instead of a table row
-  char* zero_row = nullptr;
-  size_t zero_cap = 0;
   std::vector<IdSource> last_ids;  // slots of the most recent fused launch
   const void* last_ids_owner = nullptr;  // identity tag only (never dereferenced): skip re-copying
   int sm_count = 148;
@@ -138,20 +135,6 @@ int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
   return CTRFE_OK;
 }
 
-int zero_row_reserve(ctrfe_ctx* ctx, size_t row_bytes) {
-  if (ctx->zero_cap >= row_bytes) return CTRFE_OK;
-  if (ctx->zero_row) {
-    CU(cudaDeviceSynchronize());
-    CU(cudaFree(ctx->zero_row));
-    ctx->zero_row = nullptr;
-  }
-  size_t cap = row_bytes < (1u << 16) ? (1u << 16) : align_up(row_bytes, 256);
-  CU(cudaMalloc(reinterpret_cast<void**>(&ctx->zero_row), cap));
-  CU(cudaMemset(ctx->zero_row, 0, cap));
-  ctx->zero_cap = cap;
-  return CTRFE_OK;
-}
-
 // Validates a descriptor the way the reference ops' InferShape/Compute do, derives the launch
 // geometry and fills everything of the plan that does not depend on where the LoD lives.
 // *lod_bytes = device bytes needed for the host LoDs (0 when they are already on the device).
@@ -196,9 +179,6 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
-  int rc = zero_row_reserve(ctx, static_cast<size_t>(row_bytes));
-  if (rc) return rc;
-
   // lane chunk: 32 bytes (one 256-bit load) for fp32 rows that allow it, else 16, else one element
   int cb = 16;
   // 256-bit lanes halve the instruction count but also the warps in flight; on B200 the
@@ -239,7 +219,6 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       ctrfe::KParams& k = plan->chunks[c];
       memset(&k, 0, sizeof(k));
       k.err = ctx->err_dev;
-      k.zero_row = ctx->zero_row;
       k.padding_idx = d->padding_idx;
       k.dim = static_cast<int>(d->dim);
       k.row_bytes = static_cast<int>(row_bytes);
@@ -413,7 +392,6 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
     if (s.host) cudaFreeHost(s.host);
   }
   if (c->scratch) cudaFree(c->scratch);
-  if (c->zero_row) cudaFree(c->zero_row);
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
   delete c;

@@ -60,7 +60,6 @@ struct SlotK {
 
 struct KParams {
   unsigned long long* err;   // [0]: min over (slot << 44 | position) of bad ids, ~0 = none
-  const char* zero_row;      // >= row_bytes of zeros: what a padding / bad id reads
   long long padding_idx;
   int dim;
   int row_bytes;
