@@ -154,6 +154,29 @@ int ctrfe_plan_destroy(ctrfe_plan* plan);
 /* Number of kernels one ctrfe_plan_launch enqueues (for launch accounting). */
 int ctrfe_plan_num_kernels(const ctrfe_plan* plan);
 
+/* ---- the fused front end without any allocation ------------------------------------
+ * No counterpart in the reference.  Same computation and argument rules as
+ * ctrfe_fused_forward, for callers that must not allocate memory: an op running inside
+ * Paddle's executor shares the GPU with the framework's allocator, which has normally
+ * reserved almost all of HBM already, so a cudaMalloc from a plugin may fail or fragment the
+ * remainder; cudaMalloc / cudaFree also synchronise the whole device, which stalls the
+ * other predictor streams of a serving process.  This entry point therefore takes no
+ * context, and keeps its scratch (the device copy of the host LoD offsets, the bad-id flag)
+ * in a fixed array inside the library that each GPU holds from load to exit.
+ *   - desc->lod_location must be CTRFE_LOD_HOST (pinned host memory keeps the copy async).
+ *   - Limits: the LoD offsets of one call, each slot padded to 16 bytes, must fit 4 MiB
+ *     (524,288 offsets); at most 64 slots, all accumulating (SUM/AVERAGE/SQRT) or all
+ *     selecting (MAX/LAST/FIRST).  Beyond that the call returns CTRFE_ERR_ARG.
+ *   - The array is shared by all calls on a device and keeps the last call's contents; each
+ *     call rewrites what it uses and resets the flag.  Calls whose GPU work overlaps (for
+ *     example on two streams) race on it: serialise them.
+ *   - The first call on a device looks up the array's device address; make that call before
+ *     any stream capture starts.
+ *   - bad_id_key_host (may be NULL): host address that receives, once `stream` has reached
+ *     this point, ~0 when every id was in range, else (slot << 44 | position) of the first
+ *     offender (the row was treated as zeros, as ctrfe_check_ids documents). */
+int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint64_t* bad_id_key_host);
+
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 
 /* lookup_table_v2 / phi embedding: out[k,:] = (ids[k]==padding_idx) ? 0 : table[ids[k],:].

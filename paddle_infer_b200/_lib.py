@@ -56,6 +56,7 @@ EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
+    "ctrfe_fused_forward_static",
 ]
 
 
@@ -81,6 +82,7 @@ def lib():
         L.ctrfe_embedding.argtypes = [vp, vp, i64, i64, vp, i32, i64, i64, vp, vp]
         L.ctrfe_sequence_pool.argtypes = [vp, vp, i32, i64, vp, i64, i32, C.c_float, vp, vp, vp]
         L.ctrfe_cvm.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp]
+        L.ctrfe_fused_forward_static.argtypes = [C.POINTER(FusedDesc), vp, vp]
         _lib = L
     return _lib
 

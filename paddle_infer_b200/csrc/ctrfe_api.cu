@@ -608,4 +608,164 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
   return CTRFE_OK;
 }
 
+
+// =====================================================================================
+// ctrfe_fused_forward_static: the fused front end for callers that must not allocate.
+//
+// The ordinary entry points keep their scratch (the device copy of the host LoD offsets and
+// the bad-id flag) in memory obtained with cudaMalloc / cudaHostAlloc.  Some callers of this
+// library cannot afford that: an op running inside Paddle's executor shares the device with
+// the framework's own allocator, which has usually reserved nearly all of HBM up front, so a
+// raw cudaMalloc from a plugin can fail outright or fragment what is left; cudaMalloc and
+// cudaFree also synchronise the whole device, stalling every other predictor stream in a
+// serving process; and allocation is off limits on latency-critical request threads in
+// general.  For them the same scratch lives in the fixed array below, which every GPU that
+// loads this library holds from load to exit.
+//
+// Limits and rules (also in include/ctrfe.h):
+//   * all LoD offsets of a call, each slot padded to 16 bytes, must fit CTRFE_STATIC_LOD_BYTES
+//     (4 MiB, i.e. 524,288 offsets); at most 64 slots of one pool family (all accumulating
+//     or all selecting pooltypes).  Larger calls are rejected with CTRFE_ERR_ARG.
+//   * the array is shared by every call on the device and keeps the previous call's
+//     contents.  This call rewrites the LoD image it uses and resets the bad-id flag itself;
+//     two calls whose GPU work overlaps (different streams) race on it -- serialise them.
+//   * the first call on each device resolves the array's device address (set-up below);
+//     make that first call before any stream capture begins.
+// =====================================================================================
+#define CTRFE_STATIC_LOD_BYTES (4u << 20)
+#define CTRFE_STATIC_FLAG_BYTES 256u
+static __device__ __align__(256) unsigned char g_static_scratch[CTRFE_STATIC_FLAG_BYTES + CTRFE_STATIC_LOD_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+unsigned char* g_static_ptr[kMaxStaticDevices] = {nullptr};  // device address of the array, per device
+
+// In host code the name g_static_scratch is only a handle for the runtime, not a device
+// address; the address a kernel can use comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+int static_scratch_for_current_device(unsigned char** out) {
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxStaticDevices) return fail(CTRFE_ERR_ARG, "static: device %d out of range", dev);
+  if (!g_static_ptr[dev]) {
+    unsigned char* p = nullptr;
+    CU(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch));
+    if (!p) return fail(CTRFE_ERR_CUDA, "static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return CTRFE_OK;
+}
+}  // namespace
+
+int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t* bad_id_key_host) {
+  auto st = static_cast<cudaStream_t>(stream);
+  // ---- argument checks (same rules as ctrfe_fused_forward), no heap, no device memory ----
+  if (!d || !d->slots || d->n_slots <= 0) return fail(CTRFE_ERR_ARG, "static: no slots");
+  if (d->n_slots > ctrfe::kMaxSlotsPerLaunch)
+    return fail(CTRFE_ERR_ARG, "static: %d slots exceed the limit of %d per call", d->n_slots, ctrfe::kMaxSlotsPerLaunch);
+  if (d->dtype != CTRFE_F32 && d->dtype != CTRFE_F16 && d->dtype != CTRFE_BF16)
+    return fail(CTRFE_ERR_UNSUPPORTED, "static: dtype %d not supported (f32, f16, bf16)", d->dtype);
+  if (d->dim <= 0 || d->dim > (1 << 20)) return fail(CTRFE_ERR_ARG, "static: bad dim %lld", (long long)d->dim);
+  if (d->cvm_mode < CTRFE_CVM_NONE || d->cvm_mode > CTRFE_CVM_STRIP) return fail(CTRFE_ERR_ARG, "static: bad cvm_mode %d", d->cvm_mode);
+  if (d->cvm_mode != CTRFE_CVM_NONE && d->dim < 2) return fail(CTRFE_ERR_ARG, "static: cvm needs the show and click columns");
+  if (d->cvm_mode == CTRFE_CVM_STRIP && (d->cvm_offset < 0 || d->cvm_offset >= d->dim))
+    return fail(CTRFE_ERR_ARG, "static: cvm_offset %d outside [0, dim)", d->cvm_offset);
+  if (d->scale_mode != CTRFE_SCALE_DIVIDE && d->scale_mode != CTRFE_SCALE_RECIPROCAL) return fail(CTRFE_ERR_ARG, "static: bad scale_mode");
+  if (d->init_mode < CTRFE_INIT_ZERO || d->init_mode > CTRFE_INIT_FIRST_ROW) return fail(CTRFE_ERR_ARG, "static: bad init_mode");
+  if (d->lod_location != CTRFE_LOD_HOST) return fail(CTRFE_ERR_ARG, "static: LoD offsets must be passed from host memory");
+
+  const int es = elem_size(d->dtype);
+  const long long row_bytes = d->dim * es;
+  const int d_out = static_cast<int>(d->dim) - (d->cvm_mode == CTRFE_CVM_STRIP ? d->cvm_offset : 0);
+  bool v = (row_bytes % 16) == 0;
+  size_t lod_bytes = 0;
+  long long max_seg = 0;
+  const int mode = d->slots[0].pooltype >= CTRFE_POOL_LAST ? ctrfe::kModeSelect : ctrfe::kModeAdd;
+  for (int s = 0; s < d->n_slots; ++s) {
+    const ctrfe_slot& sl = d->slots[s];
+    if (sl.n_seg < 0 || sl.n_seg > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "static: slot %d: n_seg outside [0, 2^31)", s);
+    if (sl.n_seg > 0 && (!sl.table || !sl.lod || !sl.out)) return fail(CTRFE_ERR_ARG, "static: slot %d: null table / lod / out", s);
+    if (sl.pooltype < CTRFE_POOL_AVERAGE || sl.pooltype > CTRFE_POOL_MAX) return fail(CTRFE_ERR_ARG, "static: slot %d: bad pooltype %d", s, sl.pooltype);
+    if ((sl.pooltype >= CTRFE_POOL_LAST ? ctrfe::kModeSelect : ctrfe::kModeAdd) != mode)
+      return fail(CTRFE_ERR_ARG, "static: slot %d mixes accumulating and selecting pooltypes in one call", s);
+    if (sl.ids_dtype != CTRFE_I64 && sl.ids_dtype != CTRFE_I32) return fail(CTRFE_ERR_UNSUPPORTED, "static: slot %d: ids must be int32 or int64", s);
+    if (sl.out_ld < d_out) return fail(CTRFE_ERR_ARG, "static: slot %d: out_ld %lld < output width %d", s, (long long)sl.out_ld, d_out);
+    if (sl.table_rows < 0 || sl.table_rows >= 0xfffffffeLL) return fail(CTRFE_ERR_UNSUPPORTED, "static: slot %d: table_rows outside [0, 2^32 - 2)", s);
+    if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
+    if (sl.n_seg > max_seg) max_seg = sl.n_seg;
+    lod_bytes += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+    // LoD rules (CheckLoD, lod_tensor.h:74-104), read in place from the caller's host memory
+    if (sl.n_seg > 0) {
+      uint64_t prev = sl.lod[0];
+      bool mono = true;
+      for (int64_t i = 1; i <= sl.n_seg; ++i) { mono &= sl.lod[i] >= prev; prev = sl.lod[i]; }
+      if (!mono) return fail(CTRFE_ERR_ARG, "static: slot %d: LoD offsets must be non-decreasing", s);
+      if (prev >= (1ull << 32)) return fail(CTRFE_ERR_ARG, "static: slot %d: a slot holds < 2^32 ids", s);
+      if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows) return fail(CTRFE_ERR_ARG, "static: slot %d: last LoD offset exceeds the rows of X", s);
+    }
+  }
+  if (lod_bytes > CTRFE_STATIC_LOD_BYTES)
+    return fail(CTRFE_ERR_ARG, "static: %zu bytes of LoD offsets exceed the %u-byte static scratch (use ctrfe_fused_forward)",
+                lod_bytes, CTRFE_STATIC_LOD_BYTES);
+
+  unsigned char* scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  auto* flag = reinterpret_cast<unsigned long long*>(scratch);
+  unsigned char* lod_img = scratch + CTRFE_STATIC_FLAG_BYTES;
+
+  // the flag starts at "no bad id" (all ones) on every call; the LoD image is overwritten
+  CU(cudaMemsetAsync(flag, 0xff, 8, st));
+
+  ctrfe::KParams k;  // 3.7 KB, on the stack
+  memset(&k, 0, sizeof(k));
+  const long long units = v ? row_bytes / 16 : d->dim;
+  int g_shift = 5;
+  if (v) { g_shift = 0; while ((1 << g_shift) < units && g_shift < 5) ++g_shift; }
+  const int tiles = static_cast<int>((units + (1 << g_shift) - 1) >> g_shift);
+  k.err = flag;
+  k.padding_idx = d->padding_idx;
+  k.dim = static_cast<int>(d->dim);
+  k.row_bytes = static_cast<int>(row_bytes);
+  k.tiles = tiles;
+  k.cvm_mode = d->cvm_mode;
+  k.cvm_offset = d->cvm_offset;
+  k.scale_mode = d->scale_mode;
+  k.init_mode = d->init_mode;
+  k.pad_value = d->pad_value;
+  k.n_slots = d->n_slots;
+  size_t off = 0;
+  for (int s = 0; s < d->n_slots; ++s) {
+    const ctrfe_slot& sl = d->slots[s];
+    ctrfe::SlotK& o = k.slots[s];
+    o.table = static_cast<const char*>(sl.table);
+    o.ids = sl.ids;
+    o.lod = reinterpret_cast<const unsigned long long*>(lod_img + off);
+    o.out = static_cast<char*>(sl.out);
+    o.out_ld_bytes = sl.out_ld * es;
+    o.table_rows = static_cast<unsigned>(sl.table_rows);
+    o.n_seg = static_cast<unsigned>(sl.n_seg);
+    o.pooltype = static_cast<short>(sl.pooltype);
+    o.id_kind = static_cast<short>(sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2);
+    o.slot_index = s;
+    // straight from the caller's host array into the static image (pinned memory keeps this
+    // asynchronous; pageable memory is staged by the driver)
+    if (sl.lod) CU(cudaMemcpyAsync(lod_img + off, sl.lod, static_cast<size_t>(sl.n_seg + 1) * 8, cudaMemcpyHostToDevice, st));
+    off += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+  }
+  const long long items = max_seg * tiles;
+  const long long gx = ((items << g_shift) + ctrfe::kThreads - 1) / ctrfe::kThreads;
+  if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "static: batch too large for one launch");
+  const dim3 grid(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(d->n_slots), 1);
+  switch (d->dtype) {
+    case CTRFE_F32: launch_fused_t<CTRFE_F32>(mode, v, g_shift, 16, grid, st, k); break;
+    case CTRFE_F16: launch_fused_t<CTRFE_F16>(mode, v, g_shift, 16, grid, st, k); break;
+    default: launch_fused_t<CTRFE_BF16>(mode, v, g_shift, 16, grid, st, k); break;
+  }
+  CU(cudaGetLastError());
+  if (bad_id_key_host) CU(cudaMemcpyAsync(bad_id_key_host, flag, 8, cudaMemcpyDeviceToHost, st));
+  return CTRFE_OK;
+}
+
 }  // extern "C"
