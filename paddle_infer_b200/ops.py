@@ -427,43 +427,121 @@ def fused_embedding_seq_pool(W: torch.Tensor, Ids: torch.Tensor, lod, combiner: 
 # ------------------------------------------------------------------------------------------
 class HostFrontEnd:
     """The fused front end with HOST inputs and outputs: per-slot id arrays and LoD offsets in
-    (pinned) host memory in, the pooled [B, S*D_out] block in pinned host memory out.  This is
-    the shape of the reference's feed path -- ZeroCopyTensor::CopyFromCpu + SetLoD per slot,
-    CopyToCpu on the result (inference/api/details/zero_copy_tensor.cc) -- around one fused
-    launch.  Device staging is allocated once and reused; run() is synchronous on return."""
+    pinned host memory in, the pooled rows in pinned host memory out.  This is the shape of the
+    reference's feed path -- ZeroCopyTensor::CopyFromCpu + SetLoD per slot, CopyToCpu on the
+    result (inference/api/details/zero_copy_tensor.cc) -- around one fused launch.  run() is
+    synchronous on return and yields one [B, D_out] pinned host view per slot (the op's
+    Out@VECTOR); concat=True instead fills one [B, S*D_out] block.
+
+    mode="zero_copy" (default): the kernel itself reads the ids and LoD offsets from the pinned
+    host buffers and writes the pooled rows into the pinned output, over PCIe, inside the one
+    launch -- no staging copies, and the transfers overlap the table gathers by construction.
+    The buffers must be pinned (cudaHostAlloc / torch pin_memory) so the device can address
+    them; LoD offsets are then not validated on the host (as with CTRFE_LOD_DEVICE).  A serving
+    loop that reuses its I/O buffers binds them once (bind()) and then only launches.
+    mode="copy": explicit H2D copies of the ids, host-validated LoD upload, launch, D2H copy."""
 
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
-                 padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2,
-                 ctx: Optional[Context] = None):
+                 padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, mode: str = "zero_copy",
+                 concat: bool = False, ctx: Optional[Context] = None):
         tables = _as_list(W, n_slots)
         t0 = tables[0]
         _need_cuda(t0, "W")
+        if mode not in ("zero_copy", "copy"):
+            raise InvalidArgument("mode must be 'zero_copy' or 'copy'")
+        self.mode, self.concat = mode, concat
         self.tables, self.S, self.B = tables, n_slots, batch
         self.pools = _as_list(pooltype, n_slots)
         self.kw = dict(pad_value=pad_value, padding_idx=padding_idx, use_cvm=use_cvm, cvm_offset=cvm_offset)
         self.ctx = ctx or default_context(t0.device)
-        d_out = t0.shape[1] - (cvm_offset if use_cvm is False else 0)
-        self.dev_ids = [torch.empty(max_ids_per_slot, dtype=torch.int64, device=t0.device) for _ in range(n_slots)]
-        self.dev_out = torch.empty((batch, n_slots * d_out), dtype=t0.dtype, device=t0.device)
-        self.host_out = torch.empty((batch, n_slots * d_out), dtype=t0.dtype, pin_memory=True)
+        self.dim = t0.shape[1]
+        self.d_out = t0.shape[1] - (cvm_offset if use_cvm is False else 0)
+        shape = (batch, n_slots * self.d_out) if concat else (n_slots, batch, self.d_out)
+        self.host_out = torch.empty(shape, dtype=t0.dtype, pin_memory=True)
+        if mode == "copy":
+            self.dev_ids = [torch.empty(max_ids_per_slot, dtype=torch.int64, device=t0.device) for _ in range(n_slots)]
+            self.dev_out = torch.empty(shape, dtype=t0.dtype, device=t0.device)
         self.h2d_bytes = 0
-        self.d2h_bytes = 0
+        self.d2h_bytes = self.host_out.numel() * self.host_out.element_size()
 
-    def run(self, ids_host: Sequence[torch.Tensor], lods_host: Sequence[np.ndarray], check: bool = False):
-        ids_dev = []
-        h2d = 0
-        for s in range(self.S):
-            n = ids_host[s].numel()
-            d = self.dev_ids[s][:n]
-            d.copy_(ids_host[s], non_blocking=True)
-            ids_dev.append(d)
-            h2d += n * 8 + lods_host[s].size * 8
-        ctr_fused_emb_seqpool_cvm(self.tables if len(self.tables) > 1 else self.tables[0], ids_dev, lods_host,
-                                  self.pools, concat=True, out=self.dev_out, check=False, ctx=self.ctx, **self.kw)
-        self.host_out.copy_(self.dev_out, non_blocking=True)
+    def _result(self):
+        return self.host_out if self.concat else [self.host_out[s] for s in range(self.S)]
+
+    def _out_views(self, block):
+        if self.concat:
+            return [block[:, s * self.d_out:(s + 1) * self.d_out] for s in range(self.S)], self.S * self.d_out
+        return [block[s] for s in range(self.S)], self.d_out
+
+    def _desc(self, ids_host, lods_host):
+        for t in list(ids_host) + list(lods_host):
+            if not (isinstance(t, torch.Tensor) and t.is_pinned()):
+                raise InvalidArgument("zero_copy mode needs pinned host tensors for ids and LoD offsets")
+        S = self.S
+        use_cvm = self.kw["use_cvm"]
+        cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
+        outs, ld = self._out_views(self.host_out)
+        slots = (B.Slot * S)()
+        for s in range(S):
+            t = self.tables[s]
+            slots[s] = B.Slot(t.data_ptr(), t.shape[0], ids_host[s].data_ptr(), lods_host[s].data_ptr(),
+                              lods_host[s].numel() - 1, outs[s].data_ptr(), ld, B.POOLTYPES[self.pools[s]],
+                              _IDT[ids_host[s].dtype])
+        desc = B.FusedDesc(S, _DT[self.tables[0].dtype], slots, self.dim, int(self.kw["padding_idx"]),
+                           float(self.kw["pad_value"]), cvm_mode, self.kw["cvm_offset"], B.SCALE_DIVIDE,
+                           B.INIT_ZERO, B.LOD_DEVICE, 0)
+        h2d = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.numel() * 8 for l in lods_host)
+        return desc, slots, h2d
+
+    def bind(self, ids_host: Sequence[torch.Tensor], lods_host: Sequence[torch.Tensor]) -> "BoundHostCall":
+        """zero_copy only: fix the (pinned) input buffers once; each BoundHostCall.run() is then
+        one kernel launch + one stream synchronise, whatever the buffers currently hold."""
+        if self.mode != "zero_copy":
+            raise InvalidArgument("bind() needs mode='zero_copy'")
+        desc, slots, h2d = self._desc(ids_host, lods_host)
+        h = C.c_void_p()
+        stream = torch.cuda.current_stream(self.tables[0].device)
+        B.check(B.lib().ctrfe_plan_create(self.ctx.handle, C.byref(desc), stream.cuda_stream, C.byref(h)))
+        return BoundHostCall(self, FusedPlan(self.ctx, h, None, (ids_host, lods_host, slots)), h2d)
+
+    def run(self, ids_host: Sequence[torch.Tensor], lods_host: Sequence, check: bool = False):
+        """ids_host: pinned int64/int32 CPU tensors, one per slot.  lods_host: per slot the
+        offsets -- numpy uint64 arrays (mode="copy") or pinned int64 CPU tensors (zero_copy)."""
+        S = self.S
+        stream = torch.cuda.current_stream(self.tables[0].device)
+        if self.mode == "copy":
+            ids_dev = []
+            for s in range(S):
+                d = self.dev_ids[s][:ids_host[s].numel()]
+                d.copy_(ids_host[s], non_blocking=True)
+                ids_dev.append(d)
+            outs, ld = self._out_views(self.dev_out)
+            desc, keep = _build_desc(self.tables, ids_dev, lods_host, self.pools, outs, ld, dim=self.dim,
+                                     dtype=_DT[self.tables[0].dtype], pad_value=self.kw["pad_value"],
+                                     padding_idx=self.kw["padding_idx"],
+                                     cvm_mode=B.CVM_NONE if self.kw["use_cvm"] is None else (B.CVM_USE if self.kw["use_cvm"] else B.CVM_STRIP),
+                                     cvm_offset=self.kw["cvm_offset"], scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_ZERO,
+                                     lod_on_device=False)
+            B.check(B.lib().ctrfe_fused_forward(self.ctx.handle, C.byref(desc), stream.cuda_stream))
+            self.host_out.copy_(self.dev_out, non_blocking=True)
+            self.h2d_bytes = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.size * 8 for l in lods_host)
+        else:
+            desc, slots, self.h2d_bytes = self._desc(ids_host, lods_host)
+            B.check(B.lib().ctrfe_fused_forward(self.ctx.handle, C.byref(desc), stream.cuda_stream))
         if check:
             self.ctx.check_ids()  # synchronises
         else:
-            torch.cuda.current_stream(self.dev_out.device).synchronize()
-        self.h2d_bytes, self.d2h_bytes = h2d, self.host_out.numel() * self.host_out.element_size()
-        return self.host_out
+            stream.synchronize()
+        return self._result()
+
+
+class BoundHostCall:
+    """HostFrontEnd with its input buffers bound: run() = one launch + one synchronise."""
+
+    def __init__(self, fe: HostFrontEnd, plan: FusedPlan, h2d_bytes: int):
+        self.fe, self.plan, self.h2d_bytes, self.d2h_bytes = fe, plan, h2d_bytes, fe.d2h_bytes
+        self._stream = torch.cuda.current_stream(fe.tables[0].device)
+
+    def run(self):
+        self.plan.launch()
+        self._stream.synchronize()
+        return self.fe._result()

@@ -434,3 +434,42 @@ def test_linearity_property_full_batch(env):
     # checksum of checksums: sum over all pooled rows == sum over all gathered rows (fp64)
     total_rows = sum(tab[i].double().sum().item() for i in ids_t)
     assert abs(a.double().sum().item() - total_rows) <= 1e-6 * max(1.0, abs(total_rows))
+
+
+def test_host_front_end_modes(env):
+    """The host-buffer doorway (what bench.py's e2e leg calls): zero-copy (the kernel reads the
+    pinned ids / LoD and writes the pinned output itself), the same with buffers bound once, and
+    the explicit-copy mode all equal the device-resident call."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(44)
+    S, Bsz, N, D = 5, 200, 3000, 16
+    table, ids, lods = _random_case(rng, S, Bsz, N, D, 9, "f32")
+    tt = _t(table, dev)
+    want = O.fused_forward([table], ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE)
+    ids_p = [torch.from_numpy(i).pin_memory() for i in ids]
+    lods_p = [torch.from_numpy(l.astype(np.int64)).pin_memory() for l in lods]
+    max_ids = max(i.size for i in ids)
+    fe = ops.HostFrontEnd(tt, S, Bsz, max_ids, "SUM", use_cvm=True, mode="zero_copy")
+    got = fe.run(ids_p, lods_p, check=True)
+    for s in range(S):
+        assert not got[s].is_cuda
+        _assert_cvm_close(got[s].numpy(), want[s], True)
+    fe.host_out.zero_()
+    call = fe.bind(ids_p, lods_p)
+    got = call.run()
+    for s in range(S):
+        _assert_cvm_close(got[s].numpy(), want[s], True)
+    assert call.h2d_bytes == sum(i.size * 8 for i in ids) + S * (Bsz + 1) * 8
+    assert call.d2h_bytes == S * Bsz * D * 4
+    # new ids in the same bound buffers: the next run() sees them
+    ids_p[0].copy_(torch.from_numpy(np.roll(ids[0], 1)))
+    want0 = O.fused_forward([table], [np.roll(ids[0], 1)], [lods[0]], ["SUM"], cvm_mode=O.CVM_USE)[0]
+    _assert_cvm_close(call.run()[0].numpy(), want0, True)
+    ids_p[0].copy_(torch.from_numpy(ids[0]))
+    # explicit-copy mode, concat layout
+    fe2 = ops.HostFrontEnd(tt, S, Bsz, max_ids, "SUM", use_cvm=True, mode="copy", concat=True)
+    got2 = fe2.run(ids_p, lods, check=True).numpy().reshape(Bsz, S, D)
+    for s in range(S):
+        _assert_cvm_close(got2[:, s, :], want[s], True)
+    with pytest.raises(ops.InvalidArgument, match="pinned"):
+        fe.run([torch.from_numpy(i) for i in ids], lods_p)
