@@ -260,17 +260,32 @@ def run_ours(args):
     from paddle_infer_b200 import ops
 
     cfg = synth.configs()[args.workload]
-    S, Bsz, D = cfg.slots, cfg.batch, cfg.dim
+    S, D = cfg.slots, cfg.dim
     tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
+    # cfg4 on N > 1 GPUs: ONE logical table row-sharded over the ranks (row r on rank r % N),
+    # the global batch split over the ranks (strong scaling); remote rows are fetched by the
+    # pooling kernel itself over NVLink.  Everything else: a full table replica per rank.
+    sharded = args.workload == "cfg4" and world > 1
+    Bsz = cfg.batch // world if sharded else cfg.batch
+    n_batches = 4 if cfg.batch * cfg.slots * cfg.dim * cfg.elem_size > (256 << 20) else N_BATCHES
+    shard_table = None
     tables = []
-    for t in range(cfg.n_tables()):
-        tab = torch.empty((cfg.rows, D), dtype=tdt, device=dev)
-        synth.fill_table(tab, cfg.seed + 1000 * t, cvm_cols=cfg.use_cvm is not None)
-        tables.append(tab)
-    W = tables if len(tables) > 1 else tables[0]
+    if sharded:
+        from paddle_infer_b200 import shard as shard_mod
+        shard_table = shard_mod.ShardedTable(cfg.rows, D, tdt)
+        synth.fill_table(shard_table.local, cfg.seed, row0=rank, row_stride=world, cvm_cols=cfg.use_cvm is not None)
+        torch.cuda.synchronize()
+        dist.barrier()
+        W = shard_table
+    else:
+        for t in range(cfg.n_tables()):
+            tab = torch.empty((cfg.rows, D), dtype=tdt, device=dev)
+            synth.fill_table(tab, cfg.seed + 1000 * t, cvm_cols=cfg.use_cvm is not None)
+            tables.append(tab)
+        W = tables if len(tables) > 1 else tables[0]
 
     # ---- batches resident in HBM (ids, LoD, output blocks), one plan each ----------------
-    host_batches = [synth.draw_batch(cfg, step=rank * 1000 + b) for b in range(N_BATCHES)]
+    host_batches = [synth.draw_batch(cfg, step=rank * 1000 + b, batch=Bsz) for b in range(n_batches)]
     plans, k_tots = [], []
     for hb in host_batches:
         ids_d = [torch.from_numpy(i).to(dev) for i in hb.ids]
@@ -284,7 +299,7 @@ def run_ours(args):
 
     K, Wm = args.steps, max(args.warmup, 0)
     for i in range(Wm):
-        plans[i % N_BATCHES].launch()
+        plans[i % n_batches].launch()
     ctx.check_ids()  # also a sync
 
     n_ev = K + 1 if K <= 20000 else 0
@@ -298,12 +313,12 @@ def run_ours(args):
     if n_ev:
         evs[0].record(stream)
         for i in range(K):
-            plans[(Wm + i) % N_BATCHES].launch()
+            plans[(Wm + i) % n_batches].launch()
             evs[i + 1].record(stream)
     else:
         evs[0].record(stream)
         for i in range(K):
-            plans[(Wm + i) % N_BATCHES].launch()
+            plans[(Wm + i) % n_batches].launch()
         evs[1].record(stream)
     sampler.sample()  # the queue is still draining: a sample under load even for tiny K
     torch.cuda.synchronize()
@@ -318,8 +333,10 @@ def run_ours(args):
         kern_ms_med = float(np.median(per))
     else:
         kern_ms = kern_ms_med = elapsed_ms / K
-    k_used = [k_tots[(Wm + i) % N_BATCHES] for i in range(K)]
-    alg_bytes = float(np.mean([cfg.algorithmic_bytes(k) for k in k_used]))
+    k_used = [k_tots[(Wm + i) % n_batches] for i in range(K)]
+    es = cfg.elem_size
+    # SURVEY 8(d) per-unit figures x the units one launch (this rank's batch) processes
+    alg_bytes = float(np.mean([k * (8 + D * es) + S * (Bsz + 1) * 8 + S * Bsz * cfg.d_out * es for k in k_used]))
 
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -336,15 +353,15 @@ def run_ours(args):
     pinned = [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
     if args.e2e_mode == "zero_copy":
         e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
-        calls = [fe.bind(pinned[b], e2e_lods[b]) for b in range(N_BATCHES)]
+        calls = [fe.bind(pinned[b], e2e_lods[b]) for b in range(n_batches)]
         step_fns = [c.run for c in calls]
         h2d_of = [c.h2d_bytes for c in calls]
     else:
-        step_fns = [(lambda b=b: fe.run(pinned[b], host_batches[b].lods)) for b in range(N_BATCHES)]
+        step_fns = [(lambda b=b: fe.run(pinned[b], host_batches[b].lods)) for b in range(n_batches)]
         h2d_of = [sum(i.numel() * 8 for i in pinned[b]) + sum(l.size * 8 for l in host_batches[b].lods)
-                  for b in range(N_BATCHES)]
+                  for b in range(n_batches)]
     for i in range(3):
-        step_fns[i % N_BATCHES]()
+        step_fns[i % n_batches]()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -353,8 +370,8 @@ def run_ours(args):
     e0.record(stream)
     h2d = d2h = 0
     for i in range(Ke):
-        step_fns[i % N_BATCHES]()
-        h2d += h2d_of[i % N_BATCHES]
+        step_fns[i % n_batches]()
+        h2d += h2d_of[i % n_batches]
         d2h += fe.d2h_bytes
     e1.record(stream)
     torch.cuda.synchronize()
@@ -369,12 +386,16 @@ def run_ours(args):
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
-        "ms_per_step": elapsed_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": elapsed_max / K, "higher_is_better": True, "scaling": "strong" if sharded else "weak",
+        "vs_baseline": None,
         "dtype": cfg.dtype, "data": "synthetic",
-        "config": {"workload": _workload_name(cfg), "global_batch": Bsz * world, "parallelism": f"replica x{world}",
+        "config": {"workload": _workload_name(cfg), "global_batch": Bsz * world,
+                   "parallelism": (f"table row-sharded x{world} (row r on GPU r % {world}), batch split x{world}, remote rows "
+                                   "fetched by the pooling kernel over NVLink peer mappings" if sharded
+                                   else f"replica x{world}"),
                    "l2_hygiene": f"table {cfg.n_tables() * cfg.rows * D * cfg.elem_size / 1e9:.1f} GB >> L2; timed loop "
-                                 f"rotates {N_BATCHES} distinct resident batches (ids+LoD+out "
-                                 f"{N_BATCHES * alg_bytes / 1e6:.0f} MB > 126 MB L2); hot table rows stay cached as in "
+                                 f"rotates {n_batches} distinct resident batches (ids+LoD+out "
+                                 f"{n_batches * alg_bytes / 1e6:.0f} MB > 126 MB L2); hot table rows stay cached as in "
                                  "steady-state serving",
                    "lod": "resident in HBM (value); host LoD uploaded per call (e2e)"},
         "clocks": sampler.summary(),
@@ -389,6 +410,13 @@ def run_ours(args):
                          "the pinned per-slot host outputs over PCIe inside the one launch, then the stream is synchronised" if args.e2e_mode == "zero_copy" else
                          "HostFrontEnd copy: H2D ids + LoD upload, launch, D2H output")},
     }
+    if sharded:
+        # bytes this rank pulls over NVLink per launch: every row whose owner is another GPU
+        nv_bytes = float(np.mean(k_used)) * (world - 1) / world * D * es
+        nv_gbs = nv_bytes / (kern_ms * 1e-3) / 1e9
+        line["nvlink"] = {"bytes_in_per_launch_per_gpu": nv_bytes, "achieved": nv_gbs, "unit": "GB/s",
+                          "peak": 770.0, "peak_source": "B200_PROFILING.md measured peer copy, per direction per GPU",
+                          "frac": nv_gbs / 770.0}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tabs, hb4, rows = host_table_and_batches(cfg, synth, 4, torch, tables)
         line["cpu_baseline"] = cpu_leg(cfg, tabs, hb4, budget_s=args.cpu_budget)
@@ -396,6 +424,9 @@ def run_ours(args):
         line["cpu_baseline"] = None
     if rank == 0:
         print(json.dumps(line), flush=True)
+    if shard_table is not None:
+        del plans, fe
+        shard_table.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -136,17 +136,19 @@ def _synth_lib():
             raise ImportError(f"{_LIB} missing: run __graft_entry__.build()")
         _lib = C.CDLL(_LIB)
         _lib.synth_fill_table.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_ulonglong, C.c_longlong,
-                                          C.c_int, C.c_void_p]
+                                          C.c_longlong, C.c_int, C.c_void_p]
     return _lib
 
 
-def fill_table(t, seed: int, row0: int = 0, cvm_cols: bool = True) -> None:
-    """Fill the CUDA tensor t [rows, dim] with rows [row0, row0+rows) of the logical table."""
+def fill_table(t, seed: int, row0: int = 0, cvm_cols: bool = True, row_stride: int = 1) -> None:
+    """Fill the CUDA tensor t [rows, dim] with logical rows row0, row0 + row_stride, ... (one
+    shard of a row-sharded table when row_stride > 1)."""
     import torch
     code = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[t.dtype]
     assert t.is_cuda and t.is_contiguous()
     with torch.cuda.device(t.device):
-        rc = _synth_lib().synth_fill_table(t.data_ptr(), t.shape[0], t.shape[1], code, seed, row0, int(cvm_cols),
+        rc = _synth_lib().synth_fill_table(t.data_ptr(), t.shape[0], t.shape[1], code, seed, row0, row_stride,
+                                           int(cvm_cols),
                                            torch.cuda.current_stream(t.device).cuda_stream)
     if rc != 0:
         raise RuntimeError(f"synth_fill_table failed: cudaError {rc}")

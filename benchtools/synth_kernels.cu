@@ -43,29 +43,30 @@ template <> __device__ inline __nv_bfloat16 cast_to<__nv_bfloat16>(float v) { re
 
 template <typename T>
 __global__ void fill_table_kernel(T* __restrict__ t, long long rows, int dim, uint64_t seed, long long row0,
-                                  int cvm_cols) {
+                                  long long row_stride, int cvm_cols) {
   const long long n = rows * dim;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
     const long long r = i / dim;
     const int c = static_cast<int>(i - r * dim);
-    t[i] = cast_to<T>(table_value(seed, static_cast<uint64_t>(row0 + r), c, cvm_cols));
+    t[i] = cast_to<T>(table_value(seed, static_cast<uint64_t>(row0 + r * row_stride), c, cvm_cols));
   }
 }
 
 }  // namespace
 
-// dtype: 0 f32, 1 f16, 2 bf16.  Rows [row0, row0+rows) of the logical table are written
-// to t[0 .. rows*dim).  Returns a cudaError_t.
+// dtype: 0 f32, 1 f16, 2 bf16.  Logical rows row0, row0 + row_stride, ... (rows of them) are
+// written to t[0 .. rows*dim) -- row_stride > 1 fills one shard of a row-sharded table.
+// Returns a cudaError_t.
 extern "C" int synth_fill_table(void* t, long long rows, int dim, int dtype, unsigned long long seed,
-                                long long row0, int cvm_cols, void* stream) {
+                                long long row0, long long row_stride, int cvm_cols, void* stream) {
   auto st = static_cast<cudaStream_t>(stream);
   const int threads = 256;
   const int blocks = 148 * 16;
   switch (dtype) {
-    case 0: fill_table_kernel<float><<<blocks, threads, 0, st>>>(static_cast<float*>(t), rows, dim, seed, row0, cvm_cols); break;
-    case 1: fill_table_kernel<__half><<<blocks, threads, 0, st>>>(static_cast<__half*>(t), rows, dim, seed, row0, cvm_cols); break;
-    case 2: fill_table_kernel<__nv_bfloat16><<<blocks, threads, 0, st>>>(static_cast<__nv_bfloat16*>(t), rows, dim, seed, row0, cvm_cols); break;
+    case 0: fill_table_kernel<float><<<blocks, threads, 0, st>>>(static_cast<float*>(t), rows, dim, seed, row0, row_stride, cvm_cols); break;
+    case 1: fill_table_kernel<__half><<<blocks, threads, 0, st>>>(static_cast<__half*>(t), rows, dim, seed, row0, row_stride, cvm_cols); break;
+    case 2: fill_table_kernel<__nv_bfloat16><<<blocks, threads, 0, st>>>(static_cast<__nv_bfloat16*>(t), rows, dim, seed, row0, row_stride, cvm_cols); break;
     default: return 1;
   }
   return static_cast<int>(cudaGetLastError());

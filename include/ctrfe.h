@@ -114,7 +114,19 @@ typedef struct ctrfe_fused_desc {
   int32_t scale_mode;     /* CTRFE_SCALE_* */
   int32_t init_mode;      /* CTRFE_INIT_* */
   int32_t lod_location;   /* CTRFE_LOD_* */
-  int32_t reserved;
+  int32_t n_shards;       /* 0: each slot reads its own `table`.  2 / 4 / 8: ROW-SHARDED table mode --
+                             every slot reads the one logical table whose row r lives on shard
+                             r % n_shards at local row r / n_shards (the HeterComm rule,
+                             framework/fleet/heter_ps/heter_comm_kernel.cu:85-93); slot.table is
+                             ignored and slot.table_rows is the LOGICAL row count */
+  const void* const* shard_tables; /* host array [n_shards] of device pointers valid on the calling
+                             GPU: its own shard and the peers' shards mapped over NVLink
+                             (ctrfe_shard_open).  Replaces c_embedding + c_allreduce_sum
+                             (operators/collective/c_embedding_op.cu:33-62,
+                             distributed/fleet/layers/mpu/mp_ops.py:547-575) and HeterComm's
+                             bucket / walk_to_dest / gather / walk_to_src pull
+                             (heter_comm_inl.h:1477-1607): rows are fetched by the pooling kernel
+                             itself with loads through the peer mapping, in sequence order */
 } ctrfe_fused_desc;
 
 /* ---- library ------------------------------------------------------------------------ */
@@ -176,6 +188,21 @@ int ctrfe_plan_num_kernels(const ctrfe_plan* plan);
  *     this point, ~0 when every id was in range, else (slot << 44 | position) of the first
  *     offender (the row was treated as zeros, as ctrfe_check_ids documents). */
 int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint64_t* bad_id_key_host);
+
+/* ---- row-sharded tables across the GPUs of one box ------------------------------------
+ * One process per GPU.  Each process allocates its shard with ctrfe_shard_alloc (plain
+ * cudaMalloc memory, so that it can be exported), exports a 64-byte handle, exchanges the
+ * handles with its peers by any means (torch.distributed all_gather in this repo), and maps
+ * every peer's shard with ctrfe_shard_open.  The mapped pointers go into
+ * ctrfe_fused_desc.shard_tables.  Stands where the reference's HeterComm keeps one
+ * HashTable per GPU and walks keys/values between them with cudaMemcpyPeerAsync
+ * (framework/fleet/heter_ps/heter_comm_inl.h:193,273-428). */
+#define CTRFE_IPC_HANDLE_BYTES 64
+int ctrfe_shard_alloc(int device, uint64_t bytes, void** ptr);
+int ctrfe_shard_free(int device, void* ptr);
+int ctrfe_shard_export(void* ptr, unsigned char handle[CTRFE_IPC_HANDLE_BYTES]);
+int ctrfe_shard_open(int device, const unsigned char handle[CTRFE_IPC_HANDLE_BYTES], void** ptr);
+int ctrfe_shard_close(int device, void* ptr);
 
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 

@@ -31,7 +31,8 @@ class FusedDesc(C.Structure):
     _fields_ = [("n_slots", C.c_int32), ("dtype", C.c_int32), ("slots", C.POINTER(Slot)),
                 ("dim", C.c_int64), ("padding_idx", C.c_int64), ("pad_value", C.c_float),
                 ("cvm_mode", C.c_int32), ("cvm_offset", C.c_int32), ("scale_mode", C.c_int32),
-                ("init_mode", C.c_int32), ("lod_location", C.c_int32), ("reserved", C.c_int32)]
+                ("init_mode", C.c_int32), ("lod_location", C.c_int32), ("n_shards", C.c_int32),
+                ("shard_tables", C.POINTER(C.c_void_p))]
 
 
 class CtrfeError(RuntimeError):
@@ -57,6 +58,7 @@ EXPORTS = [
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static",
+    "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
 ]
 
 
@@ -83,6 +85,11 @@ def lib():
         L.ctrfe_sequence_pool.argtypes = [vp, vp, i32, i64, vp, i64, i32, C.c_float, vp, vp, vp]
         L.ctrfe_cvm.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp]
         L.ctrfe_fused_forward_static.argtypes = [C.POINTER(FusedDesc), vp, vp]
+        L.ctrfe_shard_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp)]
+        L.ctrfe_shard_free.argtypes = [C.c_int, vp]
+        L.ctrfe_shard_export.argtypes = [vp, C.c_char_p]
+        L.ctrfe_shard_open.argtypes = [C.c_int, C.c_char_p, C.POINTER(vp)]
+        L.ctrfe_shard_close.argtypes = [C.c_int, vp]
         _lib = L
     return _lib
 

@@ -160,11 +160,22 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   const long long row_bytes = d->dim * es;
   const int d_out = static_cast<int>(d->dim) - (d->cvm_mode == CTRFE_CVM_STRIP ? d->cvm_offset : 0);
   bool v = (row_bytes % 16) == 0;
+  const bool sharded = d->n_shards != 0;
+  if (sharded) {
+    if (d->n_shards != 2 && d->n_shards != 4 && d->n_shards != 8)
+      return fail(CTRFE_ERR_ARG, "fused: n_shards must be 2, 4 or 8 (got %d)", d->n_shards);
+    if (!d->shard_tables) return fail(CTRFE_ERR_ARG, "fused: n_shards set but shard_tables is null");
+    if (!v) return fail(CTRFE_ERR_UNSUPPORTED, "fused: the sharded table mode needs rows that are a multiple of 16 bytes");
+    for (int g = 0; g < d->n_shards; ++g)
+      if (!d->shard_tables[g] || reinterpret_cast<uintptr_t>(d->shard_tables[g]) % 16 != 0)
+        return fail(CTRFE_ERR_ARG, "fused: shard_tables[%d] is null or not 16-byte aligned", g);
+  }
   size_t lb = 0;
   for (int s = 0; s < d->n_slots; ++s) {
     const ctrfe_slot& sl = d->slots[s];
+    if (sharded && !sl.ids) return fail(CTRFE_ERR_ARG, "slot %d: the sharded table mode needs ids", s);
     if (sl.n_seg < 0 || sl.n_seg > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "slot %d: n_seg %lld outside [0, 2^31)", s, (long long)sl.n_seg);
-    if (sl.n_seg > 0 && (!sl.table || !sl.lod || !sl.out))
+    if (sl.n_seg > 0 && ((!sl.table && !sharded) || !sl.lod || !sl.out))
       return fail(CTRFE_ERR_ARG, "slot %d: null table / lod / out", s);
     if (sl.pooltype < CTRFE_POOL_AVERAGE || sl.pooltype > CTRFE_POOL_MAX)
       return fail(CTRFE_ERR_ARG,
@@ -176,7 +187,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
                                        (long long)sl.out_ld, d_out);
     if (sl.table_rows < 0 || sl.table_rows >= 0xfffffffeLL)
       return fail(CTRFE_ERR_UNSUPPORTED, "slot %d: table_rows %lld outside [0, 2^32 - 2)", s, (long long)sl.table_rows);
-    if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
+    if (!sharded && reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
   // lane chunk: 32 bytes (one 256-bit load) for fp32 rows that allow it, else 16, else one element
@@ -184,7 +195,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   // 256-bit lanes halve the instruction count but also the warps in flight; on B200 the
   // 128-bit mapping measured faster for short sequences (profiles/), so 32-byte lanes are opt-in.
   const char* use256 = getenv("CTRFE_LDG256");
-  if (v && d->dtype == CTRFE_F32 && row_bytes % 32 == 0 && use256 && use256[0] == '1') {
+  if (v && !sharded && d->dtype == CTRFE_F32 && row_bytes % 32 == 0 && use256 && use256[0] == '1') {
     cb = 32;
     for (int s = 0; s < d->n_slots; ++s)
       if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
@@ -229,6 +240,12 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       k.init_mode = d->init_mode;
       k.pad_value = d->pad_value;
       k.n_slots = 0;
+      if (sharded) {
+        k.n_shards = d->n_shards;
+        k.shard_shift = d->n_shards == 2 ? 1 : (d->n_shards == 4 ? 2 : 3);
+        for (int g = 0; g < ctrfe::kMaxShards; ++g)
+          k.shard_tables[g] = static_cast<const char*>(d->shard_tables[g % d->n_shards]);
+      }
     }
     ctrfe::KParams& k = plan->chunks[c];
     ctrfe::SlotK& o = k.slots[k.n_slots];
@@ -294,31 +311,37 @@ int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_i
   return CTRFE_OK;
 }
 
-template <int DT, int MODE, int CB>
+template <int DT, int MODE, int CB, bool SH>
 void launch_fused_tm(bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
   using namespace ctrfe;
-  if (!vect) { fused_pool_kernel<DT, false, 5, MODE, 16><<<grid, kThreads, 0, st>>>(p); return; }
+  if (!vect) { fused_pool_kernel<DT, false, 5, MODE, 16, false><<<grid, kThreads, 0, st>>>(p); return; }
   switch (gs) {
-    case 0: fused_pool_kernel<DT, true, 0, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
-    case 1: fused_pool_kernel<DT, true, 1, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
-    case 2: fused_pool_kernel<DT, true, 2, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
-    case 3: fused_pool_kernel<DT, true, 3, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
-    case 4: fused_pool_kernel<DT, true, 4, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
-    default: fused_pool_kernel<DT, true, 5, MODE, CB><<<grid, kThreads, 0, st>>>(p); break;
+    case 0: fused_pool_kernel<DT, true, 0, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 1: fused_pool_kernel<DT, true, 1, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 2: fused_pool_kernel<DT, true, 2, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 3: fused_pool_kernel<DT, true, 3, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 4: fused_pool_kernel<DT, true, 4, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
+    default: fused_pool_kernel<DT, true, 5, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
   }
 }
 
 template <int DT>
 void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  const bool sel = mode == ctrfe::kModeSelect;
+  if (p.n_shards > 0) {  // row-sharded table: 128-bit lanes, rows fetched through peer mappings
+    if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, true>(vect, gs, grid, st, p);
+    else launch_fused_tm<DT, ctrfe::kModeAdd, 16, true>(vect, gs, grid, st, p);
+    return;
+  }
   if constexpr (DT == CTRFE_F32) {
     if (cb == 32) {  // 256-bit lanes exist for fp32 rows only
-      if (mode == ctrfe::kModeSelect) launch_fused_tm<DT, ctrfe::kModeSelect, 32>(vect, gs, grid, st, p);
-      else launch_fused_tm<DT, ctrfe::kModeAdd, 32>(vect, gs, grid, st, p);
+      if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 32, false>(vect, gs, grid, st, p);
+      else launch_fused_tm<DT, ctrfe::kModeAdd, 32, false>(vect, gs, grid, st, p);
       return;
     }
   }
-  if (mode == ctrfe::kModeSelect) launch_fused_tm<DT, ctrfe::kModeSelect, 16>(vect, gs, grid, st, p);
-  else launch_fused_tm<DT, ctrfe::kModeAdd, 16>(vect, gs, grid, st, p);
+  if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, false>(vect, gs, grid, st, p);
+  else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p);
 }
 
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
@@ -609,6 +632,49 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
 }
 
 
+// ---- row-sharded tables: exportable shard memory and peer mappings ----------------------
+int ctrfe_shard_alloc(int device, uint64_t bytes, void** ptr) {
+  if (!ptr || bytes == 0) return fail(CTRFE_ERR_ARG, "shard_alloc: null ptr / zero bytes");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CTRFE_ERR_CUDA, "shard_alloc: cannot select device %d", device);
+  CU(cudaMalloc(ptr, bytes));  // plain cudaMalloc: cudaIpcGetMemHandle needs it (no pooled memory)
+  return CTRFE_OK;
+}
+
+int ctrfe_shard_free(int device, void* ptr) {
+  if (!ptr) return CTRFE_OK;
+  DeviceGuard g(device);
+  CU(cudaFree(ptr));
+  return CTRFE_OK;
+}
+
+int ctrfe_shard_export(void* ptr, unsigned char handle[CTRFE_IPC_HANDLE_BYTES]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == CTRFE_IPC_HANDLE_BYTES, "IPC handle size");
+  if (!ptr || !handle) return fail(CTRFE_ERR_ARG, "shard_export: null argument");
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle, &h, sizeof(h));
+  return CTRFE_OK;
+}
+
+int ctrfe_shard_open(int device, const unsigned char handle[CTRFE_IPC_HANDLE_BYTES], void** ptr) {
+  if (!ptr || !handle) return fail(CTRFE_ERR_ARG, "shard_open: null argument");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CTRFE_ERR_CUDA, "shard_open: cannot select device %d", device);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  // maps the peer's allocation into this process and enables peer access over NVLink
+  CU(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return CTRFE_OK;
+}
+
+int ctrfe_shard_close(int device, void* ptr) {
+  if (!ptr) return CTRFE_OK;
+  DeviceGuard g(device);
+  CU(cudaIpcCloseMemHandle(ptr));
+  return CTRFE_OK;
+}
+
 // =====================================================================================
 // ctrfe_fused_forward_static: the fused front end for callers that must not allocate.
 //
@@ -674,6 +740,7 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
   if (d->scale_mode != CTRFE_SCALE_DIVIDE && d->scale_mode != CTRFE_SCALE_RECIPROCAL) return fail(CTRFE_ERR_ARG, "static: bad scale_mode");
   if (d->init_mode < CTRFE_INIT_ZERO || d->init_mode > CTRFE_INIT_FIRST_ROW) return fail(CTRFE_ERR_ARG, "static: bad init_mode");
   if (d->lod_location != CTRFE_LOD_HOST) return fail(CTRFE_ERR_ARG, "static: LoD offsets must be passed from host memory");
+  if (d->n_shards != 0) return fail(CTRFE_ERR_UNSUPPORTED, "static: the sharded table mode is not available here");
 
   const int es = elem_size(d->dtype);
   const long long row_bytes = d->dim * es;

@@ -39,7 +39,8 @@ namespace ctrfe {
 
 constexpr int kThreads = 256;          // threads per CTA of the pooling kernel
 constexpr int kUnroll = 4;             // row loads in flight per lane
-constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters
+constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters (block <= 4 KB)
+constexpr int kMaxShards = 8;           // GPUs of one NVSwitch box
 constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequence: no load, no add
 constexpr uint32_t kZero = 0xfffffffeu;  // padding_idx / out-of-range id: contributes a zero row
 
@@ -71,8 +72,15 @@ struct KParams {
   int reserved;
   float pad_value;
   int n_slots;
+  // row-sharded table mode: row r of the logical table lives on shard r % n_shards at local
+  // row r / n_shards; shard_tables[] are device pointers valid on THIS GPU (local memory or
+  // NVLink peer mappings obtained through CUDA IPC).  n_shards is a power of two, 0 = off.
+  int shard_shift;
+  int n_shards;
+  const char* shard_tables[kMaxShards];
   SlotK slots[kMaxSlotsPerLaunch];
 };
+static_assert(sizeof(KParams) <= 4096, "kernel parameter block must stay within 4 KB");
 
 __device__ __forceinline__ uint4 ldg128(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
@@ -163,10 +171,17 @@ __device__ __forceinline__ double cvm_log1(float x) { return log(static_cast<dou
 // MODE: kModeAdd for SUM / AVERAGE / SQRT slots, kModeSelect for MAX / LAST / FIRST slots
 // (the host puts slots of different modes into different launches).
 // ---------------------------------------------------------------------------------------
-template <int DT, bool VECT, int GS, int MODE, int CB>
+template <int DT, bool VECT, int GS, int MODE, int CB, bool SHARDED = false>
 __global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
 fused_pool_kernel(const __grid_constant__ KParams kp) {
   using L = Lane<DT, VECT, CB>;
+  // sharded mode: the shard base pointers sit in shared memory (the owner differs per lane,
+  // and a lane-varying index into the parameter bank would serialise)
+  __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
+  if constexpr (SHARDED) {
+    if (threadIdx.x < kMaxShards) s_shards[threadIdx.x] = reinterpret_cast<unsigned long long>(kp.shard_tables[threadIdx.x]);
+    __syncthreads();
+  }
   constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
@@ -220,6 +235,19 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
   const uint32_t pad_lo = static_cast<uint32_t>(kp.padding_idx);
   const uint32_t pad_hi = static_cast<uint32_t>(static_cast<unsigned long long>(kp.padding_idx) >> 32);
   CTRFE_KEEP64(lane_base);
+  const unsigned lane_off = static_cast<unsigned>(col0 * ES);
+  const unsigned shard_mask = SHARDED ? static_cast<unsigned>(kp.n_shards - 1) : 0u;
+  const int shard_shift = SHARDED ? kp.shard_shift : 0;
+  // address of this lane's chunk of table row `rid`: local table, or -- sharded -- the owner
+  // shard's memory (rid % n_shards), reached with ordinary loads through the NVLink mapping
+  auto row_ptr = [&](uint32_t rid) -> const char* {
+    if constexpr (SHARDED) {
+      const unsigned long long base = s_shards[rid & shard_mask];
+      return reinterpret_cast<const char*>(base + static_cast<unsigned long long>(rid >> shard_shift) * row_bytes + lane_off);
+    } else {
+      return reinterpret_cast<const char*>(lane_base + static_cast<unsigned long long>(rid) * row_bytes);
+    }
+  };
   CTRFE_KEEP32(table_rows);
   CTRFE_KEEP32(row_bytes);
   CTRFE_KEEP32(id_kind);
@@ -283,7 +311,7 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
 #pragma unroll
         for (int r = 0; r < RW; ++r) raw[u][r] = 0u;
         if (rid < kZero && col_ok)
-          L::load(reinterpret_cast<const char*>(lane_base + static_cast<unsigned long long>(rid) * row_bytes), raw[u]);
+          L::load(row_ptr(rid), raw[u]);
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {

@@ -242,11 +242,23 @@ class FusedPlan:
             pass
 
 
+class _TableRef:
+    """What a slot descriptor needs from a table: a base pointer and a row count."""
+
+    def __init__(self, ptr, rows):
+        self._ptr, self.shape = ptr, (rows,)
+
+    def data_ptr(self):
+        return self._ptr
+
+
 def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_value, padding_idx, cvm_mode,
-                cvm_offset, scale_mode, init_mode, lod_on_device):
+                cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None):
     S = len(lods)
     slots = (B.Slot * S)()
     keep = []
+    if sharded is not None:  # slot.table is ignored; table_rows is the LOGICAL row count
+        tables = [_TableRef(None, sharded.n_rows)] * S
     for s in range(S):
         t = tables[s]
         if lod_on_device:
@@ -262,6 +274,10 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
                           _IDT[i.dtype] if i is not None else B.I64)
     desc = B.FusedDesc(S, dtype, slots, dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset, scale_mode,
                        init_mode, B.LOD_DEVICE if lod_on_device else B.LOD_HOST, 0)
+    if sharded is not None:
+        desc.n_shards = sharded.n_shards
+        desc.shard_tables = C.cast(sharded.shard_ptrs, C.POINTER(C.c_void_p))
+        keep.append(sharded)
     keep.append(slots)
     return desc, keep
 
@@ -273,7 +289,9 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
                               out: Optional[torch.Tensor] = None, ctx: Optional[Context] = None):
     """lookup_table_v2 -> sequence_pool -> cvm for every slot of a CTR batch in one launch.
 
-    W         one table [N, D] shared by all slots, or a list with one table per slot
+    W         one table [N, D] shared by all slots, or a list with one table per slot, or a
+              shard.ShardedTable: one logical table row-sharded over the GPUs of the box, whose
+              remote rows the kernel fetches itself over NVLink (results are bit-identical)
     Ids       per slot: 1-D int64/int32 ids, LoD-packed
     lods      per slot: offsets of the last LoD level -- a host sequence / numpy array, or a
               CUDA uint64-as-int64 tensor when the offsets are already on the device
@@ -285,15 +303,22 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
     Returns a list of [B_s, D_out] tensors, or the [B, S*D_out] tensor when concat=True;
     with plan_only=True returns a FusedPlan instead (nothing launched yet).
     """
+    from .shard import LocalShards, ShardedTable
     S = len(Ids)
-    tables = _as_list(W, S)
-    if len(tables) != S:
-        raise InvalidArgument("W must be one table or one per slot")
+    sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
     pools = _as_list(pooltype, S)
     for p in pools:
         if p not in B.POOLTYPES:
             raise InvalidArgument(f"unsupported pooling pooltype: {p}")
-    t0 = tables[0]
+    if sharded is not None:
+        # W is one logical table row-sharded over the GPUs of the box (shard.py)
+        tables = []
+        t0 = torch.empty((0, sharded.dim), dtype=sharded.dtype, device=sharded.device)
+    else:
+        tables = _as_list(W, S)
+        if len(tables) != S:
+            raise InvalidArgument("W must be one table or one per slot")
+        t0 = tables[0]
     _need_cuda(t0, "W")
     if t0.dtype not in (torch.float32, torch.float16, torch.bfloat16):
         raise Unimplemented(f"dtype {t0.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
@@ -323,7 +348,7 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
         ld = d_out
     desc, keep = _build_desc(tables, ids_c, lods, pools, outs, ld, dim=dim, dtype=_DT[t0.dtype],
                              pad_value=pad_value, padding_idx=padding_idx, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
-                             scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device)
+                             scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device, sharded=sharded)
     result = out if concat else outs
     if plan_only:
         h = C.c_void_p()
@@ -444,12 +469,21 @@ class HostFrontEnd:
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
                  padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, mode: str = "zero_copy",
                  concat: bool = False, ctx: Optional[Context] = None):
-        tables = _as_list(W, n_slots)
-        t0 = tables[0]
-        _need_cuda(t0, "W")
+        from .shard import LocalShards, ShardedTable
+        self.sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
+        if self.sharded is not None:  # one logical table row-sharded over the GPUs of the box
+            t0 = torch.empty((0, W.dim), dtype=W.dtype, device=W.device)
+            tables = [_TableRef(None, W.n_rows)] * n_slots
+            self._dev = W.device
+        else:
+            tables = _as_list(W, n_slots)
+            t0 = tables[0]
+            _need_cuda(t0, "W")
+            self._dev = t0.device
         if mode not in ("zero_copy", "copy"):
             raise InvalidArgument("mode must be 'zero_copy' or 'copy'")
         self.mode, self.concat = mode, concat
+        self._dtype = t0.dtype
         self.tables, self.S, self.B = tables, n_slots, batch
         self.pools = _as_list(pooltype, n_slots)
         self.kw = dict(pad_value=pad_value, padding_idx=padding_idx, use_cvm=use_cvm, cvm_offset=cvm_offset)
@@ -486,9 +520,12 @@ class HostFrontEnd:
             slots[s] = B.Slot(t.data_ptr(), t.shape[0], ids_host[s].data_ptr(), lods_host[s].data_ptr(),
                               lods_host[s].numel() - 1, outs[s].data_ptr(), ld, B.POOLTYPES[self.pools[s]],
                               _IDT[ids_host[s].dtype])
-        desc = B.FusedDesc(S, _DT[self.tables[0].dtype], slots, self.dim, int(self.kw["padding_idx"]),
+        desc = B.FusedDesc(S, _DT[self._dtype], slots, self.dim, int(self.kw["padding_idx"]),
                            float(self.kw["pad_value"]), cvm_mode, self.kw["cvm_offset"], B.SCALE_DIVIDE,
                            B.INIT_ZERO, B.LOD_DEVICE, 0)
+        if self.sharded is not None:
+            desc.n_shards = self.sharded.n_shards
+            desc.shard_tables = C.cast(self.sharded.shard_ptrs, C.POINTER(C.c_void_p))
         h2d = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.numel() * 8 for l in lods_host)
         return desc, slots, h2d
 
@@ -499,7 +536,7 @@ class HostFrontEnd:
             raise InvalidArgument("bind() needs mode='zero_copy'")
         desc, slots, h2d = self._desc(ids_host, lods_host)
         h = C.c_void_p()
-        stream = torch.cuda.current_stream(self.tables[0].device)
+        stream = torch.cuda.current_stream(self._dev)
         B.check(B.lib().ctrfe_plan_create(self.ctx.handle, C.byref(desc), stream.cuda_stream, C.byref(h)))
         return BoundHostCall(self, FusedPlan(self.ctx, h, None, (ids_host, lods_host, slots)), h2d)
 
@@ -507,7 +544,7 @@ class HostFrontEnd:
         """ids_host: pinned int64/int32 CPU tensors, one per slot.  lods_host: per slot the
         offsets -- numpy uint64 arrays (mode="copy") or pinned int64 CPU tensors (zero_copy)."""
         S = self.S
-        stream = torch.cuda.current_stream(self.tables[0].device)
+        stream = torch.cuda.current_stream(self._dev)
         if self.mode == "copy":
             ids_dev = []
             for s in range(S):
@@ -516,11 +553,11 @@ class HostFrontEnd:
                 ids_dev.append(d)
             outs, ld = self._out_views(self.dev_out)
             desc, keep = _build_desc(self.tables, ids_dev, lods_host, self.pools, outs, ld, dim=self.dim,
-                                     dtype=_DT[self.tables[0].dtype], pad_value=self.kw["pad_value"],
+                                     dtype=_DT[self._dtype], pad_value=self.kw["pad_value"],
                                      padding_idx=self.kw["padding_idx"],
                                      cvm_mode=B.CVM_NONE if self.kw["use_cvm"] is None else (B.CVM_USE if self.kw["use_cvm"] else B.CVM_STRIP),
                                      cvm_offset=self.kw["cvm_offset"], scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_ZERO,
-                                     lod_on_device=False)
+                                     lod_on_device=False, sharded=self.sharded)
             B.check(B.lib().ctrfe_fused_forward(self.ctx.handle, C.byref(desc), stream.cuda_stream))
             self.host_out.copy_(self.dev_out, non_blocking=True)
             self.h2d_bytes = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.size * 8 for l in lods_host)
@@ -539,7 +576,7 @@ class BoundHostCall:
 
     def __init__(self, fe: HostFrontEnd, plan: FusedPlan, h2d_bytes: int):
         self.fe, self.plan, self.h2d_bytes, self.d2h_bytes = fe, plan, h2d_bytes, fe.d2h_bytes
-        self._stream = torch.cuda.current_stream(fe.tables[0].device)
+        self._stream = torch.cuda.current_stream(fe._dev)
 
     def run(self):
         self.plan.launch()
