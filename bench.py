@@ -260,6 +260,9 @@ def run_ours(args):
     from paddle_infer_b200 import ops
 
     cfg = synth.configs()[args.workload]
+    if args.rows:  # diagnostic override: same workload shape on a smaller / larger table
+        cfg.rows = args.rows
+        cfg.name += f"[rows={args.rows}]"
     S, D = cfg.slots, cfg.dim
     tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
     # cfg4 on N > 1 GPUs: ONE logical table row-sharded over the ranks (row r on rank r % N),
@@ -272,7 +275,7 @@ def run_ours(args):
     tables = []
     if sharded:
         from paddle_infer_b200 import shard as shard_mod
-        shard_table = shard_mod.ShardedTable(cfg.rows, D, tdt)
+        shard_table = shard_mod.ShardedTable(cfg.rows, D, tdt, sharing=os.environ.get("CTRFE_SHARING", "vmm"))
         synth.fill_table(shard_table.local, cfg.seed, row0=rank, row_stride=world, cvm_cols=cfg.use_cvm is not None)
         torch.cuda.synchronize()
         dist.barrier()
@@ -411,12 +414,15 @@ def run_ours(args):
                          "HostFrontEnd copy: H2D ids + LoD upload, launch, D2H output")},
     }
     if sharded:
-        # bytes this rank pulls over NVLink per launch: every row whose owner is another GPU
+        # rows whose owner is another GPU: the bytes the kernel asks the NVLink mappings for per
+        # launch (an upper bound on link traffic -- peer rows are cached in L1, and the Zipf head
+        # repeats within a launch)
         nv_bytes = float(np.mean(k_used)) * (world - 1) / world * D * es
         nv_gbs = nv_bytes / (kern_ms * 1e-3) / 1e9
-        line["nvlink"] = {"bytes_in_per_launch_per_gpu": nv_bytes, "achieved": nv_gbs, "unit": "GB/s",
-                          "peak": 770.0, "peak_source": "B200_PROFILING.md measured peer copy, per direction per GPU",
-                          "frac": nv_gbs / 770.0}
+        line["nvlink"] = {"remote_row_bytes_per_launch_per_gpu": nv_bytes, "requested_gbs": nv_gbs,
+                          "link_peak_gbs": 770.0,
+                          "peak_source": "B200_PROFILING.md measured peer copy, per direction per GPU",
+                          "note": "requested bytes / time; above the link peak means L1 hits on repeated hot rows"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tabs, hb4, rows = host_table_and_batches(cfg, synth, 4, torch, tables)
         line["cpu_baseline"] = cpu_leg(cfg, tabs, hb4, budget_s=args.cpu_budget)
@@ -444,6 +450,7 @@ def main():
     ap.add_argument("--e2e-mode", default="zero_copy", choices=["zero_copy", "copy"])
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rows", type=int, default=0, help="diagnostic: override the table rows of the workload")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -203,6 +203,13 @@ int ctrfe_shard_free(int device, void* ptr);
 int ctrfe_shard_export(void* ptr, unsigned char handle[CTRFE_IPC_HANDLE_BYTES]);
 int ctrfe_shard_open(int device, const unsigned char handle[CTRFE_IPC_HANDLE_BYTES], void** ptr);
 int ctrfe_shard_close(int device, void* ptr);
+/* Preferred variant of the above: the shard is allocated through the CUDA virtual-memory-
+ * management API at 2 MiB granularity and shared as a POSIX file descriptor (pass it to the
+ * peers over a Unix socket); the importer maps it with large pages, which random row reads
+ * over a multi-GB peer shard need (legacy IPC mappings measured 50x slower there). */
+int ctrfe_shard_alloc_fd(int device, uint64_t bytes, void** ptr, int* fd, uint64_t* mapped_bytes);
+int ctrfe_shard_open_fd(int device, int fd, uint64_t mapped_bytes, void** ptr);
+int ctrfe_shard_unmap(int device, void* ptr, uint64_t mapped_bytes);
 
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 

@@ -59,6 +59,7 @@ EXPORTS = [
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
+    "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap",
 ]
 
 
@@ -90,6 +91,9 @@ def lib():
         L.ctrfe_shard_export.argtypes = [vp, C.c_char_p]
         L.ctrfe_shard_open.argtypes = [C.c_int, C.c_char_p, C.POINTER(vp)]
         L.ctrfe_shard_close.argtypes = [C.c_int, vp]
+        L.ctrfe_shard_alloc_fd.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
+        L.ctrfe_shard_open_fd.argtypes = [C.c_int, C.c_int, C.c_uint64, C.POINTER(vp)]
+        L.ctrfe_shard_unmap.argtypes = [C.c_int, vp, C.c_uint64]
         _lib = L
     return _lib
 

@@ -6,12 +6,14 @@ Placement rule: row r of the logical [N, D] table lives on shard r % G at local 
 contiguous ranges (operators/collective/c_embedding_op.cu:48-49) because it spreads the Zipf
 head evenly.
 
-One process per GPU.  Each process allocates its shard with plain cudaMalloc (exportable),
-publishes a CUDA IPC handle, and maps every peer's shard over NVLink; the fused pooling
-kernel then fetches remote rows itself with ordinary loads through those mappings, in
-sequence order, so sharded results are bit-identical to the single-table results.  There
-is no bucketing, no all-to-all and no host synchronisation on the data path; torch.distributed
-only carries the 64-byte handles at set-up (any backend: gloo works).
+One process per GPU.  Each process allocates its shard through the CUDA virtual-memory-
+management API (2 MiB pages), hands a file descriptor for it to its peers, and maps every
+peer's shard over NVLink; the fused pooling kernel then fetches remote rows itself with
+ordinary loads through those mappings, in sequence order, so sharded results are
+bit-identical to the single-table results.  There is no bucketing, no all-to-all and no host
+synchronisation on the data path; torch.distributed only carries set-up metadata (any
+backend: gloo works).  Large pages matter: with legacy cudaIpc mappings random row reads over
+a 12.8 GB peer shard ran 50x slower on B200 (page walks), see profiles/README.md.
 """
 from __future__ import annotations
 
@@ -63,6 +65,49 @@ def exchange_handles(handle: bytes, group=None) -> List[bytes]:
     return [bytes(h) for h in out]
 
 
+def exchange_fds(fd: int, group=None, tag: str = "ctrfe") -> List[int]:
+    """Give every rank of the (single-node) group a duplicate of every other rank's file
+    descriptor: each rank serves its fd on a Unix socket, peers fetch it with SCM_RIGHTS.
+    Returns the fds in rank order (this rank's own fd at its index)."""
+    import os
+    import socket
+    import tempfile
+    import threading
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    base = os.path.join(tempfile.gettempdir(), f"{tag}_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}")
+    path = f"{base}_{rank}.sock"
+    if os.path.exists(path):
+        os.unlink(path)
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(path)
+    srv.listen(world)
+
+    def serve():
+        for _ in range(world - 1):
+            conn, _ = srv.accept()
+            with conn:
+                socket.send_fds(conn, [b"f"], [fd])
+
+    t = threading.Thread(target=serve, daemon=True)
+    t.start()
+    dist.barrier(group)  # every socket is listening
+    out = []
+    for r in range(world):
+        if r == rank:
+            out.append(fd)
+            continue
+        with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+            c.connect(f"{base}_{r}.sock")
+            _, fds, _, _ = socket.recv_fds(c, 1, 1)
+            out.append(fds[0])
+    t.join(60)
+    dist.barrier(group)
+    srv.close()
+    os.unlink(path)
+    return out
+
+
 class _RawCudaBuffer:
     """Adapter so torch can view memory this library allocated (no copy)."""
 
@@ -72,42 +117,74 @@ class _RawCudaBuffer:
 
 
 class ShardedTable:
-    """This rank's view of a logical [n_rows, dim] table sharded over the process group."""
+    """This rank's view of a logical [n_rows, dim] table sharded over the process group.
 
-    def __init__(self, n_rows: int, dim: int, dtype, group=None, device=None):
+    sharing="vmm" (default): shards are cuMemCreate allocations at 2 MiB granularity, passed to
+    the peers as POSIX file descriptors -- peer mappings then use large pages, which random row
+    reads over multi-GB shards need.  sharing="ipc": legacy cudaIpc handles (small-page peer
+    mappings; fine for shards well under a GB)."""
+
+    def __init__(self, n_rows: int, dim: int, dtype, group=None, device=None, sharing: str = "vmm"):
+        import os
         import torch
         import torch.distributed as dist
         self.group = group
         self.rank = dist.get_rank(group)
         self.n_shards = dist.get_world_size(group)
         check_n_shards(self.n_shards)
+        if sharing not in ("vmm", "ipc"):
+            raise ValueError("sharing must be 'vmm' or 'ipc'")
+        self.sharing = sharing
         self.n_rows, self.dim, self.dtype = int(n_rows), int(dim), dtype
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.local_rows = shard_num_rows(self.n_rows, self.n_shards, self.rank)
         es = torch.empty(0, dtype=dtype).element_size()
         self.nbytes = max(self.local_rows, 1) * self.dim * es
+        L = B.lib()
         p = C.c_void_p()
-        B.check(B.lib().ctrfe_shard_alloc(self.device.index, self.nbytes, C.byref(p)))
-        self._own = p
+        self._peer_ptrs: List[Optional[C.c_void_p]] = []
+        self._peer_sizes: List[int] = []
+        ptrs = []
+        if sharing == "vmm":
+            fd, mapped = C.c_int(-1), C.c_uint64(0)
+            B.check(L.ctrfe_shard_alloc_fd(self.device.index, self.nbytes, C.byref(p), C.byref(fd), C.byref(mapped)))
+            self._own, self._own_mapped = p, mapped.value
+            sizes: List[Optional[int]] = [None] * self.n_shards
+            dist.all_gather_object(sizes, int(mapped.value), group=group)
+            fds = exchange_fds(fd.value, group)
+            for g in range(self.n_shards):
+                if g == self.rank:
+                    self._peer_ptrs.append(None)
+                    self._peer_sizes.append(0)
+                    ptrs.append(self._own.value)
+                else:
+                    q = C.c_void_p()
+                    B.check(L.ctrfe_shard_open_fd(self.device.index, fds[g], sizes[g], C.byref(q)))
+                    os.close(fds[g])
+                    self._peer_ptrs.append(q)
+                    self._peer_sizes.append(sizes[g])
+                    ptrs.append(q.value)
+            os.close(fd.value)
+        else:
+            B.check(L.ctrfe_shard_alloc(self.device.index, self.nbytes, C.byref(p)))
+            self._own = p
+            hb = C.create_string_buffer(HANDLE_BYTES)
+            B.check(L.ctrfe_shard_export(self._own, hb))
+            handles = exchange_handles(hb.raw, group)
+            for g in range(self.n_shards):
+                if g == self.rank:
+                    self._peer_ptrs.append(None)
+                    ptrs.append(self._own.value)
+                else:
+                    q = C.c_void_p()
+                    B.check(L.ctrfe_shard_open(self.device.index, handles[g], C.byref(q)))
+                    self._peer_ptrs.append(q)
+                    ptrs.append(q.value)
         typestr = {torch.float32: "<f4", torch.float16: "<f2", torch.bfloat16: "<u2"}[dtype]
-        t = torch.as_tensor(_RawCudaBuffer(p.value, (max(self.local_rows, 1), self.dim), typestr), device=self.device)
+        t = torch.as_tensor(_RawCudaBuffer(self._own.value, (max(self.local_rows, 1), self.dim), typestr),
+                            device=self.device)
         self.local = t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
         self.local = self.local[: self.local_rows]
-        # publish / map
-        hb = C.create_string_buffer(HANDLE_BYTES)
-        B.check(B.lib().ctrfe_shard_export(self._own, hb))
-        handles = exchange_handles(hb.raw, group)
-        self._peer_ptrs: List[Optional[C.c_void_p]] = []
-        ptrs = []
-        for g in range(self.n_shards):
-            if g == self.rank:
-                self._peer_ptrs.append(None)
-                ptrs.append(self._own.value)
-            else:
-                q = C.c_void_p()
-                B.check(B.lib().ctrfe_shard_open(self.device.index, handles[g], C.byref(q)))
-                self._peer_ptrs.append(q)
-                ptrs.append(q.value)
         self.shard_ptrs = (C.c_void_p * self.n_shards)(*ptrs)
         dist.barrier(group)
 
@@ -118,11 +195,19 @@ class ShardedTable:
             return
         torch.cuda.synchronize(self.device)
         dist.barrier(self.group)  # nobody unmaps or frees while a peer may still be reading
-        for q in self._peer_ptrs:
+        L = B.lib()
+        for g, q in enumerate(self._peer_ptrs):
             if q is not None:
-                B.lib().ctrfe_shard_close(self.device.index, q)
+                if self.sharing == "vmm":
+                    L.ctrfe_shard_unmap(self.device.index, q, self._peer_sizes[g])
+                else:
+                    L.ctrfe_shard_close(self.device.index, q)
         dist.barrier(self.group)
-        B.lib().ctrfe_shard_free(self.device.index, self._own)
+        self.local = None
+        if self.sharing == "vmm":
+            L.ctrfe_shard_unmap(self.device.index, self._own, self._own_mapped)
+        else:
+            L.ctrfe_shard_free(self.device.index, self._own)
         self._own = None
 
 

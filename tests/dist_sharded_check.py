@@ -31,7 +31,7 @@ def main():
     from paddle_infer_b200 import ops, shard
 
     N, D, seed, S, Bsz = 200_003, 32, 9, 6, 512
-    table = shard.ShardedTable(N, D, torch.float32)
+    table = shard.ShardedTable(N, D, torch.float32, sharing=os.environ.get("CTRFE_SHARING", "vmm"))
     assert table.local_rows == shard.shard_num_rows(N, world, rank)
     synth_rows = shard.global_rows_of_shard(N, world, rank)
     table.local.copy_(torch.from_numpy(synth.table_rows_numpy(seed, synth_rows, D, "f32")))
