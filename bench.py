@@ -42,6 +42,18 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def _random_row_ceiling(row_bytes):
+    """Measured ceiling for uniform-random row reads of this size (profiles/random_row_ceiling.json)."""
+    p = os.path.join(ROOT, "profiles", "random_row_ceiling.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        tab = json.load(f)["gbs_by_row_bytes"]
+    keys = sorted(int(k) for k in tab)
+    k = max([k for k in keys if k <= row_bytes] or [keys[0]])
+    return float(tab[str(k)])
+
+
 def _traffic_from_profiles(workload):
     """dram bytes per launch from the committed ncu summary, or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -406,7 +418,12 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": _traffic_from_profiles(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": kern_ms, "kernel_ms_median": kern_ms_med,
-                     "frac_of_nominal_8000": achieved / 8000.0, "kernel": "ctrfe::fused_pool_kernel"},
+                     "frac_of_nominal_8000": achieved / 8000.0, "kernel": "ctrfe::fused_pool_kernel",
+                     "random_row_ceiling_gbs": _random_row_ceiling(D * es),
+                     "frac_of_random_row_ceiling": (achieved / _random_row_ceiling(D * es)) if _random_row_ceiling(D * es) else None,
+                     "random_row_ceiling_note": "what a stripped uniform-random gather of rows this size sustains on this GPU "
+                                                "(benchtools/gather_ceiling.cu, profiles/r1_gather_ceiling.txt); Zipf ids can "
+                                                "exceed it through L2 hits"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // Ke, "d2h_bytes_per_step": d2h // Ke,
                 "steps": Ke, "ms_per_step": float(te.item()) / Ke,
                 "path": ("HostFrontEnd zero_copy (buffers bound once): the kernel reads pinned host ids/LoD and writes "
