@@ -11,6 +11,7 @@
 #include <utility>
 #include <vector>
 
+#include "ctrfe_fast_kernel.cuh"
 #include "ctrfe_kernels.cuh"
 
 namespace {
@@ -75,6 +76,8 @@ struct ctrfe_plan {
   bool vect = false;
   int g_shift = 0;
   int chunk_bytes = 16;  // bytes of a row one lane holds (32: 256-bit loads, fp32 only)
+  bool fast = false;     // accumulating chunks may use the specialised kernel (ctrfe_fast_kernel.cuh)
+  bool cvm_use = false;
   std::vector<IdSource> id_src;
 };
 
@@ -202,6 +205,19 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
   }
   plan->chunk_bytes = cb;
+  // the specialised kernel: exact 16*G-byte rows, zero-initialised accumulating pools, no
+  // padding_idx, aligned outputs (CTRFE_NO_FAST=1 forces the general kernel, for A/B runs)
+  {
+    const char* nofast = getenv("CTRFE_NO_FAST");
+    bool f = v && cb == 16 && row_bytes <= 512 && (row_bytes & (row_bytes - 1)) == 0 && d->padding_idx == -1 &&
+             d->init_mode == CTRFE_INIT_ZERO && d->cvm_mode != CTRFE_CVM_STRIP && !(nofast && nofast[0] == '1');
+    for (int s = 0; f && s < d->n_slots; ++s) {
+      const ctrfe_slot& sl = d->slots[s];
+      if (!sl.ids || reinterpret_cast<uintptr_t>(sl.out) % 16 != 0 || (sl.out_ld * es) % 16 != 0) f = false;
+    }
+    plan->fast = f;
+    plan->cvm_use = d->cvm_mode == CTRFE_CVM_USE;
+  }
   const long long units = v ? row_bytes / cb : d->dim;  // lane-sized pieces per row
   int g_shift = 5;                                      // the scalar fallback always uses whole warps
   if (v) { g_shift = 0; while ((1 << g_shift) < units && g_shift < 5) ++g_shift; }
@@ -345,9 +361,37 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p);
 }
 
+template <int DT, bool CVM, bool SH>
+void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  using namespace ctrfe;
+  switch (gs) {
+    case 0: fused_pool_fast_kernel<DT, 0, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 1: fused_pool_fast_kernel<DT, 1, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 2: fused_pool_fast_kernel<DT, 2, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 3: fused_pool_fast_kernel<DT, 3, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 4: fused_pool_fast_kernel<DT, 4, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    default: fused_pool_fast_kernel<DT, 5, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+  }
+}
+
+template <int DT>
+void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+  const bool sh = p.n_shards > 0;
+  if (cvm) { if (sh) launch_fast_g<DT, true, true>(gs, grid, st, p); else launch_fast_g<DT, true, false>(gs, grid, st, p); }
+  else { if (sh) launch_fast_g<DT, false, true>(gs, grid, st, p); else launch_fast_g<DT, false, false>(gs, grid, st, p); }
+}
+
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
     const int m = plan.modes[c];
+    if (plan.fast && m == ctrfe::kModeAdd) {
+      switch (plan.dtype) {
+        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
+        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
+        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
+      }
+      continue;
+    }
     switch (plan.dtype) {
       case CTRFE_F32: launch_fused_t<CTRFE_F32>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
       case CTRFE_F16: launch_fused_t<CTRFE_F16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;

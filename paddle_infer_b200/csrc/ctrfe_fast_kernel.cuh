@@ -1,0 +1,186 @@
+// ctrfe_fast_kernel.cuh -- the specialised instantiation of the fused gather + pool + CVM
+// kernel for the case every BASELINE config is in:
+//   * rows are exactly 16 * G bytes (G = 1..32 lanes, a power of two) and 16-byte aligned,
+//     outputs 16-byte aligned: every lane always holds a valid 128-bit chunk;
+//   * SUM / AVERAGE / SQRT slots, accumulator starts at zero, no padding_idx;
+//   * ids present (int64 or int32); CVM on or absent.
+// ncu showed the general kernel bound by warp-instruction issue (profiles/README.md); here the
+// row width is a compile-time constant and every per-row decision that the general kernel
+// takes at run time (zero rows, first-row copy, column masks, tiles) is gone:
+// a row slot is SHFL + compare + address + LDG.128 + two FADD2.
+// Same arithmetic, same order, same results as ctrfe::fused_pool_kernel (the GPU tests run
+// both paths on the same inputs).  An out-of-range id is flagged and its row skipped.
+#pragma once
+
+#include "ctrfe_kernels.cuh"
+
+namespace ctrfe {
+
+template <int DT, int GS, bool CVM, bool SHARDED>
+__global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
+fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
+  using L = Lane<DT, true, 16>;
+  constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
+  constexpr unsigned kFull = 0xffffffffu;
+  constexpr int G = 1 << GS;
+  constexpr int U = kUnroll;
+  constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
+  constexpr int R = G * NI;               // rows consumed per step of the sequence loop
+  constexpr unsigned kRowShift = GS + 4;  // row_bytes = 16 << GS
+
+  __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
+  if constexpr (SHARDED) {
+    if (threadIdx.x < kMaxShards) s_shards[threadIdx.x] = reinterpret_cast<unsigned long long>(kp.shard_tables[threadIdx.x]);
+    __syncthreads();
+  }
+
+  const SlotK* const slp = &kp.slots[blockIdx.y];
+  const unsigned n_seg = slp->n_seg;
+  if (((blockIdx.x * static_cast<unsigned>(kThreads)) >> GS) >= n_seg) return;  // CTA past this slot's work
+  const unsigned seg = (blockIdx.x * static_cast<unsigned>(kThreads) + threadIdx.x) >> GS;
+  const unsigned gl = threadIdx.x & (G - 1);
+  const bool seg_ok = seg < n_seg;
+
+  uint32_t start = 0u, endo = 0u;
+  if (seg_ok) {
+    const unsigned* w = reinterpret_cast<const unsigned*>(slp->lod) + 2u * seg;  // low words: offsets < 2^32
+    start = __ldg(w);
+    endo = __ldg(w + 2);
+  }
+  const int len = static_cast<int>(endo - start);
+  const int maxlen = __reduce_max_sync(kFull, len);
+
+  const unsigned table_rows = slp->table_rows;
+  const bool ids_i32 = slp->id_kind == 1;
+  const unsigned lane_off = gl * 16u;
+  const unsigned long long lane_base = reinterpret_cast<unsigned long long>(slp->table) + lane_off;
+  const unsigned shard_mask = SHARDED ? static_cast<unsigned>(kp.n_shards - 1) : 0u;
+  const int shard_shift = SHARDED ? kp.shard_shift : 0;
+
+  auto row_ptr = [&](uint32_t rid) -> const char* {
+    if constexpr (SHARDED) {
+      return reinterpret_cast<const char*>(s_shards[rid & shard_mask] +
+                                           (static_cast<unsigned long long>(rid >> shard_shift) << kRowShift) + lane_off);
+    } else {
+      return reinterpret_cast<const char*>(lane_base + (static_cast<unsigned long long>(rid) << kRowShift));
+    }
+  };
+
+  // row index of the id at sequence position `off`, kSkip past the end or for a bad id
+  auto fetch_rid = [&](int off) -> uint32_t {
+    if (off >= len) return kSkip;
+    const unsigned pos = start + static_cast<unsigned>(off);
+    uint32_t lo, hi;
+    if (!ids_i32) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(slp->ids) + pos);
+      lo = v.x;
+      hi = v.y;
+    } else {
+      const int v = __ldg(reinterpret_cast<const int*>(slp->ids) + pos);
+      lo = static_cast<uint32_t>(v);
+      hi = static_cast<uint32_t>(v >> 31);
+    }
+    if (hi == 0u && lo < table_rows) return lo;
+    atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) | pos);
+    return kSkip;
+  };
+
+  float acc[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
+
+  uint32_t cur[NI];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) cur[i] = fetch_rid(i * G + static_cast<int>(gl));
+
+  for (int base = 0; base < maxlen; base += R) {
+    uint32_t nxt[NI];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) nxt[i] = kSkip;
+    if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
+#pragma unroll
+      for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(base + R + i * G + static_cast<int>(gl));
+    }
+#pragma unroll
+    for (int c = 0; c < R / U; ++c) {
+      if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
+      uint32_t raw[U][RW];
+      bool ok[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = c * U + u;
+        const uint32_t rid = __shfl_sync(kFull, cur[j / G], j % G, G);
+        ok[u] = rid != kSkip;
+        if (ok[u]) L::load(row_ptr(rid), raw[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        if constexpr (ES == 4) {
+#pragma unroll
+          for (int e = 0; e < VEC; e += 2)
+            add_f32x2(acc[e], acc[e + 1], __uint_as_float(raw[u][e]), __uint_as_float(raw[u][e + 1]));
+        } else {
+#pragma unroll
+          for (int r = 0; r < RW; ++r) {
+            const float2 x = L::unpack2(raw[u][r]);
+            add_f32x2(acc[2 * r], acc[2 * r + 1], x.x, x.y);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
+  }
+
+  // ---- epilogue: pad / scale / CVM / store (same arithmetic as the general kernel) ------
+  const int pooltype = slp->pooltype;
+  if (len == 0) {
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = kp.pad_value;
+  } else if (pooltype != CTRFE_POOL_SUM) {
+    const float h = static_cast<float>(len);
+    if (kp.scale_mode == CTRFE_SCALE_DIVIDE) {
+      const float d = pooltype == CTRFE_POOL_AVERAGE ? h : sqrtf(h);
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) acc[e] = acc[e] / d;
+    } else {
+      float s = 1.0f;
+      s = pooltype == CTRFE_POOL_AVERAGE ? s / h : s / sqrtf(h);
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) acc[e] = s * acc[e];
+    }
+  }
+
+  if constexpr (CVM) {
+    if constexpr (G >= 2) {
+      const float x1 = __shfl_sync(kFull, acc[1], 0, G);
+      double lg = 0.0;
+      if (gl < 2) lg = cvm_log1(gl == 0 ? acc[0] : x1);
+      const float y0 = __shfl_sync(kFull, static_cast<float>(lg), 0, G);
+      float y1 = 0.0f;
+      if (gl == 1) y1 = static_cast<float>(lg - static_cast<double>(y0));
+      y1 = __shfl_sync(kFull, y1, 1, G);
+      if (gl == 0) { acc[0] = y0; acc[1] = y1; }
+    } else {
+      const float y0 = static_cast<float>(cvm_log1(acc[0]));
+      acc[1] = static_cast<float>(cvm_log1(acc[1]) - static_cast<double>(y0));
+      acc[0] = y0;
+    }
+  }
+
+  if (!seg_ok) return;
+  uint32_t packed[RW];
+#pragma unroll
+  for (int r = 0; r < RW; ++r) packed[r] = 0u;
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) {
+    const uint32_t b = float_to_elem<DT>(acc[e]);
+    if constexpr (ES == 4) packed[e] = b;
+    else packed[e >> 1] |= b << ((e & 1) * 16);
+  }
+  char* dst = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes + lane_off;
+  *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+}
+
+}  // namespace ctrfe
