@@ -99,6 +99,22 @@ typedef struct ctrfe_slot {
   int32_t ids_dtype;     /* CTRFE_I64 / CTRFE_I32 */
 } ctrfe_slot;
 
+/* Hot-row replica cache for the row-sharded mode.  CTR ids are Zipf-distributed: a few
+ * hundred MB of replicated hot rows per GPU absorb most look-ups, which would otherwise all
+ * cross NVLink (peer memory is not cached by the local L2).  `rows` holds exact copies of table
+ * rows; `keys` / `vals` are an open-addressing hash (2^log2_slots entries, linear probing, at
+ * most 8 probes) from row id to the index of its copy.  The table is read-only at inference
+ * time, so there is nothing to keep coherent; results stay bit-identical.  The reference has no
+ * counterpart on this path (HeterComm always walks to the owner GPU,
+ * framework/fleet/heter_ps/heter_comm_inl.h:1477-1607). */
+typedef struct ctrfe_hot_cache {
+  const void* rows;       /* device [n_rows, dim], same dtype as the table */
+  const uint32_t* keys;   /* device [2^log2_slots]; 0xffffffff = empty */
+  const uint32_t* vals;   /* device [2^log2_slots]; index into rows */
+  int32_t log2_slots;
+  int32_t n_rows;
+} ctrfe_hot_cache;
+
 typedef struct ctrfe_fused_desc {
   int32_t n_slots;
   int32_t dtype;          /* CTRFE_F32 / F16 / BF16: storage type of tables and outputs;
@@ -127,6 +143,8 @@ typedef struct ctrfe_fused_desc {
                              bucket / walk_to_dest / gather / walk_to_src pull
                              (heter_comm_inl.h:1477-1607): rows are fetched by the pooling kernel
                              itself with loads through the peer mapping, in sequence order */
+  const struct ctrfe_hot_cache* hot_cache; /* sharded mode only, may be NULL: local replicas of the
+                             most frequently looked-up rows (see ctrfe_hot_cache_build) */
 } ctrfe_fused_desc;
 
 /* ---- library ------------------------------------------------------------------------ */
@@ -210,6 +228,11 @@ int ctrfe_shard_close(int device, void* ptr);
 int ctrfe_shard_alloc_fd(int device, uint64_t bytes, void** ptr, int* fd, uint64_t* mapped_bytes);
 int ctrfe_shard_open_fd(int device, int fd, uint64_t mapped_bytes, void** ptr);
 int ctrfe_shard_unmap(int device, void* ptr, uint64_t mapped_bytes);
+/* Fills the hash of a ctrfe_hot_cache: inserts the n DISTINCT row ids hot_ids[i] -> i.  `keys`
+ * must have been set to 0xff bytes.  An id that finds no free slot within 8 probes is left out
+ * (its replica is simply never used).  Asynchronous on `stream`. */
+int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, uint32_t* keys, uint32_t* vals,
+                          int32_t log2_slots, void* stream);
 
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 

@@ -27,12 +27,17 @@ class Slot(C.Structure):
                 ("out_ld", C.c_int64), ("pooltype", C.c_int32), ("ids_dtype", C.c_int32)]
 
 
+class HotCache(C.Structure):
+    _fields_ = [("rows", C.c_void_p), ("keys", C.c_void_p), ("vals", C.c_void_p), ("log2_slots", C.c_int32),
+                ("n_rows", C.c_int32)]
+
+
 class FusedDesc(C.Structure):
     _fields_ = [("n_slots", C.c_int32), ("dtype", C.c_int32), ("slots", C.POINTER(Slot)),
                 ("dim", C.c_int64), ("padding_idx", C.c_int64), ("pad_value", C.c_float),
                 ("cvm_mode", C.c_int32), ("cvm_offset", C.c_int32), ("scale_mode", C.c_int32),
                 ("init_mode", C.c_int32), ("lod_location", C.c_int32), ("n_shards", C.c_int32),
-                ("shard_tables", C.POINTER(C.c_void_p))]
+                ("shard_tables", C.POINTER(C.c_void_p)), ("hot_cache", C.POINTER(HotCache))]
 
 
 class CtrfeError(RuntimeError):
@@ -59,7 +64,7 @@ EXPORTS = [
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
-    "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap",
+    "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build",
 ]
 
 
@@ -94,6 +99,7 @@ def lib():
         L.ctrfe_shard_alloc_fd.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
         L.ctrfe_shard_open_fd.argtypes = [C.c_int, C.c_int, C.c_uint64, C.POINTER(vp)]
         L.ctrfe_shard_unmap.argtypes = [C.c_int, vp, C.c_uint64]
+        L.ctrfe_hot_cache_build.argtypes = [vp, vp, i64, vp, vp, i32, vp]
         _lib = L
     return _lib
 

@@ -78,6 +78,7 @@ struct ctrfe_plan {
   int chunk_bytes = 16;  // bytes of a row one lane holds (32: 256-bit loads, fp32 only)
   bool fast = false;     // accumulating chunks may use the specialised kernel (ctrfe_fast_kernel.cuh)
   bool cvm_use = false;
+  bool hot = false;      // sharded mode with a hot-row replica cache
   std::vector<IdSource> id_src;
 };
 
@@ -173,6 +174,17 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     for (int g = 0; g < d->n_shards; ++g)
       if (!d->shard_tables[g] || reinterpret_cast<uintptr_t>(d->shard_tables[g]) % 16 != 0)
         return fail(CTRFE_ERR_ARG, "fused: shard_tables[%d] is null or not 16-byte aligned", g);
+    if (d->hot_cache && d->hot_cache->rows) {
+      const ctrfe_hot_cache* hc = d->hot_cache;
+      if (!hc->keys || !hc->vals || hc->log2_slots < 4 || hc->log2_slots > 30 || hc->n_rows <= 0 ||
+          reinterpret_cast<uintptr_t>(hc->rows) % 16 != 0)
+        return fail(CTRFE_ERR_ARG, "fused: malformed hot_cache");
+      for (int s = 0; s < d->n_slots; ++s)
+        if (d->slots[s].table_rows >= 0x7fffffffLL)
+          return fail(CTRFE_ERR_UNSUPPORTED, "fused: a hot-row cache needs table_rows < 2^31");
+    }
+  } else if (d->hot_cache) {
+    return fail(CTRFE_ERR_ARG, "fused: hot_cache is only meaningful in the sharded table mode");
   }
   size_t lb = 0;
   for (int s = 0; s < d->n_slots; ++s) {
@@ -257,6 +269,13 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       k.init_mode = d->init_mode;
       k.pad_value = d->pad_value;
       k.n_slots = 0;
+      if (sharded && plan->fast && d->hot_cache && d->hot_cache->rows && d->hot_cache->log2_slots > 0) {
+        k.hot_rows = static_cast<const char*>(d->hot_cache->rows);
+        k.hot_keys = d->hot_cache->keys;
+        k.hot_vals = d->hot_cache->vals;
+        k.hot_mask = (1u << d->hot_cache->log2_slots) - 1u;
+        k.hot_shift = 32 - d->hot_cache->log2_slots;
+      }
       if (sharded) {
         k.n_shards = d->n_shards;
         k.shard_shift = d->n_shards == 2 ? 1 : (d->n_shards == 4 ? 2 : 3);
@@ -361,24 +380,30 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p);
 }
 
-template <int DT, bool CVM, bool SH>
+template <int DT, bool CVM, bool SH, bool HOT>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
   using namespace ctrfe;
   switch (gs) {
-    case 0: fused_pool_fast_kernel<DT, 0, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 1: fused_pool_fast_kernel<DT, 1, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 2: fused_pool_fast_kernel<DT, 2, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 3: fused_pool_fast_kernel<DT, 3, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 4: fused_pool_fast_kernel<DT, 4, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
-    default: fused_pool_fast_kernel<DT, 5, CVM, SH><<<grid, kThreads, 0, st>>>(p); break;
+    case 0: fused_pool_fast_kernel<DT, 0, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    case 1: fused_pool_fast_kernel<DT, 1, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    case 2: fused_pool_fast_kernel<DT, 2, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    case 3: fused_pool_fast_kernel<DT, 3, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    case 4: fused_pool_fast_kernel<DT, 4, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    default: fused_pool_fast_kernel<DT, 5, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
   }
 }
 
 template <int DT>
 void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
   const bool sh = p.n_shards > 0;
-  if (cvm) { if (sh) launch_fast_g<DT, true, true>(gs, grid, st, p); else launch_fast_g<DT, true, false>(gs, grid, st, p); }
-  else { if (sh) launch_fast_g<DT, false, true>(gs, grid, st, p); else launch_fast_g<DT, false, false>(gs, grid, st, p); }
+  const bool hot = sh && p.hot_rows != nullptr;
+  if (hot) {
+    if (cvm) launch_fast_g<DT, true, true, true>(gs, grid, st, p); else launch_fast_g<DT, false, true, true>(gs, grid, st, p);
+  } else if (cvm) {
+    if (sh) launch_fast_g<DT, true, true, false>(gs, grid, st, p); else launch_fast_g<DT, true, false, false>(gs, grid, st, p);
+  } else {
+    if (sh) launch_fast_g<DT, false, true, false>(gs, grid, st, p); else launch_fast_g<DT, false, false, false>(gs, grid, st, p);
+  }
 }
 
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
@@ -676,6 +701,19 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
   return CTRFE_OK;
 }
 
+
+int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, uint32_t* keys, uint32_t* vals,
+                          int32_t log2_slots, void* stream) {
+  if (!ctx || !hot_ids || !keys || !vals || n < 0 || log2_slots < 4 || log2_slots > 30)
+    return fail(CTRFE_ERR_ARG, "hot_cache_build: bad argument");
+  if (n == 0) return CTRFE_OK;
+  DeviceGuard g(ctx->device);
+  const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+  ctrfe::hot_insert_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const long long*>(hot_ids), n, keys, vals, (1u << log2_slots) - 1u, 32 - log2_slots);
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
 
 // ---- row-sharded tables: exportable shard memory and peer mappings ----------------------
 int ctrfe_shard_alloc(int device, uint64_t bytes, void** ptr) {

@@ -16,7 +16,7 @@
 
 namespace ctrfe {
 
-template <int DT, int GS, bool CVM, bool SHARDED>
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
 __global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
 fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   using L = Lane<DT, true, 16>;
@@ -57,7 +57,12 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   const unsigned shard_mask = SHARDED ? static_cast<unsigned>(kp.n_shards - 1) : 0u;
   const int shard_shift = SHARDED ? kp.shard_shift : 0;
 
+  const unsigned long long hot_base = HOT ? reinterpret_cast<unsigned long long>(kp.hot_rows) + lane_off : 0ull;
   auto row_ptr = [&](uint32_t rid) -> const char* {
+    if constexpr (HOT) {
+      if (rid & kHotBit)  // a local replica of a hot row
+        return reinterpret_cast<const char*>(hot_base + (static_cast<unsigned long long>(rid & ~kHotBit) << kRowShift));
+    }
     if constexpr (SHARDED) {
       return reinterpret_cast<const char*>(s_shards[rid & shard_mask] +
                                            (static_cast<unsigned long long>(rid >> shard_shift) << kRowShift) + lane_off);
@@ -80,7 +85,20 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
       lo = static_cast<uint32_t>(v);
       hi = static_cast<uint32_t>(v >> 31);
     }
-    if (hi == 0u && lo < table_rows) return lo;
+    if (hi == 0u && lo < table_rows) {
+      if constexpr (HOT) {
+        // is there a local replica?  open addressing, linear probing, bounded probe count
+        unsigned h = (lo * 2654435761u) >> kp.hot_shift;
+#pragma unroll 1
+        for (int pr = 0; pr < kHotProbes; ++pr) {
+          const unsigned k = __ldg(kp.hot_keys + h);
+          if (k == lo) return kHotBit | __ldg(kp.hot_vals + h);
+          if (k == 0xffffffffu) break;
+          h = (h + 1u) & kp.hot_mask;
+        }
+      }
+      return lo;
+    }
     atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) | pos);
     return kSkip;
   };
@@ -181,6 +199,22 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   }
   char* dst = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes + lane_off;
   *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+}
+
+// Inserts hot_ids[i] -> i into the open-addressing hash of a hot-row cache.
+__global__ void hot_insert_kernel(const long long* __restrict__ hot_ids, long long n, unsigned* keys, unsigned* vals,
+                                  unsigned mask, int shift) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long id = hot_ids[i];
+  if (id < 0 || id >= 0x7fffffffLL) return;  // the hot bit needs row ids below 2^31
+  const unsigned lo = static_cast<unsigned>(id);
+  unsigned h = (lo * 2654435761u) >> shift;
+  for (int pr = 0; pr < kHotProbes; ++pr) {
+    const unsigned old = atomicCAS(keys + h, 0xffffffffu, lo);
+    if (old == 0xffffffffu || old == lo) { vals[h] = static_cast<unsigned>(i); return; }
+    h = (h + 1u) & mask;
+  }
 }
 
 }  // namespace ctrfe

@@ -43,6 +43,8 @@ constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel
 constexpr int kMaxShards = 8;           // GPUs of one NVSwitch box
 constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequence: no load, no add
 constexpr uint32_t kZero = 0xfffffffeu;  // padding_idx / out-of-range id: contributes a zero row
+constexpr uint32_t kHotBit = 0x80000000u; // row index refers to the hot-row replica cache (sharded mode)
+constexpr int kHotProbes = 8;             // linear probes of the hot-row hash
 
 // Slot descriptor, passed BY VALUE in the kernel parameter block (constant bank): a CTA
 // reads its slot's pointers without a dependent global load.
@@ -78,6 +80,12 @@ struct KParams {
   int shard_shift;
   int n_shards;
   const char* shard_tables[kMaxShards];
+  // hot-row replica cache of the sharded mode (ctrfe_hot_cache): null = none
+  const char* hot_rows;
+  const unsigned* hot_keys;
+  const unsigned* hot_vals;
+  unsigned hot_mask;   // slots - 1
+  int hot_shift;       // 32 - log2(slots)
   SlotK slots[kMaxSlotsPerLaunch];
 };
 static_assert(sizeof(KParams) <= 4096, "kernel parameter block must stay within 4 KB");

@@ -277,6 +277,10 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
     if sharded is not None:
         desc.n_shards = sharded.n_shards
         desc.shard_tables = C.cast(sharded.shard_ptrs, C.POINTER(C.c_void_p))
+        hot = getattr(sharded, "hot", None)
+        if hot is not None:  # local replicas of the hot rows (shard.HotRowCache)
+            desc.hot_cache = C.pointer(hot.struct)
+            keep.append(hot)
         keep.append(sharded)
     keep.append(slots)
     return desc, keep
@@ -526,6 +530,8 @@ class HostFrontEnd:
         if self.sharded is not None:
             desc.n_shards = self.sharded.n_shards
             desc.shard_tables = C.cast(self.sharded.shard_ptrs, C.POINTER(C.c_void_p))
+            if getattr(self.sharded, "hot", None) is not None:
+                desc.hot_cache = C.pointer(self.sharded.hot.struct)
         h2d = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.numel() * 8 for l in lods_host)
         return desc, slots, h2d
 

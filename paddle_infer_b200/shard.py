@@ -224,3 +224,50 @@ class LocalShards:
         self.device = shards[0].device
         self.shard_ptrs = (C.c_void_p * self.n_shards)(*[s.data_ptr() for s in shards])
         self.n_rows = sum(s.shape[0] for s in shards)
+
+
+def pick_hot_ids(sample_ids, capacity: int):
+    """The `capacity` most frequent ids of a sample of look-ups (a torch int64 tensor of any
+    shape, on the GPU), most frequent first.  Set-up helper, not on the data path."""
+    import torch
+    uniq, counts = torch.unique(sample_ids.reshape(-1), return_counts=True)
+    order = torch.argsort(counts, descending=True)[:capacity]
+    return uniq[order].contiguous()
+
+
+class HotRowCache:
+    """Local replicas of a sharded table's most frequently looked-up rows (ctrfe_hot_cache).
+
+    Peer memory is not cached by the local L2, so without this every look-up of a popular row
+    crosses NVLink again; with Zipf ids a few hundred MB of replicas absorb most look-ups.  The
+    replicas are exact copies fetched through the sharded kernel itself (pooltype FIRST over
+    one-id sequences), so results do not change by a bit.  The table is read-only at inference
+    time; rebuild the cache if the table or the id distribution changes."""
+
+    def __init__(self, table, hot_ids, ctx=None):
+        import torch
+        from . import ops
+        dev = table.device
+        hot_ids = hot_ids.to(dev).to(torch.int64).contiguous()
+        n = hot_ids.numel()
+        if n == 0:
+            raise ValueError("no hot ids")
+        ctx = ctx or ops.default_context(dev)
+        lod = torch.arange(n + 1, dtype=torch.int64, device=dev)
+        saved, table.hot = getattr(table, "hot", None), None
+        try:
+            rows = ops.ctr_fused_emb_seqpool_cvm(table, [hot_ids], [lod], "FIRST", use_cvm=None, ctx=ctx)[0]
+        finally:
+            table.hot = saved
+        self.rows = rows.contiguous()
+        log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.5))))
+        self.log2_slots = log2
+        self.keys = torch.full((1 << log2,), -1, dtype=torch.int32, device=dev)
+        self.vals = torch.zeros((1 << log2,), dtype=torch.int32, device=dev)
+        B.check(B.lib().ctrfe_hot_cache_build(ctx.handle, hot_ids.data_ptr(), n, self.keys.data_ptr(),
+                                              self.vals.data_ptr(), log2, torch.cuda.current_stream(dev).cuda_stream))
+        torch.cuda.synchronize(dev)
+        self.n_rows = n
+        self.hot_ids = hot_ids
+        self.struct = B.HotCache(self.rows.data_ptr(), self.keys.data_ptr(), self.vals.data_ptr(), log2, n)
+        self.nbytes = self.rows.numel() * self.rows.element_size() + 8 * (1 << log2)

@@ -57,6 +57,12 @@ def main():
     want = O.fused_forward([full], ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE, concat=True)
     np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
     np.testing.assert_array_equal(got.reshape(Bsz, S, D)[:, :, 2:], want.reshape(Bsz, S, D)[:, :, 2:])
+    # hot-row replicas: same bits, fewer NVLink look-ups
+    plain = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "SUM", use_cvm=True, concat=True)
+    table.hot = shard.HotRowCache(table, shard.pick_hot_ids(torch.cat(ids_t), 4096))
+    cached = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "SUM", use_cvm=True, concat=True)
+    assert torch.equal(plain, cached)
+    table.hot = None
     frac_remote = float(np.mean(np.concatenate(ids) % world != rank))
     dist.barrier()
     table.close()

@@ -133,6 +133,52 @@ def test_sharded_kernel_on_one_gpu(G):
         ops.ctr_fused_emb_seqpool_cvm(table, [bad], [[0, 3]], "SUM", use_cvm=None)
 
 
+@pytest.mark.gpu
+def test_hot_row_cache_changes_nothing_but_the_source_of_the_rows():
+    """Replicas of the most frequent rows (shard.HotRowCache): same bits out, with and without."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import __graft_entry__ as g
+    g.build()
+    from benchtools import synth
+    from oracle import oracle as O
+    from paddle_infer_b200 import ops, shard
+    dev = torch.device("cuda:0")
+    G, N, D, seed, S, Bsz = 4, 50_021, 32, 11, 3, 400
+    full = synth.table_rows_numpy(seed, np.arange(N), D, "f32")
+    full[7] = -0.0  # a row of negative zeros must be replicated with its sign
+    table = shard.LocalShards([torch.from_numpy(full[shard.global_rows_of_shard(N, G, k)]).to(dev) for k in range(G)])
+    rng = np.random.default_rng(5)
+    lods, ids = [], []
+    for _ in range(S):
+        l = rng.integers(0, 9, Bsz)
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        lods.append(lod)
+        ids.append(synth.zipf_ids(rng, int(lod[-1]), N))   # a real head: most look-ups hit few rows
+    ids[0][:5] = 7
+    ids_t = [torch.from_numpy(i).to(dev) for i in ids]
+    plain = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "SUM", use_cvm=True)
+    hot_ids = shard.pick_hot_ids(torch.cat(ids_t), 500)
+    assert hot_ids.numel() == 500 and 7 in hot_ids.tolist()
+    table.hot = shard.HotRowCache(table, hot_ids)
+    np.testing.assert_array_equal(table.hot.rows.cpu().numpy().view(np.uint32), full[hot_ids.cpu().numpy()].view(np.uint32))
+    hit = np.isin(np.concatenate(ids), hot_ids.cpu().numpy()).mean()
+    assert hit > 0.4
+    cached = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "SUM", use_cvm=True)
+    want = O.fused_forward([full], ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE)
+    for s in range(S):
+        assert torch.equal(plain[s], cached[s])
+        np.testing.assert_array_equal(cached[s].cpu().numpy()[:, 2:], want[s][:, 2:])
+    # AVERAGE without CVM, and a cache so small that its hash is nearly full
+    table.hot = shard.HotRowCache(table, hot_ids[:10])
+    a = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "AVERAGE", use_cvm=None)
+    table.hot = None
+    b = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "AVERAGE", use_cvm=None)
+    for s in range(S):
+        assert torch.equal(a[s], b[s])
+
+
 # ------------------------------------------------------------------ the NVLink path, >= 2 GPUs
 @pytest.mark.gpu
 def test_sharded_across_processes():
