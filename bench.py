@@ -281,7 +281,10 @@ def run_ours(args):
     # the global batch split over the ranks (strong scaling); remote rows are fetched by the
     # pooling kernel itself over NVLink.  Everything else: a full table replica per rank.
     sharded = args.workload == "cfg4" and world > 1
-    Bsz = cfg.batch // world if sharded else cfg.batch
+    # diagnostic (one GPU): the sharded kernel over G shards that all live on this GPU, on 1/G
+    # of the batch -- what one rank of a G-GPU run does, minus NVLink
+    local_G = args.local_shards if world == 1 and args.workload == "cfg4" else 0
+    Bsz = cfg.batch // world if sharded else (cfg.batch // local_G if local_G else cfg.batch)
     n_batches = 4 if cfg.batch * cfg.slots * cfg.dim * cfg.elem_size > (256 << 20) else N_BATCHES
     shard_table = None
     tables = []
@@ -292,6 +295,15 @@ def run_ours(args):
         torch.cuda.synchronize()
         dist.barrier()
         W = shard_table
+    elif local_G:
+        from paddle_infer_b200 import shard as shard_mod
+        parts = []
+        for k in range(local_G):
+            part = torch.empty((shard_mod.shard_num_rows(cfg.rows, local_G, k), D), dtype=tdt, device=dev)
+            synth.fill_table(part, cfg.seed, row0=k, row_stride=local_G, cvm_cols=cfg.use_cvm is not None)
+            parts.append(part)
+        W = shard_table = shard_mod.LocalShards(parts)
+        cfg.name += f"[diagnostic: {local_G} shards on one GPU, 1/{local_G} of the batch]"
     else:
         for t in range(cfg.n_tables()):
             tab = torch.empty((cfg.rows, D), dtype=tdt, device=dev)
@@ -302,15 +314,16 @@ def run_ours(args):
     # sharded mode: replicate the hottest rows locally (shard.HotRowCache).  The hot set comes
     # from sample traffic drawn from the same distribution but DISJOINT from the timed batches.
     hot_info = None
-    if sharded and args.hot_rows > 0:
-        sample = [synth.draw_batch(cfg, step=rank * 1000 + 500 + b, batch=Bsz) for b in range(4)]
+    if (sharded or local_G) and args.hot_rows > 0:
+        sample = [synth.draw_batch(cfg, step=rank * 1000 + 500 + b, batch=Bsz) for b in range(args.hot_sample_batches)]
         sample_ids = torch.cat([torch.from_numpy(i).to(dev) for sb in sample for i in sb.ids])
         hot_ids = shard_mod.pick_hot_ids(sample_ids, args.hot_rows)
         shard_table.hot = shard_mod.HotRowCache(shard_table, hot_ids)
         hot_info = {"rows": int(hot_ids.numel()), "bytes": int(shard_table.hot.nbytes),
-                    "built_from": "4 sample batches per rank, disjoint from the timed batches"}
+                    "built_from": f"{args.hot_sample_batches} sample batches per rank, disjoint from the timed batches"}
         del sample, sample_ids
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
 
     # ---- batches resident in HBM (ids, LoD, output blocks), one plan each ----------------
     host_batches = [synth.draw_batch(cfg, step=rank * 1000 + b, batch=Bsz) for b in range(n_batches)]
@@ -459,7 +472,9 @@ def run_ours(args):
                           "link_peak_gbs": 770.0,
                           "peak_source": "B200_PROFILING.md measured peer copy, per direction per GPU",
                           "note": "requested bytes / time; above the link peak means L1 hits on repeated hot rows"}
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if local_G and hot_info is not None:
+        line["config"]["hot_row_cache"] = hot_info
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not local_G:
         tabs, hb4, rows = host_table_and_batches(cfg, synth, 4, torch, tables)
         line["cpu_baseline"] = cpu_leg(cfg, tabs, hb4, budget_s=args.cpu_budget)
     elif rank == 0:
@@ -487,7 +502,10 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows", type=int, default=0, help="diagnostic: override the table rows of the workload")
-    ap.add_argument("--hot-rows", type=int, default=2_000_000,
+    ap.add_argument("--hot-sample-batches", type=int, default=12)
+    ap.add_argument("--local-shards", type=int, default=0,
+                    help="diagnostic, one GPU, cfg4: run the sharded kernel over this many shards on the same GPU")
+    ap.add_argument("--hot-rows", type=int, default=4_000_000,
                     help="sharded mode: rows replicated locally by the hot-row cache (0 = none)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

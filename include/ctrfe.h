@@ -101,18 +101,17 @@ typedef struct ctrfe_slot {
 
 /* Hot-row replica cache for the row-sharded mode.  CTR ids are Zipf-distributed: a few
  * hundred MB of replicated hot rows per GPU absorb most look-ups, which would otherwise all
- * cross NVLink (peer memory is not cached by the local L2).  `rows` holds exact copies of table
- * rows; `keys` / `vals` are an open-addressing hash (2^log2_slots entries, linear probing, at
- * most 8 probes) from row id to the index of its copy.  The table is read-only at inference
+ * cross NVLink (peer memory is not cached by the local L2).  `keys` is an open-addressing
+ * hash of row ids (2^log2_slots entries, linear probing, at most 8 probes) and `rows` holds, at
+ * the same slot index, an exact copy of that table row: a hit costs one 4-byte probe.  The table is read-only at inference
  * time, so there is nothing to keep coherent; results stay bit-identical.  The reference has no
  * counterpart on this path (HeterComm always walks to the owner GPU,
  * framework/fleet/heter_ps/heter_comm_inl.h:1477-1607). */
 typedef struct ctrfe_hot_cache {
-  const void* rows;       /* device [n_rows, dim], same dtype as the table */
+  const void* rows;       /* device [2^log2_slots, dim], same dtype as the table */
   const uint32_t* keys;   /* device [2^log2_slots]; 0xffffffff = empty */
-  const uint32_t* vals;   /* device [2^log2_slots]; index into rows */
   int32_t log2_slots;
-  int32_t n_rows;
+  int32_t n_rows;         /* replicas held (informational) */
 } ctrfe_hot_cache;
 
 typedef struct ctrfe_fused_desc {
@@ -228,11 +227,12 @@ int ctrfe_shard_close(int device, void* ptr);
 int ctrfe_shard_alloc_fd(int device, uint64_t bytes, void** ptr, int* fd, uint64_t* mapped_bytes);
 int ctrfe_shard_open_fd(int device, int fd, uint64_t mapped_bytes, void** ptr);
 int ctrfe_shard_unmap(int device, void* ptr, uint64_t mapped_bytes);
-/* Fills the hash of a ctrfe_hot_cache: inserts the n DISTINCT row ids hot_ids[i] -> i.  `keys`
- * must have been set to 0xff bytes.  An id that finds no free slot within 8 probes is left out
- * (its replica is simply never used).  Asynchronous on `stream`. */
-int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, uint32_t* keys, uint32_t* vals,
-                          int32_t log2_slots, void* stream);
+/* Fills a ctrfe_hot_cache: for each of the n DISTINCT row ids hot_ids[i], claims a hash slot in
+ * `keys` and copies src_rows[i] (row_bytes each, a multiple of 16) to rows[slot].  `keys` must
+ * have been set to 0xff bytes.  An id that finds no free slot within 8 probes is left out (it
+ * is then always fetched from its shard).  Asynchronous on `stream`. */
+int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, const void* src_rows, int64_t row_bytes,
+                          uint32_t* keys, void* rows, int32_t log2_slots, void* stream);
 
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 

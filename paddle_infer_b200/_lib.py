@@ -28,7 +28,7 @@ class Slot(C.Structure):
 
 
 class HotCache(C.Structure):
-    _fields_ = [("rows", C.c_void_p), ("keys", C.c_void_p), ("vals", C.c_void_p), ("log2_slots", C.c_int32),
+    _fields_ = [("rows", C.c_void_p), ("keys", C.c_void_p), ("log2_slots", C.c_int32),
                 ("n_rows", C.c_int32)]
 
 
@@ -99,7 +99,7 @@ def lib():
         L.ctrfe_shard_alloc_fd.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
         L.ctrfe_shard_open_fd.argtypes = [C.c_int, C.c_int, C.c_uint64, C.POINTER(vp)]
         L.ctrfe_shard_unmap.argtypes = [C.c_int, vp, C.c_uint64]
-        L.ctrfe_hot_cache_build.argtypes = [vp, vp, i64, vp, vp, i32, vp]
+        L.ctrfe_hot_cache_build.argtypes = [vp, vp, i64, vp, i64, vp, vp, i32, vp]
         _lib = L
     return _lib
 

@@ -176,7 +176,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
         return fail(CTRFE_ERR_ARG, "fused: shard_tables[%d] is null or not 16-byte aligned", g);
     if (d->hot_cache && d->hot_cache->rows) {
       const ctrfe_hot_cache* hc = d->hot_cache;
-      if (!hc->keys || !hc->vals || hc->log2_slots < 4 || hc->log2_slots > 30 || hc->n_rows <= 0 ||
+      if (!hc->keys || hc->log2_slots < 4 || hc->log2_slots > 30 || hc->n_rows <= 0 ||
           reinterpret_cast<uintptr_t>(hc->rows) % 16 != 0)
         return fail(CTRFE_ERR_ARG, "fused: malformed hot_cache");
       for (int s = 0; s < d->n_slots; ++s)
@@ -272,7 +272,6 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       if (sharded && plan->fast && d->hot_cache && d->hot_cache->rows && d->hot_cache->log2_slots > 0) {
         k.hot_rows = static_cast<const char*>(d->hot_cache->rows);
         k.hot_keys = d->hot_cache->keys;
-        k.hot_vals = d->hot_cache->vals;
         k.hot_mask = (1u << d->hot_cache->log2_slots) - 1u;
         k.hot_shift = 32 - d->hot_cache->log2_slots;
       }
@@ -702,15 +701,17 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
 }
 
 
-int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, uint32_t* keys, uint32_t* vals,
-                          int32_t log2_slots, void* stream) {
-  if (!ctx || !hot_ids || !keys || !vals || n < 0 || log2_slots < 4 || log2_slots > 30)
+int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, const void* src_rows, int64_t row_bytes,
+                          uint32_t* keys, void* rows, int32_t log2_slots, void* stream) {
+  if (!ctx || !hot_ids || !src_rows || !keys || !rows || n < 0 || log2_slots < 4 || log2_slots > 30 || row_bytes <= 0 ||
+      row_bytes % 16 != 0 || reinterpret_cast<uintptr_t>(src_rows) % 16 != 0 || reinterpret_cast<uintptr_t>(rows) % 16 != 0)
     return fail(CTRFE_ERR_ARG, "hot_cache_build: bad argument");
   if (n == 0) return CTRFE_OK;
   DeviceGuard g(ctx->device);
-  const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+  const unsigned blocks = static_cast<unsigned>((n * 32 + 255) / 256);
   ctrfe::hot_insert_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const long long*>(hot_ids), n, keys, vals, (1u << log2_slots) - 1u, 32 - log2_slots);
+      reinterpret_cast<const long long*>(hot_ids), n, static_cast<const char*>(src_rows), static_cast<unsigned>(row_bytes),
+      keys, static_cast<char*>(rows), (1u << log2_slots) - 1u, 32 - log2_slots);
   CU(cudaGetLastError());
   return CTRFE_OK;
 }

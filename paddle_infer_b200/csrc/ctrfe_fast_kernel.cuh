@@ -92,7 +92,7 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
 #pragma unroll 1
         for (int pr = 0; pr < kHotProbes; ++pr) {
           const unsigned k = __ldg(kp.hot_keys + h);
-          if (k == lo) return kHotBit | __ldg(kp.hot_vals + h);
+          if (k == lo) return kHotBit | h;  // the replica lives at the hash slot itself
           if (k == 0xffffffffu) break;
           h = (h + 1u) & kp.hot_mask;
         }
@@ -201,20 +201,32 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
 }
 
-// Inserts hot_ids[i] -> i into the open-addressing hash of a hot-row cache.
-__global__ void hot_insert_kernel(const long long* __restrict__ hot_ids, long long n, unsigned* keys, unsigned* vals,
-                                  unsigned mask, int shift) {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+// Fills a hot-row cache: one warp per hot id claims a hash slot (open addressing, linear
+// probing) and copies the id's row from src_rows[i] to rows[slot].  An id that finds no free
+// slot within kHotProbes is left out.
+__global__ void hot_insert_kernel(const long long* __restrict__ hot_ids, long long n, const char* __restrict__ src_rows,
+                                  unsigned row_bytes, unsigned* keys, char* rows, unsigned mask, int shift) {
+  const long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   if (i >= n) return;
-  const long long id = hot_ids[i];
-  if (id < 0 || id >= 0x7fffffffLL) return;  // the hot bit needs row ids below 2^31
-  const unsigned lo = static_cast<unsigned>(id);
-  unsigned h = (lo * 2654435761u) >> shift;
-  for (int pr = 0; pr < kHotProbes; ++pr) {
-    const unsigned old = atomicCAS(keys + h, 0xffffffffu, lo);
-    if (old == 0xffffffffu || old == lo) { vals[h] = static_cast<unsigned>(i); return; }
-    h = (h + 1u) & mask;
+  const unsigned lane = threadIdx.x & 31u;
+  unsigned slot = 0xffffffffu;
+  if (lane == 0) {
+    const long long id = hot_ids[i];
+    if (id >= 0 && id < 0x7fffffffLL) {  // the hot bit needs row ids below 2^31
+      const unsigned lo = static_cast<unsigned>(id);
+      unsigned h = (lo * 2654435761u) >> shift;
+      for (int pr = 0; pr < kHotProbes; ++pr) {
+        const unsigned old = atomicCAS(keys + h, 0xffffffffu, lo);
+        if (old == 0xffffffffu || old == lo) { slot = h; break; }
+        h = (h + 1u) & mask;
+      }
+    }
   }
+  slot = __shfl_sync(0xffffffffu, slot, 0);
+  if (slot == 0xffffffffu) return;
+  const uint4* src = reinterpret_cast<const uint4*>(src_rows + static_cast<unsigned long long>(i) * row_bytes);
+  uint4* dst = reinterpret_cast<uint4*>(rows + static_cast<unsigned long long>(slot) * row_bytes);
+  for (unsigned c = lane; c < row_bytes / 16u; c += 32u) dst[c] = src[c];
 }
 
 }  // namespace ctrfe

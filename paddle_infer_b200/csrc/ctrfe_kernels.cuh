@@ -83,7 +83,6 @@ struct KParams {
   // hot-row replica cache of the sharded mode (ctrfe_hot_cache): null = none
   const char* hot_rows;
   const unsigned* hot_keys;
-  const unsigned* hot_vals;
   unsigned hot_mask;   // slots - 1
   int hot_shift;       // 32 - log2(slots)
   SlotK slots[kMaxSlotsPerLaunch];

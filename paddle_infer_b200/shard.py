@@ -259,15 +259,18 @@ class HotRowCache:
             rows = ops.ctr_fused_emb_seqpool_cvm(table, [hot_ids], [lod], "FIRST", use_cvm=None, ctx=ctx)[0]
         finally:
             table.hot = saved
-        self.rows = rows.contiguous()
-        log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.5))))
+        src = rows.contiguous()
+        log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.0))))   # load factor <= 0.5
         self.log2_slots = log2
         self.keys = torch.full((1 << log2,), -1, dtype=torch.int32, device=dev)
-        self.vals = torch.zeros((1 << log2,), dtype=torch.int32, device=dev)
-        B.check(B.lib().ctrfe_hot_cache_build(ctx.handle, hot_ids.data_ptr(), n, self.keys.data_ptr(),
-                                              self.vals.data_ptr(), log2, torch.cuda.current_stream(dev).cuda_stream))
+        # the replica of a row sits at its hash slot: a hit is one 4-byte probe, no index look-up
+        self.rows = torch.zeros((1 << log2, src.shape[1]), dtype=src.dtype, device=dev)
+        B.check(B.lib().ctrfe_hot_cache_build(ctx.handle, hot_ids.data_ptr(), n, src.data_ptr(),
+                                              src.shape[1] * src.element_size(), self.keys.data_ptr(),
+                                              self.rows.data_ptr(), log2, torch.cuda.current_stream(dev).cuda_stream))
         torch.cuda.synchronize(dev)
+        del src
         self.n_rows = n
         self.hot_ids = hot_ids
-        self.struct = B.HotCache(self.rows.data_ptr(), self.keys.data_ptr(), self.vals.data_ptr(), log2, n)
-        self.nbytes = self.rows.numel() * self.rows.element_size() + 8 * (1 << log2)
+        self.struct = B.HotCache(self.rows.data_ptr(), self.keys.data_ptr(), log2, n)
+        self.nbytes = self.rows.numel() * self.rows.element_size() + 4 * (1 << log2)
