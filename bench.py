@@ -261,6 +261,9 @@ def run_ours(args):
         raise SystemExit("bench.py needs a GPU: paddle_infer_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # pinned host buffers of the e2e leg should sit on the GPU's own NUMA node
+    from paddle_infer_b200 import affinity
+    prev_affinity = None if os.environ.get("CTRFE_NO_BIND") == "1" else affinity.bind_to_gpu(local_rank)
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
@@ -474,6 +477,8 @@ def run_ours(args):
                           "note": "requested bytes / time; above the link peak means L1 hits on repeated hot rows"}
     if local_G and hot_info is not None:
         line["config"]["hot_row_cache"] = hot_info
+    line["e2e"]["host_thread_bound_to_gpu_local_cpus"] = prev_affinity is not None
+    affinity.restore(prev_affinity)  # the CPU leg below gets every host core
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not local_G:
         tabs, hb4, rows = host_table_and_batches(cfg, synth, 4, torch, tables)
         line["cpu_baseline"] = cpu_leg(cfg, tabs, hb4, budget_s=args.cpu_budget)
@@ -502,10 +507,10 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows", type=int, default=0, help="diagnostic: override the table rows of the workload")
-    ap.add_argument("--hot-sample-batches", type=int, default=12)
+    ap.add_argument("--hot-sample-batches", type=int, default=96)
     ap.add_argument("--local-shards", type=int, default=0,
                     help="diagnostic, one GPU, cfg4: run the sharded kernel over this many shards on the same GPU")
-    ap.add_argument("--hot-rows", type=int, default=4_000_000,
+    ap.add_argument("--hot-rows", type=int, default=16_000_000,
                     help="sharded mode: rows replicated locally by the hot-row cache (0 = none)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
