@@ -393,7 +393,7 @@ void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) 
 }
 
 template <int DT>
-void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+void launch_fast_t(int gs, bool cvm, dim3 grid, int sm_count, cudaStream_t st, const ctrfe::KParams& p) {
   const bool sh = p.n_shards > 0;
   const bool hot = sh && p.hot_rows != nullptr;
   if (hot) {
@@ -410,9 +410,9 @@ int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
     const int m = plan.modes[c];
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
-        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
-        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
-        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c]); break;
+        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
+        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
+        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
       }
       continue;
     }

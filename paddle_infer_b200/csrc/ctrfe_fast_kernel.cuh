@@ -16,142 +16,16 @@
 
 namespace ctrfe {
 
-template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
-__global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
-fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
+// Epilogue shared by the specialised kernels: pad / scale / CVM / one 128-bit store per lane
+// (same arithmetic as the general kernel).  Every lane of the warp must call it (shuffles).
+template <int DT, int GS, bool CVM>
+__device__ __forceinline__ void finish_segment(const KParams& kp, const SlotK* slp, float (&acc)[Lane<DT, true, 16>::VEC],
+                                               int len, unsigned seg, unsigned gl, bool seg_ok) {
   using L = Lane<DT, true, 16>;
   constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
-  constexpr int U = kUnroll;
-  constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
-  constexpr int R = G * NI;               // rows consumed per step of the sequence loop
-  constexpr unsigned kRowShift = GS + 4;  // row_bytes = 16 << GS
-
-  __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
-  if constexpr (SHARDED) {
-    if (threadIdx.x < kMaxShards) s_shards[threadIdx.x] = reinterpret_cast<unsigned long long>(kp.shard_tables[threadIdx.x]);
-    __syncthreads();
-  }
-
-  const SlotK* const slp = &kp.slots[blockIdx.y];
-  const unsigned n_seg = slp->n_seg;
-  if (((blockIdx.x * static_cast<unsigned>(kThreads)) >> GS) >= n_seg) return;  // CTA past this slot's work
-  const unsigned seg = (blockIdx.x * static_cast<unsigned>(kThreads) + threadIdx.x) >> GS;
-  const unsigned gl = threadIdx.x & (G - 1);
-  const bool seg_ok = seg < n_seg;
-
-  uint32_t start = 0u, endo = 0u;
-  if (seg_ok) {
-    const unsigned* w = reinterpret_cast<const unsigned*>(slp->lod) + 2u * seg;  // low words: offsets < 2^32
-    start = __ldg(w);
-    endo = __ldg(w + 2);
-  }
-  const int len = static_cast<int>(endo - start);
-  const int maxlen = __reduce_max_sync(kFull, len);
-
-  const unsigned table_rows = slp->table_rows;
-  const bool ids_i32 = slp->id_kind == 1;
   const unsigned lane_off = gl * 16u;
-  const unsigned long long lane_base = reinterpret_cast<unsigned long long>(slp->table) + lane_off;
-  const unsigned shard_mask = SHARDED ? static_cast<unsigned>(kp.n_shards - 1) : 0u;
-  const int shard_shift = SHARDED ? kp.shard_shift : 0;
-
-  const unsigned long long hot_base = HOT ? reinterpret_cast<unsigned long long>(kp.hot_rows) + lane_off : 0ull;
-  auto row_ptr = [&](uint32_t rid) -> const char* {
-    if constexpr (HOT) {
-      if (rid & kHotBit)  // a local replica of a hot row
-        return reinterpret_cast<const char*>(hot_base + (static_cast<unsigned long long>(rid & ~kHotBit) << kRowShift));
-    }
-    if constexpr (SHARDED) {
-      return reinterpret_cast<const char*>(s_shards[rid & shard_mask] +
-                                           (static_cast<unsigned long long>(rid >> shard_shift) << kRowShift) + lane_off);
-    } else {
-      return reinterpret_cast<const char*>(lane_base + (static_cast<unsigned long long>(rid) << kRowShift));
-    }
-  };
-
-  // row index of the id at sequence position `off`, kSkip past the end or for a bad id
-  auto fetch_rid = [&](int off) -> uint32_t {
-    if (off >= len) return kSkip;
-    const unsigned pos = start + static_cast<unsigned>(off);
-    uint32_t lo, hi;
-    if (!ids_i32) {
-      const uint2 v = __ldg(reinterpret_cast<const uint2*>(slp->ids) + pos);
-      lo = v.x;
-      hi = v.y;
-    } else {
-      const int v = __ldg(reinterpret_cast<const int*>(slp->ids) + pos);
-      lo = static_cast<uint32_t>(v);
-      hi = static_cast<uint32_t>(v >> 31);
-    }
-    if (hi == 0u && lo < table_rows) {
-      if constexpr (HOT) {
-        // is there a local replica?  open addressing, linear probing, bounded probe count
-        unsigned h = (lo * 2654435761u) >> kp.hot_shift;
-#pragma unroll 1
-        for (int pr = 0; pr < kHotProbes; ++pr) {
-          const unsigned k = __ldg(kp.hot_keys + h);
-          if (k == lo) return kHotBit | h;  // the replica lives at the hash slot itself
-          if (k == 0xffffffffu) break;
-          h = (h + 1u) & kp.hot_mask;
-        }
-      }
-      return lo;
-    }
-    atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) | pos);
-    return kSkip;
-  };
-
-  float acc[VEC];
-#pragma unroll
-  for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
-
-  uint32_t cur[NI];
-#pragma unroll
-  for (int i = 0; i < NI; ++i) cur[i] = fetch_rid(i * G + static_cast<int>(gl));
-
-  for (int base = 0; base < maxlen; base += R) {
-    uint32_t nxt[NI];
-#pragma unroll
-    for (int i = 0; i < NI; ++i) nxt[i] = kSkip;
-    if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
-#pragma unroll
-      for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(base + R + i * G + static_cast<int>(gl));
-    }
-#pragma unroll
-    for (int c = 0; c < R / U; ++c) {
-      if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
-      uint32_t raw[U][RW];
-      bool ok[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int j = c * U + u;
-        const uint32_t rid = __shfl_sync(kFull, cur[j / G], j % G, G);
-        ok[u] = rid != kSkip;
-        if (ok[u]) L::load(row_ptr(rid), raw[u]);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (!ok[u]) continue;
-        if constexpr (ES == 4) {
-#pragma unroll
-          for (int e = 0; e < VEC; e += 2)
-            add_f32x2(acc[e], acc[e + 1], __uint_as_float(raw[u][e]), __uint_as_float(raw[u][e + 1]));
-        } else {
-#pragma unroll
-          for (int r = 0; r < RW; ++r) {
-            const float2 x = L::unpack2(raw[u][r]);
-            add_f32x2(acc[2 * r], acc[2 * r + 1], x.x, x.y);
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
-  }
-
-  // ---- epilogue: pad / scale / CVM / store (same arithmetic as the general kernel) ------
   const int pooltype = slp->pooltype;
   if (len == 0) {
 #pragma unroll
@@ -199,6 +73,178 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   }
   char* dst = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes + lane_off;
   *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+}
+
+// Where rows come from and how an id becomes a row index: the slot's table, the shards of a
+// row-sharded table, or the hot-row replicas.
+template <int DT, int GS, bool SHARDED, bool HOT>
+struct RowSource {
+  static constexpr unsigned kRowShift = GS + 4;  // row_bytes = 16 << GS
+  const KParams& kp;
+  const SlotK* slp;
+  const unsigned long long* s_shards;  // shared-memory copy of kp.shard_tables (SHARDED)
+  unsigned lane_off;
+  unsigned long long lane_base;
+  unsigned long long hot_base;
+
+  __device__ __forceinline__ RowSource(const KParams& kp_, const SlotK* slp_, const unsigned long long* sh, unsigned gl)
+      : kp(kp_), slp(slp_), s_shards(sh), lane_off(gl * 16u),
+        lane_base(reinterpret_cast<unsigned long long>(slp_->table) + gl * 16u),
+        hot_base(HOT ? reinterpret_cast<unsigned long long>(kp_.hot_rows) + gl * 16u : 0ull) {
+    // keep the lane's base address in registers: left alone, ptxas re-derives it from the
+    // parameter block in front of every row load (9 instructions per row)
+    asm volatile("" : "+l"(lane_base));
+  }
+
+  __device__ __forceinline__ const char* row_ptr(uint32_t rid) const {
+    if constexpr (HOT) {
+      if (rid & kHotBit)  // a local replica of a hot row
+        return reinterpret_cast<const char*>(hot_base + (static_cast<unsigned long long>(rid & ~kHotBit) << kRowShift));
+    }
+    if constexpr (SHARDED) {
+      const unsigned shard_mask = static_cast<unsigned>(kp.n_shards - 1);
+      return reinterpret_cast<const char*>(s_shards[rid & shard_mask] +
+                                           (static_cast<unsigned long long>(rid >> kp.shard_shift) << kRowShift) + lane_off);
+    } else {
+      return reinterpret_cast<const char*>(lane_base + (static_cast<unsigned long long>(rid) << kRowShift));
+    }
+  }
+
+  // row index of the id at position `pos` of the slot's id array; kSkip (and the error flag)
+  // for an id outside the table
+  __device__ __forceinline__ uint32_t resolve(unsigned pos) const {
+    uint32_t lo, hi;
+    if (slp->id_kind != 1) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(slp->ids) + pos);
+      lo = v.x;
+      hi = v.y;
+    } else {
+      const int v = __ldg(reinterpret_cast<const int*>(slp->ids) + pos);
+      lo = static_cast<uint32_t>(v);
+      hi = static_cast<uint32_t>(v >> 31);
+    }
+    if (hi == 0u && lo < slp->table_rows) {
+      if constexpr (HOT) {
+        // is there a local replica?  open addressing, linear probing, bounded probe count
+        unsigned h = (lo * 2654435761u) >> kp.hot_shift;
+#pragma unroll 1
+        for (int pr = 0; pr < kHotProbes; ++pr) {
+          const unsigned k = __ldg(kp.hot_keys + h);
+          if (k == lo) return kHotBit | h;  // the replica lives at the hash slot itself
+          if (k == 0xffffffffu) break;
+          h = (h + 1u) & kp.hot_mask;
+        }
+      }
+      return lo;
+    }
+    atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) | pos);
+    return kSkip;
+  }
+};
+
+// Adds U loaded rows into the accumulator, in order.
+template <int DT, int U>
+__device__ __forceinline__ void add_rows(float (&acc)[Lane<DT, true, 16>::VEC],
+                                         const uint32_t (&raw)[U][Lane<DT, true, 16>::RW], const bool (&ok)[U]) {
+  using L = Lane<DT, true, 16>;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (!ok[u]) continue;
+    if constexpr (L::ES == 4) {
+#pragma unroll
+      for (int e = 0; e < L::VEC; e += 2)
+        add_f32x2(acc[e], acc[e + 1], __uint_as_float(raw[u][e]), __uint_as_float(raw[u][e + 1]));
+    } else {
+#pragma unroll
+      for (int r = 0; r < L::RW; ++r) {
+        const float2 x = L::unpack2(raw[u][r]);
+        add_f32x2(acc[2 * r], acc[2 * r + 1], x.x, x.y);
+      }
+    }
+  }
+}
+
+// The warp-level row loop: lanes of a group fetch G consecutive ids with one request and
+// broadcast them with shuffles; the whole warp walks to its longest sequence.
+template <int DT, int GS, bool SHARDED, bool HOT>
+__device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDED, HOT>& src, uint32_t start, int len,
+                                                  unsigned gl, float (&acc)[Lane<DT, true, 16>::VEC]) {
+  using L = Lane<DT, true, 16>;
+  constexpr int RW = L::RW;
+  constexpr unsigned kFull = 0xffffffffu;
+  constexpr int G = 1 << GS;
+  constexpr int U = kUnroll;
+  constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
+  constexpr int R = G * NI;               // rows consumed per step of the sequence loop
+  const int maxlen = __reduce_max_sync(kFull, len);
+  auto fetch_rid = [&](int off) -> uint32_t {
+    return off < len ? src.resolve(start + static_cast<unsigned>(off)) : kSkip;
+  };
+  uint32_t cur[NI];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) cur[i] = fetch_rid(i * G + static_cast<int>(gl));
+
+  for (int base = 0; base < maxlen; base += R) {
+    uint32_t nxt[NI];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) nxt[i] = kSkip;
+    if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
+#pragma unroll
+      for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(base + R + i * G + static_cast<int>(gl));
+    }
+#pragma unroll
+    for (int c = 0; c < R / U; ++c) {
+      if (c > 0 && base + c * U >= maxlen) break;  // warp-uniform
+      uint32_t raw[U][RW];
+      bool ok[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = c * U + u;
+        const uint32_t rid = __shfl_sync(kFull, cur[j / G], j % G, G);
+        ok[u] = rid != kSkip;
+        if (ok[u]) L::load(src.row_ptr(rid), raw[u]);
+      }
+      add_rows<DT, U>(acc, raw, ok);
+    }
+#pragma unroll
+    for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
+  }
+}
+
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
+__global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
+fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
+  using L = Lane<DT, true, 16>;
+  constexpr int VEC = L::VEC;
+  constexpr int G = 1 << GS;
+
+  __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
+  if constexpr (SHARDED) {
+    if (threadIdx.x < kMaxShards) s_shards[threadIdx.x] = reinterpret_cast<unsigned long long>(kp.shard_tables[threadIdx.x]);
+    __syncthreads();
+  }
+
+  const SlotK* const slp = &kp.slots[blockIdx.y];
+  const unsigned n_seg = slp->n_seg;
+  if (((blockIdx.x * static_cast<unsigned>(kThreads)) >> GS) >= n_seg) return;  // CTA past this slot's work
+  const unsigned seg = (blockIdx.x * static_cast<unsigned>(kThreads) + threadIdx.x) >> GS;
+  const unsigned gl = threadIdx.x & (G - 1);
+  const bool seg_ok = seg < n_seg;
+
+  uint32_t start = 0u, endo = 0u;
+  if (seg_ok) {
+    const unsigned* w = reinterpret_cast<const unsigned*>(slp->lod) + 2u * seg;  // low words: offsets < 2^32
+    start = __ldg(w);
+    endo = __ldg(w + 2);
+  }
+  const int len = static_cast<int>(endo - start);
+
+  const RowSource<DT, GS, SHARDED, HOT> src(kp, slp, s_shards, gl);
+  float acc[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
+  pool_rows_by_warp<DT, GS, SHARDED, HOT>(src, start, len, gl, acc);
+  finish_segment<DT, GS, CVM>(kp, slp, acc, len, seg, gl, seg_ok);
 }
 
 // Fills a hot-row cache: one warp per hot id claims a hash slot (open addressing, linear
