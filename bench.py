@@ -447,7 +447,7 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": _traffic_from_profiles(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_mean": kern_ms, "kernel_ms_median": kern_ms_med,
-                     "frac_of_nominal_8000": achieved / 8000.0, "kernel": "ctrfe::fused_pool_kernel",
+                     "frac_of_nominal_8000": achieved / 8000.0, "kernel": "ctrfe::fused_pool_fast_kernel",
                      "random_row_ceiling_gbs": _random_row_ceiling(D * es),
                      "frac_of_random_row_ceiling": (achieved / _random_row_ceiling(D * es)) if _random_row_ceiling(D * es) else None,
                      "random_row_ceiling_note": "what a stripped uniform-random gather of rows this size sustains on this GPU "
