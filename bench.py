@@ -318,12 +318,14 @@ def run_ours(args):
     # from sample traffic drawn from the same distribution but DISJOINT from the timed batches.
     hot_info = None
     if (sharded or local_G) and args.hot_rows > 0:
-        sample = [synth.draw_batch(cfg, step=rank * 1000 + 500 + b, batch=Bsz) for b in range(args.hot_sample_batches)]
+        # the same amount of sample traffic per rank whatever the world size
+        n_sample = max(1, int(round(args.hot_sample_batches * (cfg.batch / 8) / Bsz)))
+        sample = [synth.draw_batch(cfg, step=rank * 1000 + 500 + b, batch=Bsz) for b in range(n_sample)]
         sample_ids = torch.cat([torch.from_numpy(i).to(dev) for sb in sample for i in sb.ids])
         hot_ids = shard_mod.pick_hot_ids(sample_ids, args.hot_rows)
         shard_table.hot = shard_mod.HotRowCache(shard_table, hot_ids)
         hot_info = {"rows": int(hot_ids.numel()), "bytes": int(shard_table.hot.nbytes),
-                    "built_from": f"{args.hot_sample_batches} sample batches per rank, disjoint from the timed batches"}
+                    "built_from": f"{n_sample} sample batches of {Bsz} per rank, disjoint from the timed batches"}
         del sample, sample_ids
         if world > 1:
             dist.barrier()
@@ -507,7 +509,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows", type=int, default=0, help="diagnostic: override the table rows of the workload")
-    ap.add_argument("--hot-sample-batches", type=int, default=96)
+    ap.add_argument("--hot-sample-batches", type=int, default=96,
+                    help="sample traffic for the hot set, in batches of 1/8 of the global batch, per rank")
     ap.add_argument("--local-shards", type=int, default=0,
                     help="diagnostic, one GPU, cfg4: run the sharded kernel over this many shards on the same GPU")
     ap.add_argument("--hot-rows", type=int, default=16_000_000,
