@@ -114,6 +114,23 @@ typedef struct ctrfe_hot_cache {
   int32_t n_rows;         /* replicas held (informational) */
 } ctrfe_hot_cache;
 
+/* Feasign key map: the `pull_box_sparse`-shaped front.  With a key map in the descriptor the
+ * slots' `ids` are uint64 feasign keys (stored as int64, operators/pull_box_sparse_op.h:36-40)
+ * and the kernel resolves each key to a table row itself, so keys -> values -> pooled rows is
+ * still one launch and the [K, D] values of pull_box_sparse are never written.  Key 0 reads as
+ * a zero row (framework/fleet/heter_ps/feature_value.cu:76-80, feature_value.h:498-514); so does
+ * a key the map does not hold (the reference's search leaves the value untouched,
+ * heter_ps/hashtable_kernel.cu:79-82).  Open addressing, linear probing, at most 32 probes,
+ * 0 = empty slot.  The parameter server that fills the reference's table is out of scope: the
+ * table here is the dense [n_keys, dim] image of its pull values (show, click, embed_w, mf). */
+typedef struct ctrfe_keymap {
+  const uint64_t* keys;   /* device [2^log2_slots]; 0 = empty */
+  const uint32_t* rows;   /* device [2^log2_slots]; table row of the key in the same slot */
+  int32_t log2_slots;
+  int32_t reserved;
+  int64_t n_keys;         /* keys held (informational) */
+} ctrfe_keymap;
+
 typedef struct ctrfe_fused_desc {
   int32_t n_slots;
   int32_t dtype;          /* CTRFE_F32 / F16 / BF16: storage type of tables and outputs;
@@ -144,6 +161,8 @@ typedef struct ctrfe_fused_desc {
                              itself with loads through the peer mapping, in sequence order */
   const struct ctrfe_hot_cache* hot_cache; /* sharded mode only, may be NULL: local replicas of the
                              most frequently looked-up rows (see ctrfe_hot_cache_build) */
+  const struct ctrfe_keymap* keymap; /* may be NULL: ids are uint64 feasign keys looked up in this
+                             map (not with sharded tables; ids_dtype must be CTRFE_I64) */
 } ctrfe_fused_desc;
 
 /* ---- library ------------------------------------------------------------------------ */
@@ -233,6 +252,14 @@ int ctrfe_shard_unmap(int device, void* ptr, uint64_t mapped_bytes);
  * is then always fetched from its shard).  Asynchronous on `stream`. */
 int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, const void* src_rows, int64_t row_bytes,
                           uint32_t* keys, void* rows, int32_t log2_slots, void* stream);
+
+/* Fills a ctrfe_keymap: keys[i] -> row i for i < n (distinct keys; key 0 is skipped).  map_keys
+ * must have been zeroed.  *n_unplaced (device, may be NULL) counts keys that found no slot
+ * within 32 probes: rebuild with a larger log2_slots if it is not 0.  Asynchronous on `stream`.
+ * Stands where the reference builds its per-GPU HashTable (heter_ps/hashtable_kernel.cu:216-235,
+ * insert). */
+int ctrfe_keymap_build(ctrfe_ctx* ctx, const uint64_t* keys, int64_t n, uint64_t* map_keys, uint32_t* map_rows,
+                       int32_t log2_slots, uint32_t* n_unplaced, void* stream);
 
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 

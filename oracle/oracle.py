@@ -258,6 +258,33 @@ def fused_forward(tables: Sequence[np.ndarray], ids: Sequence[np.ndarray], lods:
 
 
 # bf16 helpers for tests (numpy has no bfloat16): bit patterns in uint16
+def pull_sparse(keys: np.ndarray, values: np.ndarray, query: np.ndarray) -> np.ndarray:
+    """pull_box_sparse / pull_gpups_sparse restated (operators/pull_box_sparse_op.h:32-62 ->
+    PSGPUWrapper::PullSparse -> HashTable::get + PullCopy): out[k] = values[i] where
+    keys[i] == query[k]; key 0 gives a zero row ("0 key fill zero",
+    framework/fleet/heter_ps/feature_value.cu:76-80, feature_value.h:498-514); a key the table
+    does not hold gives a zero row too (hashtable_kernel.cu:79-82 leaves the value untouched;
+    zeros are this repo's definition).  keys / query: uint64 (or int64 views of them)."""
+    rows = pull_sparse_rows(keys, query, zero_row=values.shape[0])
+    padded = np.concatenate([values, np.zeros((1, values.shape[1]), values.dtype)])
+    return padded[rows]
+
+
+def pull_sparse_rows(keys: np.ndarray, query: np.ndarray, zero_row: int) -> np.ndarray:
+    """Row index of every queried feasign key (see pull_sparse); `zero_row` for key 0 and for
+    unknown keys."""
+    keys = np.ascontiguousarray(keys).view(np.uint64).reshape(-1)
+    query = np.ascontiguousarray(query).view(np.uint64).reshape(-1)
+    order = np.argsort(keys, kind="stable")
+    sk = keys[order]
+    pos = np.searchsorted(sk, query)
+    pos_c = np.minimum(pos, max(sk.size - 1, 0))
+    hit = (sk.size > 0) & (sk[pos_c] == query) & (query != 0) if sk.size else np.zeros(query.shape, bool)
+    rows = np.full(query.shape, zero_row, np.int64)
+    rows[hit] = order[pos_c[hit]]
+    return rows
+
+
 def f32_to_bf16_bits(a: np.ndarray) -> np.ndarray:
     """RNE float32 -> bfloat16 bit patterns (vectorised twin of orc_float_to_bf16)."""
     x = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)

@@ -32,12 +32,18 @@ class HotCache(C.Structure):
                 ("n_rows", C.c_int32)]
 
 
+class KeyMap(C.Structure):
+    _fields_ = [("keys", C.c_void_p), ("rows", C.c_void_p), ("log2_slots", C.c_int32), ("reserved", C.c_int32),
+                ("n_keys", C.c_int64)]
+
+
 class FusedDesc(C.Structure):
     _fields_ = [("n_slots", C.c_int32), ("dtype", C.c_int32), ("slots", C.POINTER(Slot)),
                 ("dim", C.c_int64), ("padding_idx", C.c_int64), ("pad_value", C.c_float),
                 ("cvm_mode", C.c_int32), ("cvm_offset", C.c_int32), ("scale_mode", C.c_int32),
                 ("init_mode", C.c_int32), ("lod_location", C.c_int32), ("n_shards", C.c_int32),
-                ("shard_tables", C.POINTER(C.c_void_p)), ("hot_cache", C.POINTER(HotCache))]
+                ("shard_tables", C.POINTER(C.c_void_p)), ("hot_cache", C.POINTER(HotCache)),
+                ("keymap", C.POINTER(KeyMap))]
 
 
 class CtrfeError(RuntimeError):
@@ -64,7 +70,7 @@ EXPORTS = [
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
-    "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build",
+    "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build", "ctrfe_keymap_build",
 ]
 
 
@@ -99,6 +105,7 @@ def lib():
         L.ctrfe_shard_alloc_fd.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
         L.ctrfe_shard_open_fd.argtypes = [C.c_int, C.c_int, C.c_uint64, C.POINTER(vp)]
         L.ctrfe_shard_unmap.argtypes = [C.c_int, vp, C.c_uint64]
+        L.ctrfe_keymap_build.argtypes = [vp, vp, i64, vp, vp, i32, vp, vp]
         L.ctrfe_hot_cache_build.argtypes = [vp, vp, i64, vp, i64, vp, vp, i32, vp]
         _lib = L
     return _lib

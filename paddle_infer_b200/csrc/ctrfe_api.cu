@@ -186,6 +186,15 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   } else if (d->hot_cache) {
     return fail(CTRFE_ERR_ARG, "fused: hot_cache is only meaningful in the sharded table mode");
   }
+  const ctrfe_keymap* km = d->keymap;
+  if (km) {
+    if (sharded) return fail(CTRFE_ERR_UNSUPPORTED, "fused: a key map cannot be combined with a sharded table");
+    if (!km->keys || !km->rows || km->log2_slots < 4 || km->log2_slots > 31)
+      return fail(CTRFE_ERR_ARG, "fused: malformed keymap");
+    for (int s = 0; s < d->n_slots; ++s)
+      if (!d->slots[s].ids || d->slots[s].ids_dtype != CTRFE_I64)
+        return fail(CTRFE_ERR_ARG, "slot %d: with a key map the ids are uint64 feasign keys (ids_dtype CTRFE_I64)", s);
+  }
   size_t lb = 0;
   for (int s = 0; s < d->n_slots; ++s) {
     const ctrfe_slot& sl = d->slots[s];
@@ -222,7 +231,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   {
     const char* nofast = getenv("CTRFE_NO_FAST");
     bool f = v && cb == 16 && row_bytes <= 512 && (row_bytes & (row_bytes - 1)) == 0 && d->padding_idx == -1 &&
-             d->init_mode == CTRFE_INIT_ZERO && d->cvm_mode != CTRFE_CVM_STRIP && !(nofast && nofast[0] == '1');
+             d->init_mode == CTRFE_INIT_ZERO && d->cvm_mode != CTRFE_CVM_STRIP && !km && !(nofast && nofast[0] == '1');
     for (int s = 0; f && s < d->n_slots; ++s) {
       const ctrfe_slot& sl = d->slots[s];
       if (!sl.ids || reinterpret_cast<uintptr_t>(sl.out) % 16 != 0 || (sl.out_ld * es) % 16 != 0) f = false;
@@ -275,6 +284,12 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
         k.hot_mask = (1u << d->hot_cache->log2_slots) - 1u;
         k.hot_shift = 32 - d->hot_cache->log2_slots;
       }
+      if (km) {
+        k.km_keys = reinterpret_cast<const unsigned long long*>(km->keys);
+        k.km_rows = km->rows;
+        k.km_mask = (1u << km->log2_slots) - 1u;
+        k.km_shift = 64 - km->log2_slots;
+      }
       if (sharded) {
         k.n_shards = d->n_shards;
         k.shard_shift = d->n_shards == 2 ? 1 : (d->n_shards == 4 ? 2 : 3);
@@ -294,7 +309,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     o.table_rows = static_cast<unsigned>(sl.table_rows);
     o.n_seg = static_cast<unsigned>(sl.n_seg);
     o.pooltype = static_cast<short>(sl.pooltype);
-    o.id_kind = static_cast<short>(sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2);
+    o.id_kind = static_cast<short>(km ? 3 : (sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2));
     o.slot_index = s;
     if (sl.n_seg > max_seg[c]) max_seg[c] = sl.n_seg;
   }
@@ -701,6 +716,20 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
 }
 
 
+int ctrfe_keymap_build(ctrfe_ctx* ctx, const uint64_t* keys, int64_t n, uint64_t* map_keys, uint32_t* map_rows,
+                       int32_t log2_slots, uint32_t* n_unplaced, void* stream) {
+  if (!ctx || !keys || !map_keys || !map_rows || n < 0 || n >= 0xfffffffeLL || log2_slots < 4 || log2_slots > 31)
+    return fail(CTRFE_ERR_ARG, "keymap_build: bad argument");
+  if (n == 0) return CTRFE_OK;
+  DeviceGuard g(ctx->device);
+  const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+  ctrfe::keymap_insert_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const unsigned long long*>(keys), n, reinterpret_cast<unsigned long long*>(map_keys), map_rows,
+      (1u << log2_slots) - 1u, 64 - log2_slots, n_unplaced);
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
 int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, const void* src_rows, int64_t row_bytes,
                           uint32_t* keys, void* rows, int32_t log2_slots, void* stream) {
   if (!ctx || !hot_ids || !src_rows || !keys || !rows || n < 0 || log2_slots < 4 || log2_slots > 30 || row_bytes <= 0 ||
@@ -962,6 +991,7 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
   if (d->init_mode < CTRFE_INIT_ZERO || d->init_mode > CTRFE_INIT_FIRST_ROW) return fail(CTRFE_ERR_ARG, "static: bad init_mode");
   if (d->lod_location != CTRFE_LOD_HOST) return fail(CTRFE_ERR_ARG, "static: LoD offsets must be passed from host memory");
   if (d->n_shards != 0) return fail(CTRFE_ERR_UNSUPPORTED, "static: the sharded table mode is not available here");
+  if (d->keymap) return fail(CTRFE_ERR_UNSUPPORTED, "static: feasign key maps are not available here");
 
   const int es = elem_size(d->dtype);
   const long long row_bytes = d->dim * es;

@@ -45,6 +45,8 @@ constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequenc
 constexpr uint32_t kZero = 0xfffffffeu;  // padding_idx / out-of-range id: contributes a zero row
 constexpr uint32_t kHotBit = 0x80000000u; // row index refers to the hot-row replica cache (sharded mode)
 constexpr int kHotProbes = 8;             // linear probes of the hot-row hash
+constexpr int kKeyProbes = 32;            // linear probes of the feasign key map
+constexpr unsigned long long kKeyHashMul = 0x9E3779B97F4A7C15ull;
 
 // Slot descriptor, passed BY VALUE in the kernel parameter block (constant bank): a CTA
 // reads its slot's pointers without a dependent global load.
@@ -57,7 +59,7 @@ struct SlotK {
   unsigned int table_rows;         // < 2^32 - 2
   unsigned int n_seg;
   short pooltype;
-  short id_kind;                   // 0 int64, 1 int32, 2 dense (row index = position)
+  short id_kind;                   // 0 int64, 1 int32, 2 dense (row index = position), 3 uint64 feasign keys (key map)
   int slot_index;                  // position in the caller's slot array (bad-id report)
 };
 
@@ -85,6 +87,11 @@ struct KParams {
   const unsigned* hot_keys;
   unsigned hot_mask;   // slots - 1
   int hot_shift;       // 32 - log2(slots)
+  // feasign key map (ctrfe_keymap): ids are uint64 keys, resolved to table rows in the kernel
+  const unsigned long long* km_keys;
+  const unsigned* km_rows;
+  unsigned km_mask;    // slots - 1
+  int km_shift;        // 64 - log2(slots)
   SlotK slots[kMaxSlotsPerLaunch];
 };
 static_assert(sizeof(KParams) <= 4096, "kernel parameter block must stay within 4 KB");
@@ -303,6 +310,25 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
   // host to raise so that the kernel itself never faults.
   auto fetch_rid = [&](unsigned long long a, int off) -> uint32_t {
     if (off >= len) return kSkip;
+    if (id_kind == 3) {
+      // a feasign key: key 0 reads as zeros ("0 key fill zero", heter_ps/feature_value.cu:76-80,
+      // feature_value.h:498-514); so does a key the map does not hold (the reference leaves the
+      // value untouched, hashtable_kernel.cu:79-82)
+      const unsigned long long key = __ldg(reinterpret_cast<const unsigned long long*>(a));
+      if (key == 0ull) return kZero;
+      unsigned h = static_cast<unsigned>((key * kKeyHashMul) >> kp.km_shift);
+#pragma unroll 1
+      for (int pr = 0; pr < kKeyProbes; ++pr) {
+        const unsigned long long k = __ldg(kp.km_keys + h);
+        if (k == key) {
+          const unsigned r = __ldg(kp.km_rows + h);
+          return r < table_rows ? r : kZero;
+        }
+        if (k == 0ull) break;
+        h = (h + 1u) & kp.km_mask;
+      }
+      return kZero;
+    }
     long long id;
     if (id_kind == 0) id = __ldg(reinterpret_cast<const long long*>(a));
     else if (id_kind == 1) id = static_cast<long long>(__ldg(reinterpret_cast<const int*>(a)));
@@ -641,6 +667,27 @@ __global__ void cvm_kernel(const char* __restrict__ x, long long rows, int width
   char* q = y + t * ES;
   if constexpr (ES == 4) *reinterpret_cast<uint32_t*>(q) = b;
   else *reinterpret_cast<unsigned short*>(q) = static_cast<unsigned short>(b);
+}
+
+// Fills a feasign key map: keys[i] -> row i.  Open addressing, linear probing, 0 = empty slot
+// (key 0 is the padding feasign and is never stored).  A key that finds no slot within
+// kKeyProbes is counted in *n_unplaced (the caller rebuilds with more slots).
+__global__ void keymap_insert_kernel(const unsigned long long* __restrict__ keys, long long n, unsigned long long* map_keys,
+                                     unsigned* map_rows, unsigned mask, int shift, unsigned* n_unplaced) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long key = keys[i];
+  if (key == 0ull) return;
+  unsigned h = static_cast<unsigned>((key * kKeyHashMul) >> shift);
+  for (int pr = 0; pr < kKeyProbes; ++pr) {
+    const unsigned long long old = atomicCAS(map_keys + h, 0ull, key);
+    if (old == 0ull || old == key) {
+      map_rows[h] = static_cast<unsigned>(i);
+      return;
+    }
+    h = (h + 1u) & mask;
+  }
+  if (n_unplaced) atomicAdd(n_unplaced, 1u);
 }
 
 }  // namespace ctrfe

@@ -253,7 +253,7 @@ class _TableRef:
 
 
 def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_value, padding_idx, cvm_mode,
-                cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None):
+                cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None, keymap=None):
     S = len(lods)
     slots = (B.Slot * S)()
     keep = []
@@ -282,6 +282,9 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
             desc.hot_cache = C.pointer(hot.struct)
             keep.append(hot)
         keep.append(sharded)
+    if keymap is not None:  # ids are uint64 feasign keys, resolved in the kernel (KeyMap)
+        desc.keymap = C.pointer(keymap.struct)
+        keep.append(keymap)
     keep.append(slots)
     return desc, keep
 
@@ -290,7 +293,8 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
                               pad_value: float = 0.0, padding_idx: int = -1, use_cvm: Optional[bool] = True,
                               cvm_offset: int = 2, concat: bool = False, scale_mode: int = B.SCALE_DIVIDE,
                               init_mode: int = B.INIT_ZERO, check: bool = True, plan_only: bool = False,
-                              out: Optional[torch.Tensor] = None, ctx: Optional[Context] = None):
+                              out: Optional[torch.Tensor] = None, ctx: Optional[Context] = None,
+                              keymap: Optional["KeyMap"] = None):
     """lookup_table_v2 -> sequence_pool -> cvm for every slot of a CTR batch in one launch.
 
     W         one table [N, D] shared by all slots, or a list with one table per slot, or a
@@ -304,6 +308,9 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
               None: no cvm op after the pool
     concat    write all slots into one [B, S*D_out] tensor (concat(axis=1) fused, as
               fusion_seqpool_cvm_concat does)
+    keymap    a KeyMap: Ids are then uint64 feasign keys (viewed as int64, as pull_box_sparse
+              takes them) and W holds one row per key of the map; key 0 and unknown keys pool
+              as zero rows
     Returns a list of [B_s, D_out] tensors, or the [B, S*D_out] tensor when concat=True;
     with plan_only=True returns a FusedPlan instead (nothing launched yet).
     """
@@ -352,7 +359,8 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
         ld = d_out
     desc, keep = _build_desc(tables, ids_c, lods, pools, outs, ld, dim=dim, dtype=_DT[t0.dtype],
                              pad_value=pad_value, padding_idx=padding_idx, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
-                             scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device, sharded=sharded)
+                             scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device, sharded=sharded,
+                             keymap=keymap)
     result = out if concat else outs
     if plan_only:
         h = C.c_void_p()
@@ -362,6 +370,48 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
     if check:
         ctx.check_ids()
     return result
+
+
+class KeyMap:
+    """uint64 feasign key -> table row, resident on the GPU (ctrfe_keymap): the lookup half of
+    the reference's per-GPU HashTable (framework/fleet/heter_ps/hashtable_kernel.cu), which
+    pull_box_sparse / pull_gpups_sparse consult.  keys[i] maps to row i of the value table the
+    caller keeps beside it; keys must be distinct and non-zero (0 is the padding feasign)."""
+
+    def __init__(self, keys: torch.Tensor, ctx: Optional[Context] = None):
+        _need_cuda(keys, "keys")
+        if keys.dtype != torch.int64:
+            raise InvalidArgument("feasign keys are uint64 values held in an int64 tensor")
+        keys = keys.contiguous().view(-1)
+        n = keys.numel()
+        ctx = ctx or default_context(keys.device)
+        log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.0))))  # load factor <= 0.5
+        while True:
+            if log2 > 31:
+                raise InvalidArgument("too many keys for one key map")
+            self.keys = torch.zeros(1 << log2, dtype=torch.int64, device=keys.device)
+            self.rows = torch.zeros(1 << log2, dtype=torch.int32, device=keys.device)
+            unplaced = torch.zeros(1, dtype=torch.int32, device=keys.device)
+            B.check(B.lib().ctrfe_keymap_build(ctx.handle, keys.data_ptr(), n, self.keys.data_ptr(), self.rows.data_ptr(),
+                                               log2, unplaced.data_ptr(), ctx.stream()))
+            if int(unplaced.item()) == 0:
+                break
+            log2 += 1  # a probe chain longer than the kernel follows: spread the keys out
+        self.log2_slots, self.n_keys = log2, n
+        self.struct = B.KeyMap(self.keys.data_ptr(), self.rows.data_ptr(), log2, 0, n)
+
+
+def pull_box_sparse(keymap: KeyMap, W: torch.Tensor, Ids: Sequence[torch.Tensor], *,
+                    ctx: Optional[Context] = None) -> List[torch.Tensor]:
+    """pull_box_sparse / pull_gpups_sparse over a resident table (operators/pull_box_sparse_op.h:
+    32-62, .cc:62-100): per slot, Ids [K_s(, 1)] uint64 feasign keys -> Out [K_s, D] with
+    D = W.shape[1] (the op's `size`); key 0 and unknown keys give zero rows.  One launch for all
+    slots.  The fused call (ctr_fused_emb_seqpool_cvm(..., keymap=...)) never writes these
+    values; this clone exists for programs that consume them elsewhere."""
+    flat = [i.contiguous().view(-1) for i in Ids]
+    lods = [torch.arange(i.numel() + 1, dtype=torch.int64, device=i.device) for i in flat]
+    outs = ctr_fused_emb_seqpool_cvm(W, flat, lods, "FIRST", use_cvm=None, keymap=keymap, ctx=ctx, check=False)
+    return [o.view(*i.shape[:1], W.shape[1]) for o, i in zip(outs, flat)]
 
 
 def _dense_slots(Xs, lods):

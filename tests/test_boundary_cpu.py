@@ -64,7 +64,9 @@ def test_python_enums_match_header(built):
 def test_struct_layouts_match_header(built):
     # ctrfe_slot: 7 x 8-byte fields + 2 x int32; ctrfe_fused_desc: see header
     assert C.sizeof(built.Slot) == 64
-    assert C.sizeof(built.FusedDesc) == 80 and built.FusedDesc.hot_cache.offset == 72
+    assert C.sizeof(built.FusedDesc) == 88 and built.FusedDesc.hot_cache.offset == 72
+    assert built.FusedDesc.keymap.offset == 80
+    assert C.sizeof(built.KeyMap) == 32 and built.KeyMap.n_keys.offset == 24
     assert C.sizeof(built.HotCache) == 24 and built.HotCache.log2_slots.offset == 16
     assert built.FusedDesc.slots.offset == 8 and built.FusedDesc.dim.offset == 16
     assert built.FusedDesc.pad_value.offset == 32 and built.FusedDesc.lod_location.offset == 52

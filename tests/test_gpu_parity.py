@@ -473,3 +473,53 @@ def test_host_front_end_modes(env):
         _assert_cvm_close(got2[:, s, :], want[s], True)
     with pytest.raises(ops.InvalidArgument, match="pinned"):
         fe.run([torch.from_numpy(i) for i in ids], lods_p)
+
+
+# ------------------------------------------------------------------ feasign key map (pull_box_sparse front)
+def test_feasign_keymap_pull_and_fused(env):
+    """uint64 feasign keys resolved inside the kernel: the standalone pull (values by key) is a
+    bit-copy, and keys -> pool -> CVM in one launch equals the oracle on the pulled values."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(2026)
+    n, D, S, Bsz = 200_000, 16, 5, 300
+    keys = np.unique(rng.integers(1, 2**64 - 1, n + 1000, dtype=np.uint64))[:n]
+    rng.shuffle(keys)
+    assert keys.size == n and (keys >> np.uint64(63)).any()   # some keys use the top bit
+    table = rng.uniform(-1, 1, (n, D)).astype(np.float32)
+    show = rng.integers(0, 16, n)
+    table[:, 0], table[:, 1] = show, rng.integers(0, show + 1)
+    km = ops.KeyMap(_t(keys.view(np.int64), dev))
+    assert km.n_keys == n and (1 << km.log2_slots) >= 2 * n
+    tt = _t(table, dev)
+    lods, qs = [], []
+    for s in range(S):
+        l = rng.integers(0, 9, Bsz)
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        q = keys[rng.integers(0, n, int(lod[-1]))].copy()
+        q[rng.random(q.size) < 0.05] = 0                                   # padding feasign
+        miss = rng.random(q.size) < 0.05
+        q[miss] = rng.integers(1, 2**64 - 1, int(miss.sum()), dtype=np.uint64)  # (almost surely) unknown keys
+        lods.append(lod)
+        qs.append(q)
+    q_t = [_t(q.view(np.int64), dev) for q in qs]
+    # the op on its own
+    pulled = ops.pull_box_sparse(km, tt, q_t)
+    for s in range(S):
+        np.testing.assert_array_equal(pulled[s].cpu().numpy().view(np.uint32), O.pull_sparse(keys, table, qs[s]).view(np.uint32))
+    # fused: keys -> rows -> pool -> CVM, nothing in between
+    padded = np.concatenate([table, np.zeros((1, D), np.float32)])
+    rows = [O.pull_sparse_rows(keys, q, zero_row=n) for q in qs]
+    pools = ["SUM", "AVERAGE", "MAX", "SQRT", "LAST"]
+    for use_cvm, cvm_mode in ((True, O.CVM_USE), (None, O.CVM_NONE)):
+        got = ops.ctr_fused_emb_seqpool_cvm(tt, q_t, lods, pools, use_cvm=use_cvm, keymap=km)
+        want = O.fused_forward([padded], rows, lods, pools, cvm_mode=cvm_mode)
+        for s in range(S):
+            _assert_cvm_close(got[s].cpu().numpy(), want[s], use_cvm is True)
+    # same values through PaddleBox's two-op form: pull, then fused_seqpool_cvm over the values
+    two_step = ops.fused_seqpool_cvm(pulled, [[l.tolist()] for l in lods], None, "SUM", 0.0, True)
+    one_step = ops.ctr_fused_emb_seqpool_cvm(tt, q_t, lods, "SUM", use_cvm=True, keymap=km)
+    for s in range(S):
+        assert torch.equal(two_step[s], one_step[s])
+    # int32 ids cannot be feasign keys; sharded tables cannot take a key map
+    with pytest.raises((ops.InvalidArgument, ValueError, RuntimeError)):
+        ops.ctr_fused_emb_seqpool_cvm(tt, [q.to(torch.int32) for q in q_t], lods, "SUM", keymap=km)

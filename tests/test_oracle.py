@@ -256,3 +256,15 @@ def test_fused_seqpool_cvm_paddlebox_mode():
     g = O.fused_forward([x], [np.arange(20, dtype=np.int64)], [lod], ["SUM"], pad_value=0.25,
                         init_mode=O.INIT_PAD, cvm_mode=O.CVM_STRIP)[0]
     np.testing.assert_array_equal(g, out2)
+
+
+def test_pull_sparse_restatement():
+    """pull_box_sparse semantics: values by key, zeros for key 0 and for unknown keys."""
+    keys = np.array([7, 2**63 + 5, 11, 3], dtype=np.uint64)
+    vals = np.arange(12, dtype=np.float32).reshape(4, 3) + 1
+    q = np.array([3, 0, 2**63 + 5, 999, 7, 7], dtype=np.uint64)
+    got = O.pull_sparse(keys, vals, q)
+    np.testing.assert_array_equal(got, np.stack([vals[3], np.zeros(3), vals[1], np.zeros(3), vals[0], vals[0]]))
+    # int64 views of the same bits (how Paddle holds feasigns) behave the same
+    np.testing.assert_array_equal(O.pull_sparse(keys.view(np.int64), vals, q.view(np.int64)), got)
+    assert O.pull_sparse(np.zeros(0, np.uint64), np.zeros((0, 3), np.float32), q).shape == (6, 3)
