@@ -394,9 +394,29 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p);
 }
 
+// Which rows take the balanced-load kernel: by default 128-byte rows (measured on B200: +42 % on
+// cfg3, -2 % on cfg4 where the gather already sits on the random-row DRAM ceiling; 64-byte rows
+// lose, the shared-memory staging costs them the L1 hits on the Zipf head).  Never for sharded
+// tables: with rows behind NVLink it measured 527 instead of 331 us per step on 2 GPUs.
+// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows (A/B runs).
+int bal_mode() {
+  static const int mode = [] {
+    const char* e = getenv("CTRFE_BAL");
+    return e && e[0] ? atoi(e) : 1;
+  }();
+  return mode;
+}
+
 template <int DT, bool CVM, bool SH, bool HOT>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
   using namespace ctrfe;
+  if (!SH && ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2))) {
+    // a warp takes kBalM times the segments it takes in the other kernels
+    const dim3 gb((grid.x + kBalM - 1) / kBalM, grid.y, 1);
+    if (gs == 2) fused_pool_bal_kernel<DT, 2, CVM, SH, HOT><<<gb, kThreads, 0, st>>>(p);
+    else fused_pool_bal_kernel<DT, 3, CVM, SH, HOT><<<gb, kThreads, 0, st>>>(p);
+    return;
+  }
   switch (gs) {
     case 0: fused_pool_fast_kernel<DT, 0, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
     case 1: fused_pool_fast_kernel<DT, 1, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;

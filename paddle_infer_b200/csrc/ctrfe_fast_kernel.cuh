@@ -247,6 +247,163 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   finish_segment<DT, GS, CVM>(kp, slp, acc, len, seg, gl, seg_ok);
 }
 
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(static_cast<unsigned>(__cvta_generic_to_shared(smem_dst))),
+               "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// ---- balanced loads -------------------------------------------------------------------------
+// In the kernel above a lane group walks ITS segment four rows at a time, so a warp runs to its
+// longest segment, about half of the row-load slots are empty with short ragged sequences
+// (mean 4, Poisson), and -- what ncu shows to matter most -- a warp's life is a chain of
+// dependent memory latencies (LoD -> ids -> rows -> rows ...) paid once per 32 / G segments.
+// Here a warp takes M * 32 / G adjacent segments.  Their ids are one contiguous run, loaded one
+// per lane with coalesced requests; the rows of the run are fetched in batches of up to
+// 4 * M * 32 / G, every lane group taking exactly its share whatever segment a row belongs to,
+// and they go straight from global to shared memory with cp.async (no registers tied up, all
+// of a batch in flight at once).  Each group then adds the rows of ITS M segments from shared
+// memory, in sequence order -- so the arithmetic and its order are unchanged and results stay
+// bit-identical -- and runs the epilogue M times.  Per warp: one LoD wait, one id wait and
+// ceil(rows / batch) row waits for M times the segments.
+#ifndef CTRFE_BAL_M
+#define CTRFE_BAL_M 2
+#endif
+#ifndef CTRFE_BAL_MINB
+#define CTRFE_BAL_MINB 6
+#endif
+constexpr int kBalM = CTRFE_BAL_M;  // segments per lane group
+
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
+__global__ void __launch_bounds__(kThreads, CTRFE_BAL_MINB)
+fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
+  using L = Lane<DT, true, 16>;
+  static_assert(GS == 2 || GS == 3, "64- and 128-byte rows");
+  constexpr int M = kBalM;
+  constexpr int VEC = L::VEC;
+  constexpr unsigned kFull = 0xffffffffu;
+  constexpr int G = 1 << GS;
+  constexpr int NG = 32 >> GS;        // lane groups per warp
+  constexpr int WS = NG * M;          // segments per warp
+  constexpr int U = kUnroll * M;      // rows in flight per lane
+  constexpr int RB = U * NG;          // rows per batch
+  constexpr int IPL = RB / 32 > 0 ? RB / 32 : 1;  // ids per lane per batch
+  constexpr int kWarps = kThreads / 32;
+  static_assert(WS + 1 <= 32 && RB % 32 == 0 || RB < 32, "one LoD offset per lane");
+
+  __shared__ uint4 s_rows_all[kWarps][U * 32];
+  __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
+  if constexpr (SHARDED) {
+    if (threadIdx.x < kMaxShards) s_shards[threadIdx.x] = reinterpret_cast<unsigned long long>(kp.shard_tables[threadIdx.x]);
+    __syncthreads();
+  }
+
+  const SlotK* const slp = &kp.slots[blockIdx.y];
+  const unsigned n_seg = slp->n_seg;
+  const unsigned wib = threadIdx.x >> 5;
+  const unsigned seg0 = (blockIdx.x * kWarps + wib) * WS;  // first segment of this warp
+  if (blockIdx.x * kWarps * WS >= n_seg) return;           // CTA past this slot's work
+  const unsigned lane = threadIdx.x & 31u;
+  uint4* const s_rows = s_rows_all[wib];
+  const unsigned g = lane >> GS;
+  const unsigned gl = lane & (G - 1);
+
+  // the WS + 1 offsets of the warp's segments, one per lane (low words: offsets < 2^32)
+  uint32_t my_off = 0u;
+  if (lane <= static_cast<unsigned>(WS)) {
+    const unsigned i = min(seg0 + lane, n_seg);
+    my_off = __ldg(reinterpret_cast<const unsigned*>(slp->lod) + 2u * i);
+  }
+  const uint32_t run0 = __shfl_sync(kFull, my_off, 0);
+  const uint32_t run1 = __shfl_sync(kFull, my_off, WS);
+
+  const RowSource<DT, GS, SHARDED, HOT> src(kp, slp, s_shards, gl);
+  float acc[M][VEC];
+#pragma unroll
+  for (int m = 0; m < M; ++m)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[m][e] = 0.0f;
+
+  // lane L holds the row indices of batch positions L, L + 32, ...
+  auto stage_ids = [&](uint32_t p0, uint32_t (&ids)[IPL]) {
+#pragma unroll
+    for (int i = 0; i < IPL; ++i) {
+      const uint32_t pos = p0 + i * 32u + lane;
+      ids[i] = (i * 32u + lane < static_cast<unsigned>(RB) && pos < run1) ? src.resolve(pos) : kSkip;
+    }
+  };
+  uint32_t cur[IPL];
+  stage_ids(run0, cur);
+#pragma unroll 1
+  for (uint32_t p0 = run0; p0 < run1; p0 += RB) {
+    uint32_t nxt[IPL];
+#pragma unroll
+    for (int i = 0; i < IPL; ++i) nxt[i] = kSkip;
+    if (p0 + RB < run1) stage_ids(p0 + RB, nxt);  // warp-uniform: more than one batch
+    __syncwarp();  // every lane is done reading the previous batch out of shared memory
+    // batch row r = u * NG + g is fetched by group g as its u-th row; a skipped row reads as zeros
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int r = u * NG + static_cast<int>(g);
+      const uint32_t rid = __shfl_sync(kFull, cur[(u * NG) / 32], r & 31);
+      uint4* const dst = s_rows + u * 32 + lane;
+      if (rid != kSkip) cp_async_16(dst, src.row_ptr(rid));
+      else *dst = make_uint4(0u, 0u, 0u, 0u);
+    }
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncwarp();
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      const uint32_t start = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m);
+      const uint32_t endo = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m + 1);
+      // rows of this segment that sit in the batch: batch positions [j0, j1)
+      const int j0 = static_cast<int>(max(start, p0) - p0);
+      const int j1 = static_cast<int>(min(endo, p0 + RB)) - static_cast<int>(p0);
+#pragma unroll 1
+      for (int j = j0; j < j1; j += 2) {
+        const uint4 a = s_rows[j * G + gl];
+        uint4 b = make_uint4(0u, 0u, 0u, 0u);
+        const bool two = j + 1 < j1;
+        if (two) b = s_rows[(j + 1) * G + gl];
+        const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wb[4] = {b.x, b.y, b.z, b.w};
+        if constexpr (L::ES == 4) {
+          add_f32x2(acc[m][0], acc[m][1], __uint_as_float(wa[0]), __uint_as_float(wa[1]));
+          add_f32x2(acc[m][2], acc[m][3], __uint_as_float(wa[2]), __uint_as_float(wa[3]));
+          if (two) {
+            add_f32x2(acc[m][0], acc[m][1], __uint_as_float(wb[0]), __uint_as_float(wb[1]));
+            add_f32x2(acc[m][2], acc[m][3], __uint_as_float(wb[2]), __uint_as_float(wb[3]));
+          }
+        } else {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const float2 x = L::unpack2(wa[r]);
+            add_f32x2(acc[m][2 * r], acc[m][2 * r + 1], x.x, x.y);
+          }
+          if (two) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const float2 x = L::unpack2(wb[r]);
+              add_f32x2(acc[m][2 * r], acc[m][2 * r + 1], x.x, x.y);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < IPL; ++i) cur[i] = nxt[i];
+  }
+#pragma unroll
+  for (int m = 0; m < M; ++m) {
+    const unsigned seg = seg0 + g * M + m;
+    const uint32_t start = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m);
+    const uint32_t endo = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m + 1);
+    finish_segment<DT, GS, CVM>(kp, slp, acc[m], static_cast<int>(endo - start), seg, gl, seg < n_seg);
+  }
+}
+
 // Fills a hot-row cache: one warp per hot id claims a hash slot (open addressing, linear
 // probing) and copies the id's row from src_rows[i] to rows[slot].  An id that finds no free
 // slot within kHotProbes is left out.
