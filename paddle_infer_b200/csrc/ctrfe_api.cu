@@ -411,10 +411,11 @@ template <int DT, bool CVM, bool SH, bool HOT>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
   using namespace ctrfe;
   if (!SH && ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2))) {
-    // a warp takes kBalM times the segments it takes in the other kernels
-    const dim3 gb((grid.x + kBalM - 1) / kBalM, grid.y, 1);
-    if (gs == 2) fused_pool_bal_kernel<DT, 2, CVM, SH, HOT><<<gb, kThreads, 0, st>>>(p);
-    else fused_pool_bal_kernel<DT, 3, CVM, SH, HOT><<<gb, kThreads, 0, st>>>(p);
+    // a warp takes M times the segments it takes in the other kernels
+    const int m = gs == 2 ? kBalM64 : kBalM128;
+    const dim3 gb((grid.x + m - 1) / m, grid.y, 1);
+    if (gs == 2) fused_pool_bal_kernel<DT, 2, CVM, SH, HOT, kBalM64><<<gb, kThreads, 0, st>>>(p);
+    else fused_pool_bal_kernel<DT, 3, CVM, SH, HOT, kBalM128><<<gb, kThreads, 0, st>>>(p);
     return;
   }
   switch (gs) {

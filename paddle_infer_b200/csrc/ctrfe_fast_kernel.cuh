@@ -268,26 +268,38 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // memory, in sequence order -- so the arithmetic and its order are unchanged and results stay
 // bit-identical -- and runs the epilogue M times.  Per warp: one LoD wait, one id wait and
 // ceil(rows / batch) row waits for M times the segments.
+// Measured on B200 (profiles/README.md): cfg3 (128-byte bf16 rows) 328 -> 231 us with M = 2 and
+// eight rows in flight per lane; four in flight: 257 us; M = 1: 247 us.  64-byte rows (cfg2) lose
+// 10-18 % in every variant -- the staging buffers take the L1 capacity that serves the Zipf
+// head -- and rows behind NVLink lose more, so the host uses this kernel for unsharded
+// 128-byte rows only.
 #ifndef CTRFE_BAL_M
 #define CTRFE_BAL_M 2
+#endif
+#ifndef CTRFE_BAL_M64
+#define CTRFE_BAL_M64 CTRFE_BAL_M
 #endif
 #ifndef CTRFE_BAL_MINB
 #define CTRFE_BAL_MINB 6
 #endif
-constexpr int kBalM = CTRFE_BAL_M;  // segments per lane group
+constexpr int kBalM128 = CTRFE_BAL_M;   // segments per lane group, 128-byte rows
+constexpr int kBalM64 = CTRFE_BAL_M64;  // 64-byte rows
 
-template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT, int M>
 __global__ void __launch_bounds__(kThreads, CTRFE_BAL_MINB)
 fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
   using L = Lane<DT, true, 16>;
   static_assert(GS == 2 || GS == 3, "64- and 128-byte rows");
-  constexpr int M = kBalM;
   constexpr int VEC = L::VEC;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
   constexpr int NG = 32 >> GS;        // lane groups per warp
   constexpr int WS = NG * M;          // segments per warp
+#ifdef CTRFE_BAL_U
+  constexpr int U = CTRFE_BAL_U;
+#else
   constexpr int U = kUnroll * M;      // rows in flight per lane
+#endif
   constexpr int RB = U * NG;          // rows per batch
   constexpr int IPL = RB / 32 > 0 ? RB / 32 : 1;  // ids per lane per batch
   constexpr int kWarps = kThreads / 32;
