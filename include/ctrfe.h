@@ -198,6 +198,14 @@ int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stre
  * buffers it names must stay valid) and on any stream ordered after the create stream. */
 int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream, ctrfe_plan** out);
 int ctrfe_plan_launch(ctrfe_plan* plan, void* stream);
+/* ctrfe_plan_launch with flags.  CTRFE_LAUNCH_OVERLAP_PREVIOUS: the caller states that this
+ * launch does not consume what the kernel immediately before it in `stream` produces (typical:
+ * back-to-back batches of a serving loop); the grid may then start while that kernel is
+ * draining (programmatic dependent launch), which hides the tail of a launch -- 15-20 % of a
+ * cfg2 step.  Everything later in the stream still waits for both kernels.  Without the flag
+ * the launch is an ordinary stream-ordered one.  No reference counterpart. */
+enum { CTRFE_LAUNCH_OVERLAP_PREVIOUS = 1 };
+int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags);
 int ctrfe_plan_destroy(ctrfe_plan* plan);
 /* Number of kernels one ctrfe_plan_launch enqueues (for launch accounting). */
 int ctrfe_plan_num_kernels(const ctrfe_plan* plan);

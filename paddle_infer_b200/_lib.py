@@ -52,6 +52,9 @@ class CtrfeError(RuntimeError):
         self.code = code
 
 
+LAUNCH_OVERLAP_PREVIOUS = 1
+
+
 class BadIdError(CtrfeError, ValueError):
     """InvalidArgument of the reference's embedding bounds check
     (paddle/phi/kernels/cpu/embedding_kernel.cc:59-76)."""
@@ -66,7 +69,7 @@ _lib = None
 # every symbol include/ctrfe.h declares (tests check the .so exports each one)
 EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
-    "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_destroy",
+    "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
@@ -91,6 +94,7 @@ def lib():
         L.ctrfe_fused_forward.argtypes = [vp, C.POINTER(FusedDesc), vp]
         L.ctrfe_plan_create.argtypes = [vp, C.POINTER(FusedDesc), vp, C.POINTER(vp)]
         L.ctrfe_plan_launch.argtypes = [vp, vp]
+        L.ctrfe_plan_launch_ex.argtypes = [vp, vp, C.c_uint32]
         L.ctrfe_plan_destroy.argtypes = [vp]
         L.ctrfe_plan_num_kernels.argtypes = [vp]
         L.ctrfe_embedding.argtypes = [vp, vp, i64, i64, vp, i32, i64, i64, vp, vp]

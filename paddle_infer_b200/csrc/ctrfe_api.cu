@@ -407,48 +407,69 @@ int bal_mode() {
   return mode;
 }
 
+// One launch of a specialised kernel; `overlap` adds the programmatic-stream-serialization
+// attribute, so the grid may start while the kernel before it in the stream is draining.
+template <class K>
+void launch_k(K kernel, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
+  if (!overlap) {
+    kernel<<<grid, ctrfe::kThreads, 0, st>>>(p);
+    return;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(ctrfe::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 template <int DT, bool CVM, bool SH, bool HOT>
-void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
+void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   using namespace ctrfe;
   if (!SH && ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2))) {
     // a warp takes M times the segments it takes in the other kernels
     const int m = gs == 2 ? kBalM64 : kBalM128;
     const dim3 gb((grid.x + m - 1) / m, grid.y, 1);
-    if (gs == 2) fused_pool_bal_kernel<DT, 2, CVM, SH, HOT, kBalM64><<<gb, kThreads, 0, st>>>(p);
-    else fused_pool_bal_kernel<DT, 3, CVM, SH, HOT, kBalM128><<<gb, kThreads, 0, st>>>(p);
+    if (gs == 2) launch_k(fused_pool_bal_kernel<DT, 2, CVM, SH, HOT, kBalM64>, gb, st, p, overlap);
+    else launch_k(fused_pool_bal_kernel<DT, 3, CVM, SH, HOT, kBalM128>, gb, st, p, overlap);
     return;
   }
   switch (gs) {
-    case 0: fused_pool_fast_kernel<DT, 0, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
-    case 1: fused_pool_fast_kernel<DT, 1, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
-    case 2: fused_pool_fast_kernel<DT, 2, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
-    case 3: fused_pool_fast_kernel<DT, 3, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
-    case 4: fused_pool_fast_kernel<DT, 4, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
-    default: fused_pool_fast_kernel<DT, 5, CVM, SH, HOT><<<grid, kThreads, 0, st>>>(p); break;
+    case 0: launch_k(fused_pool_fast_kernel<DT, 0, CVM, SH, HOT>, grid, st, p, overlap); break;
+    case 1: launch_k(fused_pool_fast_kernel<DT, 1, CVM, SH, HOT>, grid, st, p, overlap); break;
+    case 2: launch_k(fused_pool_fast_kernel<DT, 2, CVM, SH, HOT>, grid, st, p, overlap); break;
+    case 3: launch_k(fused_pool_fast_kernel<DT, 3, CVM, SH, HOT>, grid, st, p, overlap); break;
+    case 4: launch_k(fused_pool_fast_kernel<DT, 4, CVM, SH, HOT>, grid, st, p, overlap); break;
+    default: launch_k(fused_pool_fast_kernel<DT, 5, CVM, SH, HOT>, grid, st, p, overlap); break;
   }
 }
 
 template <int DT>
-void launch_fast_t(int gs, bool cvm, dim3 grid, int sm_count, cudaStream_t st, const ctrfe::KParams& p) {
+void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   const bool sh = p.n_shards > 0;
   const bool hot = sh && p.hot_rows != nullptr;
   if (hot) {
-    if (cvm) launch_fast_g<DT, true, true, true>(gs, grid, st, p); else launch_fast_g<DT, false, true, true>(gs, grid, st, p);
+    if (cvm) launch_fast_g<DT, true, true, true>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, true, true>(gs, grid, st, p, overlap);
   } else if (cvm) {
-    if (sh) launch_fast_g<DT, true, true, false>(gs, grid, st, p); else launch_fast_g<DT, true, false, false>(gs, grid, st, p);
+    if (sh) launch_fast_g<DT, true, true, false>(gs, grid, st, p, overlap); else launch_fast_g<DT, true, false, false>(gs, grid, st, p, overlap);
   } else {
-    if (sh) launch_fast_g<DT, false, true, false>(gs, grid, st, p); else launch_fast_g<DT, false, false, false>(gs, grid, st, p);
+    if (sh) launch_fast_g<DT, false, true, false>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, false, false>(gs, grid, st, p, overlap);
   }
 }
 
-int launch_plan(const ctrfe_plan& plan, cudaStream_t st) {
+int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap = false) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
     const int m = plan.modes[c];
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
-        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
-        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
-        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], plan.ctx ? plan.ctx->sm_count : 148, st, plan.chunks[c]); break;
+        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
+        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
+        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
       }
       continue;
     }
@@ -589,6 +610,17 @@ int ctrfe_plan_launch(ctrfe_plan* plan, void* stream) {
     plan->ctx->last_ids_owner = plan;
   }
   return launch_plan(*plan, static_cast<cudaStream_t>(stream));
+}
+
+int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags) {
+  if (!plan) return fail(CTRFE_ERR_ARG, "plan_launch_ex: null plan");
+  if (flags & ~static_cast<uint32_t>(CTRFE_LAUNCH_OVERLAP_PREVIOUS)) return fail(CTRFE_ERR_ARG, "plan_launch_ex: unknown flag");
+  DeviceGuard g(plan->ctx->device);
+  if (plan->ctx->last_ids_owner != plan) {
+    plan->ctx->last_ids = plan->id_src;
+    plan->ctx->last_ids_owner = plan;
+  }
+  return launch_plan(*plan, static_cast<cudaStream_t>(stream), (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0);
 }
 
 int ctrfe_plan_destroy(ctrfe_plan* plan) {

@@ -16,6 +16,11 @@
 
 namespace ctrfe {
 
+// Programmatic dependent launch: lets a kernel that was launched with the overlap flag
+// (ctrfe_plan_launch_ex, CTRFE_LAUNCH_OVERLAP_PREVIOUS) start filling SMs as soon as every CTA
+// of this grid has been scheduled, i.e. during this grid's tail.  A no-op otherwise.
+__device__ __forceinline__ void launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Epilogue shared by the specialised kernels: pad / scale / CVM / one 128-bit store per lane
 // (same arithmetic as the general kernel).  Every lane of the warp must call it (shuffles).
 template <int DT, int GS, bool CVM>
@@ -214,6 +219,7 @@ __device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDE
 template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
 __global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
 fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
+  launch_dependents();
   using L = Lane<DT, true, 16>;
   constexpr int VEC = L::VEC;
   constexpr int G = 1 << GS;
@@ -288,6 +294,7 @@ constexpr int kBalM64 = CTRFE_BAL_M64;  // 64-byte rows
 template <int DT, int GS, bool CVM, bool SHARDED, bool HOT, int M>
 __global__ void __launch_bounds__(kThreads, CTRFE_BAL_MINB)
 fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
+  launch_dependents();
   using L = Lane<DT, true, 16>;
   static_assert(GS == 2 || GS == 3, "64- and 128-byte rows");
   constexpr int VEC = L::VEC;

@@ -224,8 +224,13 @@ class FusedPlan:
     def __init__(self, ctx: Context, handle, outs, keep):
         self.ctx, self.handle, self.outs, self._keep = ctx, handle, outs, keep
 
-    def launch(self) -> None:
-        B.check(B.lib().ctrfe_plan_launch(self.handle, self.ctx.stream()))
+    def launch(self, overlap_previous: bool = False) -> None:
+        """overlap_previous=True: this launch does not consume the output of the kernel right
+        before it in the stream (back-to-back batches), so it may start while that one drains."""
+        if overlap_previous:
+            B.check(B.lib().ctrfe_plan_launch_ex(self.handle, self.ctx.stream(), B.LAUNCH_OVERLAP_PREVIOUS))
+        else:
+            B.check(B.lib().ctrfe_plan_launch(self.handle, self.ctx.stream()))
 
     def num_kernels(self) -> int:
         return B.lib().ctrfe_plan_num_kernels(self.handle)

@@ -523,3 +523,38 @@ def test_feasign_keymap_pull_and_fused(env):
     # int32 ids cannot be feasign keys; sharded tables cannot take a key map
     with pytest.raises((ops.InvalidArgument, ValueError, RuntimeError)):
         ops.ctr_fused_emb_seqpool_cvm(tt, [q.to(torch.int32) for q in q_t], lods, "SUM", keymap=km)
+
+
+def test_overlapped_plan_launches_equal_plain_ones(env):
+    """ctrfe_plan_launch_ex(CTRFE_LAUNCH_OVERLAP_PREVIOUS): a burst of launches over independent
+    batches, each allowed to start while the previous one drains, writes the same bits as
+    ordinary stream-ordered launches."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(77)
+    S, Bsz, N, D = 8, 3000, 20000, 16
+    table, _, _ = _random_case(rng, 1, 1, N, D, 1, "f32")
+    tt = _t(table, dev)
+    plans, wants = [], []
+    for b in range(6):
+        _, ids, lods = _random_case(rng, S, Bsz, N, D, 9, "f32")
+        ids_t = [_t(i, dev) for i in ids]
+        lods_t = [_t(l.astype(np.int64), dev) for l in lods]
+        plans.append(ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods_t, "SUM", use_cvm=True, concat=True, plan_only=True))
+        wants.append((ids, lods))
+    for p in plans:
+        p.launch()
+    torch.cuda.synchronize()
+    plain = [p.outs.clone() for p in plans]
+    for p in plans:
+        p.outs.zero_()
+    for rep in range(3):
+        for p in plans:
+            p.launch(overlap_previous=True)
+    plans[0].ctx.check_ids()
+    for p, ref in zip(plans, plain):
+        assert torch.equal(p.outs, ref)
+    ids, lods = wants[0]
+    want = O.fused_forward([table], ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE, concat=True)
+    _assert_cvm_close(plans[0].outs.cpu().numpy().reshape(Bsz, S, D), want.reshape(Bsz, S, D), True)
+    with pytest.raises(B.CtrfeError):
+        B.check(B.lib().ctrfe_plan_launch_ex(plans[0].handle, plans[0].ctx.stream(), 2))
