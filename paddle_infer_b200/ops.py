@@ -643,3 +643,19 @@ class BoundHostCall:
         self.plan.launch()
         self._stream.synchronize()
         return self.fe._result()
+
+    def submit(self, overlap_previous: bool = False):
+        """Asynchronous half of run(): enqueue the launch and return a CUDA event that fires when
+        the pooled rows are in the pinned host output.  A serving loop that keeps two requests
+        in flight (each bound to its own HostFrontEnd, hence its own output block) submits
+        request i+1 before waiting for request i, so the PCIe reads of one overlap the PCIe
+        writes of the other; overlap_previous=True additionally lets the kernel start while the
+        previous request's kernel drains (the requests are independent)."""
+        self.plan.launch(overlap_previous)
+        done = torch.cuda.Event()
+        done.record(self._stream)
+        return done
+
+    def result(self, done):
+        done.synchronize()
+        return self.fe._result()

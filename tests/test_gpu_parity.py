@@ -466,6 +466,16 @@ def test_host_front_end_modes(env):
     want0 = O.fused_forward([table], [np.roll(ids[0], 1)], [lods[0]], ["SUM"], cvm_mode=O.CVM_USE)[0]
     _assert_cvm_close(call.run()[0].numpy(), want0, True)
     ids_p[0].copy_(torch.from_numpy(ids[0]))
+    # asynchronous form: submit() now, result() later, two requests in flight on two front ends
+    fe_b = ops.HostFrontEnd(tt, S, Bsz, max_ids, "SUM", use_cvm=True, mode="zero_copy")
+    call_b = fe_b.bind(ids_p, lods_p)
+    fe.host_out.zero_()
+    ev_a = call.submit()
+    ev_b = call_b.submit(overlap_previous=True)
+    got_a, got_b = call.result(ev_a), call_b.result(ev_b)
+    for s in range(S):
+        _assert_cvm_close(got_a[s].numpy(), want[s], True)
+        assert torch.equal(got_a[s], got_b[s])
     # explicit-copy mode, concat layout
     fe2 = ops.HostFrontEnd(tt, S, Bsz, max_ids, "SUM", use_cvm=True, mode="copy", concat=True)
     got2 = fe2.run(ids_p, lods, check=True).numpy().reshape(Bsz, S, D)
