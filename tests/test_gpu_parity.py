@@ -412,6 +412,56 @@ def test_config3_reduced_rows(env):
     _run_config(env, synth.configs()["cfg3"], batch=4096, rows=1_000_000, sample=256)
 
 
+def test_config4_reduced_rows_one_gpu(env):
+    """The sharded config's shape on one GPU: fp32 D=32 (128-byte rows), SUM + CVM; rows cut to
+    2e6, batch to 4096.  Takes the balanced-load kernel."""
+    from benchtools import synth
+    _run_config(env, synth.configs()["cfg4"], batch=4096, rows=2_000_000, sample=512)
+
+
+@pytest.mark.parametrize("dtype,D", [("f32", 32), ("f16", 64), ("bf16", 64), ("f32", 16)])
+def test_specialised_kernels_ragged_long_and_bad(env, dtype, D):
+    """The specialised kernels (128-byte rows: balanced loads through shared memory; 64-byte
+    rows: warp-level loop) on shapes the configs do not have: segment counts that do not fill
+    a warp or a CTA, runs of ids longer than one batch (a 300-row and a 70-row segment among
+    short ones), all-empty slots, int32 ids, and a bad id in the middle of a long run."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(D * 131 + len(dtype))
+    N, S = 3000, 5
+    table, _, _ = _random_case(rng, 1, 1, N, D, 1, dtype)
+    bf16 = dtype == "bf16"
+    tt = _t(table, dev, bf16)
+    lods, ids = [], []
+    for s, n_seg in enumerate([1, 7, 29, 333, 64]):
+        l = rng.integers(0, 9, n_seg)
+        if n_seg > 20:
+            l[3], l[n_seg - 2] = 300, 70
+        if s == 4:
+            l[:] = 0
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        lods.append(lod)
+        ids.append(rng.integers(0, N, int(lod[-1])).astype(np.int64))
+    pools = ["SUM", "AVERAGE", "SQRT", "SUM", "SUM"]
+    for use_cvm, cvm_mode in ((True, O.CVM_USE), (None, O.CVM_NONE)):
+        for as_i32 in (False, True):
+            ids_t = [_t(i.astype(np.int32) if as_i32 else i, dev) for i in ids]
+            got = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods, pools, pad_value=0.5, use_cvm=use_cvm)
+            want = O.fused_forward([table], ids, lods, pools, pad_value=0.5, cvm_mode=cvm_mode, bf16=bf16)
+            for s in range(S):
+                g, w = _np(got[s]), want[s]
+                assert g.shape == w.shape
+                if dtype == "f32":
+                    _assert_cvm_close(g, w, use_cvm is True)
+                else:
+                    np.testing.assert_array_equal(g, w)
+    bad = [i.copy() for i in ids]
+    pos = int(lods[3][3]) + 150   # inside the 300-row segment
+    bad[3][pos] = N + 5
+    with pytest.raises(ValueError) as e:
+        ops.ctr_fused_emb_seqpool_cvm(tt, [_t(i, dev) for i in bad], lods, pools, use_cvm=None)
+    assert e.value.slot == 3 and e.value.position == pos and e.value.id_value == N + 5
+
+
 def test_config5_long_sequences(env):
     """8 slots x avg 200 ids, D=128 fp16, MAX and SQRT; rows cut to 2e6 per table."""
     from benchtools import synth
