@@ -234,7 +234,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
              d->init_mode == CTRFE_INIT_ZERO && d->cvm_mode != CTRFE_CVM_STRIP && !km && !(nofast && nofast[0] == '1');
     for (int s = 0; f && s < d->n_slots; ++s) {
       const ctrfe_slot& sl = d->slots[s];
-      if (!sl.ids || reinterpret_cast<uintptr_t>(sl.out) % 16 != 0 || (sl.out_ld * es) % 16 != 0) f = false;
+      if (!sl.ids || sl.ids_dtype != CTRFE_I64 || reinterpret_cast<uintptr_t>(sl.out) % 16 != 0 || (sl.out_ld * es) % 16 != 0) f = false;
     }
     plan->fast = f;
     plan->cvm_use = d->cvm_mode == CTRFE_CVM_USE;

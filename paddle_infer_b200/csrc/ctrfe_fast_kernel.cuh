@@ -3,7 +3,7 @@
 //   * rows are exactly 16 * G bytes (G = 1..32 lanes, a power of two) and 16-byte aligned,
 //     outputs 16-byte aligned: every lane always holds a valid 128-bit chunk;
 //   * SUM / AVERAGE / SQRT slots, accumulator starts at zero, no padding_idx;
-//   * ids present (int64 or int32); CVM on or absent.
+//   * ids present, int64; CVM on or absent.
 // ncu showed the general kernel bound by warp-instruction issue (profiles/README.md); here the
 // row width is a compile-time constant and every per-row decision that the general kernel
 // takes at run time (zero rows, first-row copy, column masks, tiles) is gone:
@@ -118,16 +118,10 @@ struct RowSource {
   // row index of the id at position `pos` of the slot's id array; kSkip (and the error flag)
   // for an id outside the table
   __device__ __forceinline__ uint32_t resolve(unsigned pos) const {
-    uint32_t lo, hi;
-    if (slp->id_kind != 1) {
-      const uint2 v = __ldg(reinterpret_cast<const uint2*>(slp->ids) + pos);
-      lo = v.x;
-      hi = v.y;
-    } else {
-      const int v = __ldg(reinterpret_cast<const int*>(slp->ids) + pos);
-      lo = static_cast<uint32_t>(v);
-      hi = static_cast<uint32_t>(v >> 31);
-    }
+    // int64 ids only: slots with int32 ids take the general kernel (the per-fetch test of the
+    // id width cost 3 % on cfg2)
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(slp->ids) + pos);
+    const uint32_t lo = v.x, hi = v.y;
     if (hi == 0u && lo < slp->table_rows) {
       if constexpr (HOT) {
         // is there a local replica?  open addressing, linear probing, bounded probe count
