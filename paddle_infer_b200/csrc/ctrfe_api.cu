@@ -361,53 +361,7 @@ int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_i
   return CTRFE_OK;
 }
 
-template <int DT, int MODE, int CB, bool SH>
-void launch_fused_tm(bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
-  using namespace ctrfe;
-  if (!vect) { fused_pool_kernel<DT, false, 5, MODE, 16, false><<<grid, kThreads, 0, st>>>(p); return; }
-  switch (gs) {
-    case 0: fused_pool_kernel<DT, true, 0, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 1: fused_pool_kernel<DT, true, 1, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 2: fused_pool_kernel<DT, true, 2, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 3: fused_pool_kernel<DT, true, 3, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-    case 4: fused_pool_kernel<DT, true, 4, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-    default: fused_pool_kernel<DT, true, 5, MODE, CB, SH><<<grid, kThreads, 0, st>>>(p); break;
-  }
-}
-
-template <int DT>
-void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t st, const ctrfe::KParams& p) {
-  const bool sel = mode == ctrfe::kModeSelect;
-  if (p.n_shards > 0) {  // row-sharded table: 128-bit lanes, rows fetched through peer mappings
-    if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, true>(vect, gs, grid, st, p);
-    else launch_fused_tm<DT, ctrfe::kModeAdd, 16, true>(vect, gs, grid, st, p);
-    return;
-  }
-  if constexpr (DT == CTRFE_F32) {
-    if (cb == 32) {  // 256-bit lanes exist for fp32 rows only
-      if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 32, false>(vect, gs, grid, st, p);
-      else launch_fused_tm<DT, ctrfe::kModeAdd, 32, false>(vect, gs, grid, st, p);
-      return;
-    }
-  }
-  if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, false>(vect, gs, grid, st, p);
-  else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p);
-}
-
-// Which rows take the balanced-load kernel: by default 128-byte rows (measured on B200: +42 % on
-// cfg3, -2 % on cfg4 where the gather already sits on the random-row DRAM ceiling; 64-byte rows
-// lose, the shared-memory staging costs them the L1 hits on the Zipf head).  Never for sharded
-// tables: with rows behind NVLink it measured 527 instead of 331 us per step on 2 GPUs.
-// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows (A/B runs).
-int bal_mode() {
-  static const int mode = [] {
-    const char* e = getenv("CTRFE_BAL");
-    return e && e[0] ? atoi(e) : 1;
-  }();
-  return mode;
-}
-
-// One launch of a specialised kernel; `overlap` adds the programmatic-stream-serialization
+// One launch of a pooling kernel; `overlap` adds the programmatic-stream-serialization
 // attribute, so the grid may start while the kernel before it in the stream is draining.
 template <class K>
 void launch_k(K kernel, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
@@ -426,6 +380,53 @@ void launch_k(K kernel, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, boo
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
+template <int DT, int MODE, int CB, bool SH>
+void launch_fused_tm(bool vect, int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
+  using namespace ctrfe;
+  if (!vect) { launch_k(fused_pool_kernel<DT, false, 5, MODE, 16, false>, grid, st, p, overlap); return; }
+  switch (gs) {
+    case 0: launch_k(fused_pool_kernel<DT, true, 0, MODE, CB, SH>, grid, st, p, overlap); break;
+    case 1: launch_k(fused_pool_kernel<DT, true, 1, MODE, CB, SH>, grid, st, p, overlap); break;
+    case 2: launch_k(fused_pool_kernel<DT, true, 2, MODE, CB, SH>, grid, st, p, overlap); break;
+    case 3: launch_k(fused_pool_kernel<DT, true, 3, MODE, CB, SH>, grid, st, p, overlap); break;
+    case 4: launch_k(fused_pool_kernel<DT, true, 4, MODE, CB, SH>, grid, st, p, overlap); break;
+    default: launch_k(fused_pool_kernel<DT, true, 5, MODE, CB, SH>, grid, st, p, overlap); break;
+  }
+}
+
+template <int DT>
+void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t st, const ctrfe::KParams& p,
+                    bool overlap = false) {
+  const bool sel = mode == ctrfe::kModeSelect;
+  if (p.n_shards > 0) {  // row-sharded table: 128-bit lanes, rows fetched through peer mappings
+    if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, true>(vect, gs, grid, st, p, overlap);
+    else launch_fused_tm<DT, ctrfe::kModeAdd, 16, true>(vect, gs, grid, st, p, overlap);
+    return;
+  }
+  if constexpr (DT == CTRFE_F32) {
+    if (cb == 32) {  // 256-bit lanes exist for fp32 rows only
+      if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 32, false>(vect, gs, grid, st, p, overlap);
+      else launch_fused_tm<DT, ctrfe::kModeAdd, 32, false>(vect, gs, grid, st, p, overlap);
+      return;
+    }
+  }
+  if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, false>(vect, gs, grid, st, p, overlap);
+  else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p, overlap);
+}
+
+// Which rows take the balanced-load kernel: by default 128-byte rows (measured on B200: +42 % on
+// cfg3, -2 % on cfg4 where the gather already sits on the random-row DRAM ceiling; 64-byte rows
+// lose, the shared-memory staging costs them the L1 hits on the Zipf head).  Never for sharded
+// tables: with rows behind NVLink it measured 527 instead of 331 us per step on 2 GPUs.
+// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows (A/B runs).
+int bal_mode() {
+  static const int mode = [] {
+    const char* e = getenv("CTRFE_BAL");
+    return e && e[0] ? atoi(e) : 1;
+  }();
+  return mode;
 }
 
 template <int DT, bool CVM, bool SH, bool HOT>
@@ -474,9 +475,9 @@ int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap = false) {
       continue;
     }
     switch (plan.dtype) {
-      case CTRFE_F32: launch_fused_t<CTRFE_F32>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
-      case CTRFE_F16: launch_fused_t<CTRFE_F16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
-      default: launch_fused_t<CTRFE_BF16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c]); break;
+      case CTRFE_F32: launch_fused_t<CTRFE_F32>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c], overlap); break;
+      case CTRFE_F16: launch_fused_t<CTRFE_F16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c], overlap); break;
+      default: launch_fused_t<CTRFE_BF16>(m, plan.vect, plan.g_shift, plan.chunk_bytes, plan.grids[c], st, plan.chunks[c], overlap); break;
     }
   }
   CU(cudaGetLastError());

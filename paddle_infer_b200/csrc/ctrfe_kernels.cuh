@@ -226,6 +226,8 @@ __device__ __forceinline__ double cvm_log1(float x) {
 template <int DT, bool VECT, int GS, int MODE, int CB, bool SHARDED = false>
 __global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
 fused_pool_kernel(const __grid_constant__ KParams kp) {
+  // lets a launch made with CTRFE_LAUNCH_OVERLAP_PREVIOUS start during this grid's tail
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   using L = Lane<DT, VECT, CB>;
   // sharded mode: the shard base pointers sit in shared memory (the owner differs per lane,
   // and a lane-varying index into the parameter bank would serialise)

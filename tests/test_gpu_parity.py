@@ -618,3 +618,18 @@ def test_overlapped_plan_launches_equal_plain_ones(env):
     _assert_cvm_close(plans[0].outs.cpu().numpy().reshape(Bsz, S, D), want.reshape(Bsz, S, D), True)
     with pytest.raises(B.CtrfeError):
         B.check(B.lib().ctrfe_plan_launch_ex(plans[0].handle, plans[0].ctx.stream(), 2))
+    # a plan with two launches (accumulating and selecting pools -> specialised + general kernel),
+    # overlapped with itself and with its neighbours
+    mixed = []
+    for b in range(3):
+        _, ids, lods = _random_case(rng, 4, 2000, N, D, 30, "f32")
+        p = ops.ctr_fused_emb_seqpool_cvm(tt, [_t(i, dev) for i in ids], [_t(l.astype(np.int64), dev) for l in lods],
+                                          ["SUM", "MAX", "SQRT", "LAST"], use_cvm=None, concat=True, plan_only=True)
+        assert p.num_kernels() == 2
+        mixed.append((p, O.fused_forward([table], ids, lods, ["SUM", "MAX", "SQRT", "LAST"], concat=True)))
+    for rep in range(3):
+        for p, _ in mixed:
+            p.launch(overlap_previous=True)
+    mixed[0][0].ctx.check_ids()
+    for p, want in mixed:
+        np.testing.assert_array_equal(p.outs.cpu().numpy(), want)
