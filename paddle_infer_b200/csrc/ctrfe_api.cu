@@ -463,9 +463,12 @@ void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KP
   }
 }
 
-int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap = false) {
+int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = false) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
     const int m = plan.modes[c];
+    // the launches of one plan work on different slots: the second may always start while the
+    // first drains; the first does so only if the caller said it may (overlap_first)
+    const bool overlap = overlap_first || c > 0;
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
         case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
