@@ -292,6 +292,34 @@ int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t wi
 int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_t width,
               int32_t use_cvm, void* y, void* stream);
 
+/* ---- their backward ops, fp32 (inference never calls these) -------- */
+
+/* sequence_pool_grad: dout device [n_seg, width] -> dx device [x_rows, width]; lod HOST offsets of
+ * the last level; max_index: the forward op's MaxIndex (MAX only).  SUM copies, AVERAGE divides
+ * by the length, SQRT by its square root, LAST / FIRST / MAX scatter into zeros.  Replaces
+ * SequencePoolGradFunctor (math/sequence_pooling.cu:282-494; CPU semantics
+ * sequence_pooling.cc:179-239,309-343,438-496).  Bit-exact with the CPU functor. */
+int ctrfe_sequence_pool_grad(ctrfe_ctx* ctx, const float* dout, int64_t width, const uint64_t* lod_host,
+                             int64_t n_seg, int64_t x_rows, int32_t pooltype, const int32_t* max_index,
+                             float* dx, void* stream);
+
+/* cvm_grad: dy device [rows, width] (use_cvm) or [rows, width-2]; cvm device [n_seq, 2] (the op's
+ * CVM input: show, click); dx device [rows, width] with dx[r, 0:2] = cvm[seq(r)] and the rest
+ * copied from dy.  lod_host NULL: X has no LoD, seq(r) = r; else the HOST offsets of X's level 0.
+ * Replaces CVMGradCUDAKernel (cvm_op.cu:49-84,127-187; cvm_op.h:43-58,100-140).  Bit-exact. */
+int ctrfe_cvm_grad(ctrfe_ctx* ctx, const float* dy, const float* cvm, const uint64_t* lod_host, int64_t n_seq,
+                   int64_t rows, int64_t width, int32_t use_cvm, float* dx, void* stream);
+
+/* lookup_table_v2_grad, dense W@GRAD: dw device [table_rows, dim] = sum over k of dout[k, :] into
+ * row ids[k]; ids equal to padding_idx are skipped (cpu/embedding_grad_kernel.cc:63-66); ids
+ * outside the table are reported by ctrfe_check_ids (slot 0, position k).  Replaces
+ * EmbeddingGradCUDAFunctor / EmbeddingGrad (phi/kernels/gpu/embedding_grad_kernel.cu:38-60,
+ * 62-130).  Atomic adds as in the reference GPU kernel: the order of additions into a row is
+ * not fixed, so results match the CPU kernel to rounding (<= 1e-6 relative), not bit for bit.
+ * The SelectedRows (is_sparse) variant is not provided. */
+int ctrfe_embedding_grad(ctrfe_ctx* ctx, const float* dout, const void* ids, int32_t ids_dtype, int64_t n_ids,
+                         int64_t table_rows, int64_t dim, int64_t padding_idx, float* dw, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

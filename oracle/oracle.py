@@ -94,6 +94,13 @@ def lib(fast: bool = False):
                                         C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.orc_unfused_forward.argtypes = [C.POINTER(Slot), C.c_int, C.POINTER(FusedAttrs), C.c_void_p,
                                           C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.orc_sequence_pool_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int,
+                                             C.c_void_p, C.c_void_p]
+        L.orc_cvm_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int,
+                                   C.c_void_p]
+        L.orc_embedding_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                                         C.c_void_p]
+        L.orc_embedding_grad.restype = C.c_int64
         L.orc_fused_seqpool_cvm.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64]
         L.orc_max_threads.restype = C.c_int
@@ -258,6 +265,48 @@ def fused_forward(tables: Sequence[np.ndarray], ids: Sequence[np.ndarray], lods:
 
 
 # bf16 helpers for tests (numpy has no bfloat16): bit patterns in uint16
+def sequence_pool_grad(dout: np.ndarray, lod: Sequence[int], pooltype: str, k_rows: Optional[int] = None,
+                       max_index: Optional[np.ndarray] = None) -> np.ndarray:
+    """X@GRAD [K, w] of sequence_pool from Out@GRAD [n_seg, w] (fp32); see orc_sequence_pool_grad."""
+    dout = np.ascontiguousarray(dout, np.float32)
+    lod_a = _lod_arr(lod)
+    n_seg = lod_a.size - 1
+    w = int(np.prod(dout.shape[1:]))
+    k = int(lod_a[-1]) if k_rows is None else int(k_rows)
+    dx = np.empty((k,) + dout.shape[1:], np.float32)
+    idx = None if max_index is None else np.ascontiguousarray(max_index, np.int32)
+    rc = lib().orc_sequence_pool_grad(_ptr(dout), _ptr(lod_a), n_seg, w, k, POOLTYPES[pooltype],
+                                      _ptr(idx) if idx is not None else None, _ptr(dx))
+    assert rc == OK, rc
+    return dx
+
+
+def cvm_grad(dy: np.ndarray, cvm_in: np.ndarray, use_cvm: bool = True, lod: Optional[Sequence[int]] = None) -> np.ndarray:
+    """X@GRAD of cvm from Y@GRAD and the CVM input [n_seq, 2]; see orc_cvm_grad."""
+    dy = np.ascontiguousarray(dy, np.float32)
+    cvm_in = np.ascontiguousarray(cvm_in, np.float32)
+    rows = dy.shape[0]
+    w = dy.shape[1] + (0 if use_cvm else 2)
+    dx = np.empty((rows, w), np.float32)
+    lod_a = None if lod is None else _lod_arr(lod)
+    rc = lib().orc_cvm_grad(_ptr(dy), _ptr(cvm_in), _ptr(lod_a) if lod_a is not None else None,
+                            cvm_in.shape[0], rows, w, int(use_cvm), _ptr(dx))
+    assert rc == OK, rc
+    return dx
+
+
+def embedding_grad(dout: np.ndarray, ids: np.ndarray, n_rows: int, padding_idx: int = -1) -> np.ndarray:
+    """Dense W@GRAD [n_rows, d] of lookup_table_v2; raises IndexError on an id outside the table."""
+    ids = np.ascontiguousarray(ids, np.int64).reshape(-1)
+    dout = np.ascontiguousarray(dout, np.float32).reshape(ids.size, -1)
+    d = dout.shape[1]
+    dw = np.empty((n_rows, d), np.float32)
+    rc = lib().orc_embedding_grad(_ptr(dout), _ptr(ids), ids.size, n_rows, d, padding_idx, _ptr(dw))
+    if rc < 0:
+        raise IndexError(f"id at position {-rc - 1} is outside the table")
+    return dw
+
+
 def pull_sparse(keys: np.ndarray, values: np.ndarray, query: np.ndarray) -> np.ndarray:
     """pull_box_sparse / pull_gpups_sparse restated (operators/pull_box_sparse_op.h:32-62 ->
     PSGPUWrapper::PullSparse -> HashTable::get + PullCopy): out[k] = values[i] where

@@ -71,7 +71,7 @@ EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
-    "ctrfe_fused_forward_static",
+    "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
     "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build", "ctrfe_keymap_build",
 ]
@@ -100,6 +100,9 @@ def lib():
         L.ctrfe_embedding.argtypes = [vp, vp, i64, i64, vp, i32, i64, i64, vp, vp]
         L.ctrfe_sequence_pool.argtypes = [vp, vp, i32, i64, vp, i64, i32, C.c_float, vp, vp, vp]
         L.ctrfe_cvm.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp]
+        L.ctrfe_sequence_pool_grad.argtypes = [vp, vp, i64, vp, i64, i64, i32, vp, vp, vp]
+        L.ctrfe_cvm_grad.argtypes = [vp, vp, vp, vp, i64, i64, i64, i32, vp, vp]
+        L.ctrfe_embedding_grad.argtypes = [vp, vp, vp, i32, i64, i64, i64, i64, vp, vp]
         L.ctrfe_fused_forward_static.argtypes = [C.POINTER(FusedDesc), vp, vp]
         L.ctrfe_shard_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp)]
         L.ctrfe_shard_free.argtypes = [C.c_int, vp]

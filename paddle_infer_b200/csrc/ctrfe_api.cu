@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "ctrfe_fast_kernel.cuh"
+#include "ctrfe_grad_kernels.cuh"
 #include "ctrfe_kernels.cuh"
 
 namespace {
@@ -784,6 +785,102 @@ int ctrfe_keymap_build(ctrfe_ctx* ctx, const uint64_t* keys, int64_t n, uint64_t
       reinterpret_cast<const unsigned long long*>(keys), n, reinterpret_cast<unsigned long long*>(map_keys), map_rows,
       (1u << log2_slots) - 1u, 64 - log2_slots, n_unplaced);
   CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
+// ---- backward of the three ops (fp32) -----------------------------------------------------
+namespace {
+// host LoD -> the context scratch (through a pinned staging slot), validated: starts anywhere,
+// non-decreasing, last offset <= limit
+int upload_lod(ctrfe_ctx* ctx, const uint64_t* lod_host, int64_t n, int64_t limit, cudaStream_t st, const char* who) {
+  for (int64_t i = 1; i < n; ++i)
+    if (lod_host[i] < lod_host[i - 1]) return fail(CTRFE_ERR_ARG, "%s: LoD offsets must not decrease", who);
+  if (n > 0 && limit >= 0 && static_cast<int64_t>(lod_host[n - 1]) > limit)
+    return fail(CTRFE_ERR_ARG, "%s: the last LoD offset (%llu) exceeds the row count (%lld)", who,
+                (unsigned long long)lod_host[n - 1], (long long)limit);
+  const size_t bytes = static_cast<size_t>(n) * 8;
+  int rc = scratch_reserve(ctx, bytes, st);
+  if (rc) return rc;
+  Staging* sg = nullptr;
+  rc = stage_acquire(ctx, bytes, &sg);
+  if (rc) return rc;
+  memcpy(sg->host, lod_host, bytes);
+  CU(cudaMemcpyAsync(ctx->scratch, sg->host, bytes, cudaMemcpyHostToDevice, st));
+  CU(cudaEventRecord(sg->done, st));
+  sg->pending = true;
+  return CTRFE_OK;
+}
+}  // namespace
+
+int ctrfe_sequence_pool_grad(ctrfe_ctx* ctx, const float* dout, int64_t width, const uint64_t* lod_host, int64_t n_seg,
+                             int64_t x_rows, int32_t pooltype, const int32_t* max_index, float* dx, void* stream) {
+  if (!ctx || !lod_host) return fail(CTRFE_ERR_ARG, "sequence_pool_grad: null ctx / LoD");
+  if (n_seg < 0 || width <= 0 || x_rows < 0) return fail(CTRFE_ERR_ARG, "sequence_pool_grad: bad shape");
+  if (pooltype < CTRFE_POOL_AVERAGE || pooltype > CTRFE_POOL_MAX)
+    return fail(CTRFE_ERR_ARG, "sequence_pool_grad: unsupported pooling pooltype %d", pooltype);
+  if (pooltype == CTRFE_POOL_MAX && !max_index)
+    return fail(CTRFE_ERR_ARG, "sequence_pool_grad: MAX needs the MaxIndex of the forward op");
+  if (x_rows == 0) return CTRFE_OK;
+  if (!dx || (n_seg > 0 && !dout)) return fail(CTRFE_ERR_ARG, "sequence_pool_grad: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  int rc = upload_lod(ctx, lod_host, n_seg + 1, x_rows, st, "sequence_pool_grad");
+  if (rc) return rc;
+  const bool scattered = pooltype >= CTRFE_POOL_LAST;
+  if (scattered || lod_host[0] != 0 || static_cast<int64_t>(lod_host[n_seg]) != x_rows)
+    CU(cudaMemsetAsync(dx, 0, static_cast<size_t>(x_rows) * width * sizeof(float), st));
+  if (n_seg > 0) {
+    const unsigned blocks = static_cast<unsigned>((n_seg * 32 + 255) / 256);
+    ctrfe::seqpool_grad_kernel<<<blocks, 256, 0, st>>>(dout, reinterpret_cast<const unsigned long long*>(ctx->scratch), n_seg,
+                                                       static_cast<int>(width), pooltype, max_index, dx);
+    CU(cudaGetLastError());
+  }
+  return CTRFE_OK;
+}
+
+int ctrfe_cvm_grad(ctrfe_ctx* ctx, const float* dy, const float* cvm, const uint64_t* lod_host, int64_t n_seq,
+                   int64_t rows, int64_t width, int32_t use_cvm, float* dx, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "cvm_grad: null ctx");
+  if (width < 2 || rows < 0 || n_seq < 0) return fail(CTRFE_ERR_ARG, "cvm_grad: bad shape");
+  if (rows == 0) return CTRFE_OK;
+  if (!dy && (use_cvm || width > 2)) return fail(CTRFE_ERR_ARG, "cvm_grad: null dy");
+  if (!cvm || !dx) return fail(CTRFE_ERR_ARG, "cvm_grad: null pointer");
+  if (!lod_host && n_seq < rows) return fail(CTRFE_ERR_ARG, "cvm_grad: CVM has %lld rows, X has %lld", (long long)n_seq, (long long)rows);
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  const unsigned long long* lod_dev = nullptr;
+  if (lod_host) {
+    if (lod_host[0] != 0 || static_cast<int64_t>(lod_host[n_seq]) != rows)
+      return fail(CTRFE_ERR_ARG, "cvm_grad: the LoD of X must cover its %lld rows", (long long)rows);
+    int rc = upload_lod(ctx, lod_host, n_seq + 1, rows, st, "cvm_grad");
+    if (rc) return rc;
+    lod_dev = reinterpret_cast<const unsigned long long*>(ctx->scratch);
+  }
+  const long long total = rows * width;
+  ctrfe::cvm_grad_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(dy, cvm, lod_dev, n_seq, rows,
+                                                                                      static_cast<int>(width), use_cvm, dx);
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
+int ctrfe_embedding_grad(ctrfe_ctx* ctx, const float* dout, const void* ids, int32_t ids_dtype, int64_t n_ids,
+                         int64_t table_rows, int64_t dim, int64_t padding_idx, float* dw, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "embedding_grad: null ctx");
+  if (ids_dtype != CTRFE_I64 && ids_dtype != CTRFE_I32) return fail(CTRFE_ERR_UNSUPPORTED, "embedding_grad: ids must be int32 or int64");
+  if (n_ids < 0 || table_rows < 0 || dim <= 0) return fail(CTRFE_ERR_ARG, "embedding_grad: bad shape");
+  if (table_rows == 0) return CTRFE_OK;
+  if (!dw || (n_ids > 0 && (!dout || !ids))) return fail(CTRFE_ERR_ARG, "embedding_grad: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  CU(cudaMemsetAsync(dw, 0, static_cast<size_t>(table_rows) * dim * sizeof(float), st));
+  if (n_ids > 0) {
+    ctx->last_ids.assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
+    ctx->last_ids_owner = nullptr;
+    const long long total = n_ids * dim;
+    ctrfe::embedding_grad_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+        dout, ids, ids_dtype == CTRFE_I32, n_ids, table_rows, static_cast<int>(dim), padding_idx, dw, ctx->err_dev);
+    CU(cudaGetLastError());
+  }
   return CTRFE_OK;
 }
 

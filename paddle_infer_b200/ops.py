@@ -211,6 +211,89 @@ def cvm(X: torch.Tensor, CVM: Optional[torch.Tensor] = None, use_cvm: bool = Tru
 
 
 # ------------------------------------------------------------------------------------------
+# backward of the three ops (fp32; SURVEY 8(f) row 4 -- inference never calls these)
+# ------------------------------------------------------------------------------------------
+def _need_f32(t, name):
+    _need_cuda(t, name)
+    if t.dtype != torch.float32:
+        raise Unimplemented(f"{name}: the gradient kernels are float32 only")
+    return t.contiguous()
+
+
+def sequence_pool_grad(OutGrad: torch.Tensor, lod, pooltype: str, x_rows: Optional[int] = None,
+                       MaxIndex: Optional[torch.Tensor] = None, *, ctx: Optional[Context] = None) -> torch.Tensor:
+    """X@GRAD of sequence_pool (sequence_pool_op.h:99-121): [x_rows, ...] from Out@GRAD
+    [num_seq, ...] and X's LoD; MAX needs the forward op's MaxIndex."""
+    if pooltype not in B.POOLTYPES:
+        raise InvalidArgument(f"unsupported pooling pooltype: {pooltype}")
+    g = _need_f32(OutGrad, "Out@GRAD")
+    last = _last_level(lod)
+    n_seq = len(last) - 1
+    if g.shape[0] != n_seq:
+        raise InvalidArgument(f"Out@GRAD has {g.shape[0]} rows, the LoD names {n_seq} sequences")
+    rows = last[-1] if x_rows is None else int(x_rows)
+    width = int(np.prod(g.shape[1:])) if g.dim() > 1 else 1
+    idx = None
+    if pooltype == "MAX":
+        if MaxIndex is None:
+            raise InvalidArgument("sequence_pool_grad(MAX) needs MaxIndex")
+        _need_cuda(MaxIndex, "MaxIndex")
+        idx = MaxIndex.to(torch.int32).contiguous()
+    ctx = ctx or default_context(g.device)
+    dx = torch.empty((rows,) + tuple(g.shape[1:]), dtype=torch.float32, device=g.device)
+    lod_a = _lod_np(last)
+    B.check(B.lib().ctrfe_sequence_pool_grad(ctx.handle, g.data_ptr(), width, lod_a.ctypes.data, n_seq, rows,
+                                             B.POOLTYPES[pooltype], idx.data_ptr() if idx is not None else None,
+                                             dx.data_ptr(), ctx.stream()))
+    return dx
+
+
+def cvm_grad(YGrad: torch.Tensor, CVM: torch.Tensor, use_cvm: bool = True, lod=None, *,
+             ctx: Optional[Context] = None) -> torch.Tensor:
+    """X@GRAD of cvm (cvm_op.h:100-140): columns 0-1 take the CVM input (show, click) of the row's
+    sequence, the rest Y@GRAD.  lod: X's LoD when it has one (CVM then has one row per sequence),
+    else None (one CVM row per row of X)."""
+    g = _need_f32(YGrad, "Y@GRAD")
+    c = _need_f32(CVM, "CVM")
+    if g.dim() != 2 or c.dim() != 2 or c.shape[1] != 2:
+        raise InvalidArgument("Y@GRAD must be rank 2 and CVM [n, 2]")
+    rows = g.shape[0]
+    w = g.shape[1] + (0 if use_cvm else 2)
+    ctx = ctx or default_context(g.device)
+    dx = torch.empty((rows, w), dtype=torch.float32, device=g.device)
+    lod_a = None
+    if lod is not None and len(lod) > 0:
+        lod_a = _lod_np(lod[0] if isinstance(lod[0], (list, tuple, np.ndarray)) else lod)
+        if lod_a.size - 1 != c.shape[0]:
+            raise InvalidArgument("CVM needs one row per sequence of X")
+    B.check(B.lib().ctrfe_cvm_grad(ctx.handle, g.data_ptr(), c.data_ptr(), lod_a.ctypes.data if lod_a is not None else None,
+                                   c.shape[0], rows, w, int(bool(use_cvm)), dx.data_ptr(), ctx.stream()))
+    return dx
+
+
+def lookup_table_v2_grad(OutGrad: torch.Tensor, Ids: torch.Tensor, table_rows: int, padding_idx: int = -1, *,
+                         check: bool = True, ctx: Optional[Context] = None) -> torch.Tensor:
+    """Dense W@GRAD of lookup_table_v2 (phi embedding_grad): [table_rows, D]; rows of ids equal to
+    padding_idx get no gradient.  Atomic adds: equal to the CPU kernel up to rounding."""
+    g = _need_f32(OutGrad, "Out@GRAD")
+    _need_cuda(Ids, "Ids")
+    if Ids.dtype not in _IDT:
+        raise Unimplemented("emebdding input only support int32 and int64")
+    ids = Ids.contiguous().view(-1)
+    d = g.shape[-1]
+    g2 = g.view(-1, d)
+    if g2.shape[0] != ids.numel():
+        raise InvalidArgument("Out@GRAD must have one row per id")
+    ctx = ctx or default_context(g.device)
+    dw = torch.empty((table_rows, d), dtype=torch.float32, device=g.device)
+    B.check(B.lib().ctrfe_embedding_grad(ctx.handle, g2.data_ptr(), ids.data_ptr(), _IDT[ids.dtype], ids.numel(),
+                                         table_rows, d, int(padding_idx), dw.data_ptr(), ctx.stream()))
+    if check:
+        ctx.check_ids()
+    return dw
+
+
+# ------------------------------------------------------------------------------------------
 # the fused front end
 # ------------------------------------------------------------------------------------------
 def _as_list(x, n):

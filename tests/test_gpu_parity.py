@@ -633,3 +633,46 @@ def test_overlapped_plan_launches_equal_plain_ones(env):
     mixed[0][0].ctx.check_ids()
     for p, want in mixed:
         np.testing.assert_array_equal(p.outs.cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------ backward ops
+def test_backward_ops_match_the_oracle(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(404)
+    for w, n_seg in ((5, 9), (16, 400), (100, 77)):
+        l = rng.integers(0, 8, n_seg)
+        l[::5] = 0
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        K = int(lod[-1])
+        x = rng.normal(size=(K, w)).astype(np.float32)
+        dout = rng.normal(size=(n_seg, w)).astype(np.float32)
+        fwd = ops.sequence_pool(_t(x, dev), [lod.tolist()], "MAX", is_test=False)
+        _, idx = O.sequence_pool(x, lod, "MAX", is_test=False)
+        for pt in ("SUM", "AVERAGE", "SQRT", "LAST", "FIRST", "MAX"):
+            got = ops.sequence_pool_grad(_t(dout, dev), [lod.tolist()], pt, MaxIndex=fwd.MaxIndex if pt == "MAX" else None)
+            want = O.sequence_pool_grad(dout, lod, pt, max_index=idx if pt == "MAX" else None)
+            np.testing.assert_array_equal(got.cpu().numpy(), want, err_msg=f"{pt} w={w}")
+        # X longer than its LoD covers: the uncovered rows get zeros
+        got = ops.sequence_pool_grad(_t(dout, dev), [lod.tolist()], "SUM", x_rows=K + 3)
+        np.testing.assert_array_equal(got.cpu().numpy(), O.sequence_pool_grad(dout, lod, "SUM", k_rows=K + 3))
+        # cvm_grad on the pooled rows (no LoD) and on LoD rows
+        cv = rng.uniform(0, 9, (n_seg, 2)).astype(np.float32)
+        if w > 2:
+            for use_cvm in (True, False):
+                dy = rng.normal(size=(n_seg, w if use_cvm else w - 2)).astype(np.float32)
+                got = ops.cvm_grad(_t(dy, dev), _t(cv, dev), use_cvm)
+                np.testing.assert_array_equal(got.cpu().numpy(), O.cvm_grad(dy, cv, use_cvm))
+            dyk = rng.normal(size=(K, w)).astype(np.float32)
+            got = ops.cvm_grad(_t(dyk, dev), _t(cv, dev), True, lod=[lod.tolist()])
+            np.testing.assert_array_equal(got.cpu().numpy(), O.cvm_grad(dyk, cv, True, lod=lod))
+        # embedding grad (atomics: equal up to rounding)
+        N = 50
+        ids = rng.integers(0, N, K).astype(np.int64)
+        pad = int(ids[0]) if K else -1
+        for id_dt in (np.int64, np.int32):
+            got = ops.lookup_table_v2_grad(_t(x, dev), _t(ids.astype(id_dt), dev), N, padding_idx=pad)
+            np.testing.assert_allclose(got.cpu().numpy(), O.embedding_grad(x, ids, N, padding_idx=pad), rtol=1e-5, atol=1e-5)
+    bad = np.array([1, 2, 60, 3], np.int64)
+    with pytest.raises(ValueError) as e:
+        ops.lookup_table_v2_grad(_t(np.ones((4, 3), np.float32), dev), _t(bad, dev), 50)
+    assert e.value.position == 2 and e.value.id_value == 60

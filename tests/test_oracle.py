@@ -268,3 +268,56 @@ def test_pull_sparse_restatement():
     # int64 views of the same bits (how Paddle holds feasigns) behave the same
     np.testing.assert_array_equal(O.pull_sparse(keys.view(np.int64), vals, q.view(np.int64)), got)
     assert O.pull_sparse(np.zeros(0, np.uint64), np.zeros((0, 3), np.float32), q).shape == (6, 3)
+
+
+def test_backward_restatements_against_the_reference_formulas():
+    """sequence_pool_grad / cvm_grad / lookup_table_v2_grad of the oracle vs the formulas of
+    sequence_pooling.cc:438-496, cvm_op.h:43-58 and embedding_grad_kernel.cc:63-88 written out
+    in numpy."""
+    rng = np.random.default_rng(9)
+    lod = [0, 3, 3, 7, 8, 8]
+    w = 5
+    dout = rng.normal(size=(5, w)).astype(np.float32)
+    x = rng.normal(size=(8, w)).astype(np.float32)
+    _, idx = O.sequence_pool(x, lod, "MAX", is_test=False)
+    for pt in ("SUM", "AVERAGE", "SQRT", "LAST", "FIRST", "MAX"):
+        want = np.zeros((8, w), np.float32)
+        for i in range(5):
+            a, e = lod[i], lod[i + 1]
+            if a == e:
+                continue
+            h = np.float32(e - a)
+            if pt == "SUM":
+                want[a:e] = dout[i]
+            elif pt == "AVERAGE":
+                want[a:e] = dout[i] / h
+            elif pt == "SQRT":
+                want[a:e] = dout[i] / np.sqrt(h)
+            elif pt == "LAST":
+                want[e - 1] = dout[i]
+            elif pt == "FIRST":
+                want[a] = dout[i]
+            else:
+                for c in range(w):
+                    want[idx[i, c], c] = dout[i, c]
+        got = O.sequence_pool_grad(dout, lod, pt, max_index=idx if pt == "MAX" else None)
+        np.testing.assert_array_equal(got, want, err_msg=pt)
+    # rows past the last offset stay zero
+    assert (O.sequence_pool_grad(dout, lod, "SUM", k_rows=10)[8:] == 0).all()
+    # cvm_grad: without LoD, and with X carrying LoD (one CVM row per sequence)
+    dy = rng.normal(size=(4, 6)).astype(np.float32)
+    cv = rng.uniform(0, 5, (4, 2)).astype(np.float32)
+    np.testing.assert_array_equal(O.cvm_grad(dy, cv, True), np.concatenate([cv, dy[:, 2:]], axis=1))
+    np.testing.assert_array_equal(O.cvm_grad(dy, cv, False), np.concatenate([cv, dy], axis=1))
+    np.testing.assert_array_equal(O.cvm_grad(dy, cv[:2], True, lod=[0, 1, 4]),
+                                  np.concatenate([cv[[0, 1, 1, 1]], dy[:, 2:]], axis=1))
+    # embedding grad: in-order accumulation, padding rows skipped, bad ids refused
+    ids = np.array([3, 1, 3, 0, 2, 3], np.int64)
+    g = rng.normal(size=(6, 4)).astype(np.float32)
+    want = np.zeros((5, 4), np.float32)
+    for i, r in enumerate(ids):
+        if r != 2:
+            want[r] += g[i]
+    np.testing.assert_array_equal(O.embedding_grad(g, ids, 5, padding_idx=2), want)
+    with pytest.raises(IndexError):
+        O.embedding_grad(g, np.array([0, 1, 5, 0, 0, 0]), 5)
