@@ -27,7 +27,6 @@ import numpy as np
 import torch
 
 from . import _lib as B
-from .lod import check_lod
 
 _DT = {torch.float32: B.F32, torch.float16: B.F16, torch.bfloat16: B.BF16, torch.float64: B.F64}
 _IDT = {torch.int64: B.I64, torch.int32: B.I32}

@@ -23,7 +23,7 @@ every field this module does not name are carried through as opaque bytes / unkn
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, List, Tuple
 
 from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
 
