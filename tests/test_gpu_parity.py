@@ -676,3 +676,30 @@ def test_backward_ops_match_the_oracle(env):
     with pytest.raises(ValueError) as e:
         ops.lookup_table_v2_grad(_t(np.ones((4, 3), np.float32), dev), _t(bad, dev), 50)
     assert e.value.position == 2 and e.value.id_value == 60
+
+
+def test_more_slots_than_one_launch_carries(env):
+    """150 slots of mixed pooltypes: descriptors travel in the kernel parameters 64 at a time, so
+    this is five launches (3 accumulating + 2 selecting... whatever the split, more than two),
+    which overlap each other; every slot must still match the oracle, with concat and without."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(150)
+    S, Bsz, N, D = 150, 40, 700, 16
+    table, ids, lods = _random_case(rng, S, Bsz, N, D, 6, "f32")
+    tt = _t(table, dev)
+    pools = [POOLS[s % len(POOLS)] for s in range(S)]
+    ids_t = [_t(i, dev) for i in ids]
+    want = O.fused_forward([table], ids, lods, pools, cvm_mode=O.CVM_USE)
+    plan = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, [_t(l.astype(np.int64), dev) for l in lods], pools, use_cvm=True,
+                                         concat=True, plan_only=True)
+    assert plan.num_kernels() >= 3
+    for overlap in (False, True, True):
+        plan.outs.zero_()
+        plan.launch(overlap_previous=overlap)
+        plan.ctx.check_ids()
+        got = plan.outs.cpu().numpy().reshape(Bsz, S, D)
+        for s in range(S):
+            _assert_cvm_close(got[:, s, :], want[s], True)
+    outs = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods, pools, use_cvm=True)
+    for s in range(S):
+        _assert_cvm_close(outs[s].cpu().numpy(), want[s], True)
