@@ -80,6 +80,7 @@ struct ctrfe_plan {
   bool fast = false;     // accumulating chunks may use the specialised kernel (ctrfe_fast_kernel.cuh)
   bool cvm_use = false;
   bool hot = false;      // sharded mode with a hot-row replica cache
+  std::vector<char> all_max;  // per launch: every slot pools with MAX (selecting launches only)
   std::vector<IdSource> id_src;
 };
 
@@ -251,6 +252,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   plan->chunks.clear();
   plan->grids.clear();
   plan->modes.clear();
+  plan->all_max.clear();
   plan->where.assign(d->n_slots, std::make_pair(-1, -1));
   // Slots are grouped by kernel mode (accumulating vs selecting pools) into launches of at
   // most kMaxSlotsPerLaunch descriptors; a CTR batch with one pooltype family is ONE launch.
@@ -265,6 +267,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       c = static_cast<int>(plan->chunks.size()) - 1;
       open_chunk[mode] = c;
       plan->modes.push_back(mode);
+      plan->all_max.push_back(1);
       max_seg.push_back(0);
       ctrfe::KParams& k = plan->chunks[c];
       memset(&k, 0, sizeof(k));
@@ -313,6 +316,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     o.id_kind = static_cast<short>(km ? 3 : (sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2));
     o.slot_index = s;
     if (sl.n_seg > max_seg[c]) max_seg[c] = sl.n_seg;
+    if (sl.pooltype != CTRFE_POOL_MAX) plan->all_max[c] = 0;
   }
   for (size_t c = 0; c < plan->chunks.size(); ++c) {
     const long long items = max_seg[c] * tiles;
@@ -417,11 +421,13 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p, overlap);
 }
 
-// Which rows take the balanced-load kernel: by default 128-byte rows (measured on B200: +42 % on
+// Which rows take the balanced-load kernel: by default rows of 128 bytes and wider (measured on B200: +42 % on
 // cfg3, -2 % on cfg4 where the gather already sits on the random-row DRAM ceiling; 64-byte rows
 // lose, the shared-memory staging costs them the L1 hits on the Zipf head).  Never for sharded
 // tables: with rows behind NVLink it measured 527 instead of 331 us per step on 2 GPUs.
-// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows (A/B runs).
+// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows, CTRFE_BAL=3: also rows of 256 / 512 bytes and
+// the selecting (MAX) form -- measured slower on cfg5 (200-row sequences of 256-byte rows: only the
+// lane group that owns the current rows adds, 334 vs 219 us per step), kept for A/B runs.
 int bal_mode() {
   static const int mode = [] {
     const char* e = getenv("CTRFE_BAL");
@@ -433,13 +439,19 @@ int bal_mode() {
 template <int DT, bool CVM, bool SH, bool HOT>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   using namespace ctrfe;
-  if (!SH && ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2))) {
-    // a warp takes M times the segments it takes in the other kernels
-    const int m = gs == 2 ? kBalM64 : kBalM128;
-    const dim3 gb((grid.x + m - 1) / m, grid.y, 1);
-    if (gs == 2) launch_k(fused_pool_bal_kernel<DT, 2, CVM, SH, HOT, kBalM64>, gb, st, p, overlap);
-    else launch_k(fused_pool_bal_kernel<DT, 3, CVM, SH, HOT, kBalM128>, gb, st, p, overlap);
-    return;
+  if constexpr (!SH) {
+    if ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2) || (gs >= 4 && bal_mode() >= 3)) {
+      // a warp takes M times the segments it takes in the other kernels
+      const int m = gs == 2 ? kBalM64 : (gs == 3 ? kBalM128 : 1);
+      const dim3 gb((grid.x + m - 1) / m, grid.y, 1);
+      switch (gs) {
+        case 2: launch_k(fused_pool_bal_kernel<DT, 2, CVM, false, false, kBalM64>, gb, st, p, overlap); break;
+        case 3: launch_k(fused_pool_bal_kernel<DT, 3, CVM, false, false, kBalM128>, gb, st, p, overlap); break;
+        case 4: launch_k(fused_pool_bal_kernel<DT, 4, CVM, false, false, 1>, gb, st, p, overlap); break;
+        default: launch_k(fused_pool_bal_kernel<DT, 5, CVM, false, false, 1>, gb, st, p, overlap); break;
+      }
+      return;
+    }
   }
   switch (gs) {
     case 0: launch_k(fused_pool_fast_kernel<DT, 0, CVM, SH, HOT>, grid, st, p, overlap); break;
@@ -448,6 +460,17 @@ void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, 
     case 3: launch_k(fused_pool_fast_kernel<DT, 3, CVM, SH, HOT>, grid, st, p, overlap); break;
     case 4: launch_k(fused_pool_fast_kernel<DT, 4, CVM, SH, HOT>, grid, st, p, overlap); break;
     default: launch_k(fused_pool_fast_kernel<DT, 5, CVM, SH, HOT>, grid, st, p, overlap); break;
+  }
+}
+
+// MAX over rows of 128 bytes and wider, no CVM, unsharded: the balanced-load kernel's selecting form
+template <int DT>
+void launch_bal_max(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
+  using namespace ctrfe;
+  switch (gs) {
+    case 3: launch_k(fused_pool_bal_kernel<DT, 3, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
+    case 4: launch_k(fused_pool_bal_kernel<DT, 4, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
+    default: launch_k(fused_pool_bal_kernel<DT, 5, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
   }
 }
 
@@ -470,6 +493,15 @@ int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = fa
     // the launches of one plan work on different slots: the second may always start while the
     // first drains; the first does so only if the caller said it may (overlap_first)
     const bool overlap = overlap_first || c > 0;
+    if (plan.fast && m == ctrfe::kModeSelect && plan.all_max[c] && !plan.cvm_use && plan.g_shift >= 3 &&
+        plan.chunks[c].n_shards == 0 && bal_mode() >= 3) {
+      switch (plan.dtype) {
+        case CTRFE_F32: launch_bal_max<CTRFE_F32>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
+        case CTRFE_F16: launch_bal_max<CTRFE_F16>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
+        default: launch_bal_max<CTRFE_BF16>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
+      }
+      continue;
+    }
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
         case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;

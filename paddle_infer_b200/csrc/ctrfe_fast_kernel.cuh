@@ -283,14 +283,15 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 #define CTRFE_BAL_MINB 6
 #endif
 constexpr int kBalM128 = CTRFE_BAL_M;   // segments per lane group, 128-byte rows
-constexpr int kBalM64 = CTRFE_BAL_M64;  // 64-byte rows
+constexpr int kBalM64 = CTRFE_BAL_M64;  // 64-byte rows (wider rows: 1)
 
-template <int DT, int GS, bool CVM, bool SHARDED, bool HOT, int M>
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT, int M, int MODE = kModeAdd>
 __global__ void __launch_bounds__(kThreads, CTRFE_BAL_MINB)
 fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
   launch_dependents();
   using L = Lane<DT, true, 16>;
-  static_assert(GS == 2 || GS == 3, "64- and 128-byte rows");
+  static_assert(GS >= 2 && GS <= 5, "64- to 512-byte rows");
+  static_assert(MODE == kModeAdd || (!CVM && M == 1), "the selecting (MAX) form has no CVM and one segment per group");
   constexpr int VEC = L::VEC;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
@@ -299,12 +300,12 @@ fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
 #ifdef CTRFE_BAL_U
   constexpr int U = CTRFE_BAL_U;
 #else
-  constexpr int U = kUnroll * M;      // rows in flight per lane
+  constexpr int U = GS == 2 ? kUnroll * M : 8;  // rows in flight per lane
 #endif
   constexpr int RB = U * NG;          // rows per batch
   constexpr int IPL = RB / 32 > 0 ? RB / 32 : 1;  // ids per lane per batch
   constexpr int kWarps = kThreads / 32;
-  static_assert(WS + 1 <= 32 && RB % 32 == 0 || RB < 32, "one LoD offset per lane");
+  static_assert(WS + 1 <= 32 && (RB % 32 == 0 || RB < 32), "one LoD offset per lane");
 
   __shared__ uint4 s_rows_all[kWarps][U * 32];
   __shared__ unsigned long long s_shards[SHARDED ? kMaxShards : 1];
@@ -334,10 +335,50 @@ fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
 
   const RowSource<DT, GS, SHARDED, HOT> src(kp, slp, s_shards, gl);
   float acc[M][VEC];
+  uint32_t sel[M][4];  // selecting form on 16-bit types: raw bits of the selected elements
 #pragma unroll
-  for (int m = 0; m < M; ++m)
+  for (int m = 0; m < M; ++m) {
 #pragma unroll
     for (int e = 0; e < VEC; ++e) acc[m][e] = 0.0f;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) sel[m][r] = 0u;
+  }
+
+  // one loaded row (this lane's 16 bytes) into segment m's state; `first`: the segment's row 0
+  auto take_row = [&](int m, const uint4& v, bool first) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    if constexpr (MODE == kModeAdd) {
+      if constexpr (L::ES == 4) {
+        add_f32x2(acc[m][0], acc[m][1], __uint_as_float(w[0]), __uint_as_float(w[1]));
+        add_f32x2(acc[m][2], acc[m][3], __uint_as_float(w[2]), __uint_as_float(w[3]));
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float2 x = L::unpack2(w[r]);
+          add_f32x2(acc[m][2 * r], acc[m][2 * r + 1], x.x, x.y);
+        }
+      }
+    } else {
+      // MAX: out = row 0, then strictly-greater replaces (math/sequence_pooling.cc:166-174);
+      // NaN never replaces and a NaN in row 0 sticks, as on the CPU
+      if constexpr (L::ES == 4) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float x = __uint_as_float(w[e]);
+          if (first || x > acc[m][e]) acc[m][e] = x;
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float2 x = L::unpack2(w[r]);
+          uint32_t mask = 0u;
+          if (first || x.x > acc[m][2 * r]) { acc[m][2 * r] = x.x; mask |= 0x0000ffffu; }
+          if (first || x.y > acc[m][2 * r + 1]) { acc[m][2 * r + 1] = x.y; mask |= 0xffff0000u; }
+          sel[m][r] = (sel[m][r] & ~mask) | (w[r] & mask);
+        }
+      }
+    }
+  };
 
   // lane L holds the row indices of batch positions L, L + 32, ...
   auto stage_ids = [&](uint32_t p0, uint32_t (&ids)[IPL]) {
@@ -381,28 +422,8 @@ fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
         uint4 b = make_uint4(0u, 0u, 0u, 0u);
         const bool two = j + 1 < j1;
         if (two) b = s_rows[(j + 1) * G + gl];
-        const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wb[4] = {b.x, b.y, b.z, b.w};
-        if constexpr (L::ES == 4) {
-          add_f32x2(acc[m][0], acc[m][1], __uint_as_float(wa[0]), __uint_as_float(wa[1]));
-          add_f32x2(acc[m][2], acc[m][3], __uint_as_float(wa[2]), __uint_as_float(wa[3]));
-          if (two) {
-            add_f32x2(acc[m][0], acc[m][1], __uint_as_float(wb[0]), __uint_as_float(wb[1]));
-            add_f32x2(acc[m][2], acc[m][3], __uint_as_float(wb[2]), __uint_as_float(wb[3]));
-          }
-        } else {
-#pragma unroll
-          for (int r = 0; r < 4; ++r) {
-            const float2 x = L::unpack2(wa[r]);
-            add_f32x2(acc[m][2 * r], acc[m][2 * r + 1], x.x, x.y);
-          }
-          if (two) {
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-              const float2 x = L::unpack2(wb[r]);
-              add_f32x2(acc[m][2 * r], acc[m][2 * r + 1], x.x, x.y);
-            }
-          }
-        }
+        take_row(m, a, p0 + static_cast<uint32_t>(j) == start);
+        if (two) take_row(m, b, false);
       }
     }
 #pragma unroll
@@ -413,7 +434,20 @@ fused_pool_bal_kernel(const __grid_constant__ KParams kp) {
     const unsigned seg = seg0 + g * M + m;
     const uint32_t start = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m);
     const uint32_t endo = __shfl_sync(kFull, my_off, static_cast<int>(g) * M + m + 1);
-    finish_segment<DT, GS, CVM>(kp, slp, acc[m], static_cast<int>(endo - start), seg, gl, seg < n_seg);
+    if constexpr (MODE == kModeAdd) {
+      finish_segment<DT, GS, CVM>(kp, slp, acc[m], static_cast<int>(endo - start), seg, gl, seg < n_seg);
+    } else {
+      if (seg < n_seg) {  // the selected bits as they are; an empty sequence takes pad_value
+        uint32_t packed[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          if constexpr (L::ES == 4) packed[r] = __float_as_uint(endo == start ? kp.pad_value : acc[m][r]);
+          else packed[r] = endo == start ? float_to_elem<DT>(kp.pad_value) * 0x00010001u : sel[m][r];
+        }
+        char* dst = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes + gl * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      }
+    }
   }
 }
 

@@ -454,6 +454,32 @@ def test_specialised_kernels_ragged_long_and_bad(env, dtype, D):
                     _assert_cvm_close(g, w, use_cvm is True)
                 else:
                     np.testing.assert_array_equal(g, w)
+    # MAX over the same shapes (rows of 128 bytes and wider take the balanced-load kernel's
+    # selecting form), with special values in the table: NaN, infinities, signed zeros
+    tspec = table.copy()
+    if dtype == "f32":
+        tspec[5, :4] = [np.nan, np.inf, -np.inf, -0.0]
+        tspec[6, :4] = [0.0, -np.inf, np.nan, 0.0]
+    elif dtype == "f16":
+        tspec[5, :4] = np.array([np.nan, np.inf, -np.inf, -0.0], np.float16)
+        tspec[6, :4] = np.array([0.0, -np.inf, np.nan, 0.0], np.float16)
+    else:
+        tspec[5, :4] = O.f32_to_bf16_bits(np.array([np.nan, np.inf, -np.inf, -0.0], np.float32))
+        tspec[6, :4] = O.f32_to_bf16_bits(np.array([0.0, -np.inf, np.nan, 0.0], np.float32))
+    ids_m = [i.copy() for i in ids]
+    for s in range(S):
+        if ids_m[s].size > 6:
+            ids_m[s][::7] = 5
+            ids_m[s][3::11] = 6
+    got = ops.ctr_fused_emb_seqpool_cvm(_t(tspec, dev, bf16), [_t(i, dev) for i in ids_m], lods, "MAX", pad_value=0.5,
+                                        use_cvm=None)
+    want = O.fused_forward([tspec], ids_m, lods, ["MAX"] * S, pad_value=0.5, bf16=bf16)
+    for s in range(S):
+        g, w = _np(got[s]), want[s]
+        if dtype == "f32":
+            np.testing.assert_array_equal(g.view(np.uint32), w.view(np.uint32))
+        else:
+            np.testing.assert_array_equal(g.view(np.uint16), w.view(np.uint16))
     bad = [i.copy() for i in ids]
     pos = int(lods[3][3]) + 150   # inside the 300-row segment
     bad[3][pos] = N + 5
@@ -703,3 +729,21 @@ def test_more_slots_than_one_launch_carries(env):
     outs = ops.ctr_fused_emb_seqpool_cvm(tt, ids_t, lods, pools, use_cvm=True)
     for s in range(S):
         _assert_cvm_close(outs[s].cpu().numpy(), want[s], True)
+
+
+@pytest.mark.parametrize("switch", ["CTRFE_BAL=0", "CTRFE_BAL=2", "CTRFE_BAL=3", "CTRFE_NO_FAST=1"])
+def test_every_kernel_variant_passes_the_shape_sweep(env, switch):
+    """The library picks its kernel per process (environment switches read once): re-run the
+    ragged / long / special-value sweep and the reduced cfg3 / cfg5 runs in a child process with
+    each switch, so the warp-level kernel for every row width (CTRFE_BAL=0), the balanced-load
+    kernel on 64-byte rows (=2) and on 256-byte rows and MAX pools (=3), and the general kernel
+    on everything (CTRFE_NO_FAST=1) all meet the same bit-exact bar."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    k, v = switch.split("=")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-x", "-q", "-m", "gpu",
+                        "-k", "specialised or config3 or config5 or config4"],
+                       capture_output=True, text=True, timeout=900, cwd=root, env=dict(os.environ, **{k: v}))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
