@@ -34,7 +34,7 @@ namespace ctrfe {
 #define CTRFE_MINB32 8
 #endif
 #ifndef CTRFE_MINB16
-#define CTRFE_MINB16 4
+#define CTRFE_MINB16 8
 #endif
 
 constexpr int kThreads = 256;          // threads per CTA of the pooling kernel
