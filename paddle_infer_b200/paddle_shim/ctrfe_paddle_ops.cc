@@ -208,6 +208,27 @@ PD_BUILD_OP(b200_lookup_table_v2)
     .SetInferShapeFn(PD_INFER_SHAPE(B200LookupTableV2InferShape))
     .SetInferDtypeFn(PD_INFER_DTYPE(B200LookupTableV2InferDtype));
 
+// W@GRAD (dense) of b200_lookup_table_v2: LookupTableV2GradOpMaker takes W, Ids, Out@GRAD
+// (lookup_table_v2_op.cc:107-125); fp32 only here, SelectedRows (is_sparse) not provided.
+std::vector<paddle::Tensor> B200LookupTableV2Grad(const paddle::Tensor& w, const paddle::Tensor& ids,
+                                                  const paddle::Tensor& dout, int64_t padding_idx) {
+  NeedGpu(dout, "Out@GRAD");
+  PD_CHECK(dout.dtype() == paddle::DataType::FLOAT32, "b200_lookup_table_v2_grad: float32 only");
+  const auto wshape = w.shape();
+  auto dw = paddle::empty(wshape, dout.dtype(), dout.place());
+  ctrfe_ctx* ctx = CtxFor(dout);
+  Check(ctrfe_embedding_grad(ctx, static_cast<const float*>(Raw(dout)), Raw(ids), IdCode(ids.dtype()), ids.numel(),
+                             wshape[0], wshape[1], padding_idx, static_cast<float*>(RawMut(dw)), dout.stream()));
+  Check(ctrfe_check_ids(ctx, dout.stream(), nullptr, nullptr, nullptr));
+  return {dw};
+}
+
+PD_BUILD_GRAD_OP(b200_lookup_table_v2)
+    .Inputs({"W", "Ids", paddle::Grad("Out")})
+    .Outputs({paddle::Grad("W")})
+    .Attrs({"padding_idx: int64_t"})
+    .SetKernelFn(PD_KERNEL(B200LookupTableV2Grad));
+
 // ---------------------------------------------------------------------------------------
 // b200_sequence_pool  (SequencePoolOpMaker, sequence_pool_op.cc:45-112).  The custom-op
 // maker has no "intermediate" marker, so MaxIndex is a plain second output: int32 indices
@@ -257,6 +278,35 @@ PD_BUILD_OP(b200_sequence_pool)
     .SetInferShapeFn(PD_INFER_SHAPE(B200SequencePoolInferShape))
     .SetInferDtypeFn(PD_INFER_DTYPE(B200SequencePoolInferDtype));
 
+// X@GRAD of b200_sequence_pool (SequencePoolGradOpMaker: X, MaxIndex, Out@GRAD,
+// sequence_pool_op.cc:150-176); fp32 only.
+std::vector<paddle::Tensor> B200SequencePoolGrad(const paddle::Tensor& x, const paddle::Tensor& max_index,
+                                                 const paddle::Tensor& dout, const std::string& pooltype,
+                                                 float pad_value, bool is_test) {
+  NeedGpu(dout, "Out@GRAD");
+  PD_CHECK(dout.dtype() == paddle::DataType::FLOAT32, "b200_sequence_pool_grad: float32 only");
+  const auto& lod = LodOf(x);
+  PD_CHECK(!lod.empty(), "Input(X) Tensor of SequencePoolGradOp does not contain LoD information.");
+  const auto& last = lod.back();
+  const int64_t n_seg = static_cast<int64_t>(last.size()) - 1;
+  const auto shape = x.shape();
+  int64_t width = 1;
+  for (size_t i = 1; i < shape.size(); ++i) width *= shape[i];
+  auto dx = paddle::empty(shape, dout.dtype(), dout.place());
+  const bool is_max = pooltype == "MAX";
+  Check(ctrfe_sequence_pool_grad(CtxFor(dout), static_cast<const float*>(Raw(dout)), width,
+                                 reinterpret_cast<const uint64_t*>(last.data()), n_seg, shape[0], PoolCode(pooltype),
+                                 is_max ? max_index.data<int32_t>() : nullptr, static_cast<float*>(RawMut(dx)),
+                                 dout.stream()));
+  return {dx};
+}
+
+PD_BUILD_GRAD_OP(b200_sequence_pool)
+    .Inputs({"X", "MaxIndex", paddle::Grad("Out")})
+    .Outputs({paddle::Grad("X")})
+    .Attrs({"pooltype: std::string", "pad_value: float", "is_test: bool"})
+    .SetKernelFn(PD_KERNEL(B200SequencePoolGrad));
+
 // ---------------------------------------------------------------------------------------
 // b200_cvm  (CVMOpMaker, cvm_op.cc:127-150).  The CVM input is declared because the
 // reference op has it; forward never reads it (cvm_op.h:60-99).
@@ -287,3 +337,25 @@ PD_BUILD_OP(b200_cvm)
     .SetKernelFn(PD_KERNEL(B200Cvm))
     .SetInferShapeFn(PD_INFER_SHAPE(B200CvmInferShape))
     .SetInferDtypeFn(PD_INFER_DTYPE(B200CvmInferDtype));
+
+// X@GRAD of b200_cvm (CVMGradOpMaker: X, CVM, Y@GRAD, cvm_op.cc:152-170): columns 0-1 take
+// the CVM input of the row's sequence, the rest Y@GRAD (cvm_op.h:100-140); fp32 only.
+std::vector<paddle::Tensor> B200CvmGrad(const paddle::Tensor& x, const paddle::Tensor& cvm, const paddle::Tensor& dy,
+                                        bool use_cvm) {
+  NeedGpu(dy, "Y@GRAD");
+  PD_CHECK(dy.dtype() == paddle::DataType::FLOAT32, "b200_cvm_grad: float32 only");
+  const auto shape = x.shape();
+  auto dx = paddle::empty(shape, dy.dtype(), dy.place());
+  const auto& lod = LodOf(x);
+  const uint64_t* lod0 = lod.empty() ? nullptr : reinterpret_cast<const uint64_t*>(lod[0].data());
+  const int64_t n_seq = lod.empty() ? cvm.shape()[0] : static_cast<int64_t>(lod[0].size()) - 1;
+  Check(ctrfe_cvm_grad(CtxFor(dy), static_cast<const float*>(Raw(dy)), static_cast<const float*>(Raw(cvm)), lod0, n_seq,
+                       shape[0], shape[1], use_cvm ? 1 : 0, static_cast<float*>(RawMut(dx)), dy.stream()));
+  return {dx};
+}
+
+PD_BUILD_GRAD_OP(b200_cvm)
+    .Inputs({"X", "CVM", paddle::Grad("Y")})
+    .Outputs({paddle::Grad("X")})
+    .Attrs({"use_cvm: bool"})
+    .SetKernelFn(PD_KERNEL(B200CvmGrad));
