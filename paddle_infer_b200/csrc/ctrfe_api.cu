@@ -421,17 +421,17 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p, overlap);
 }
 
-// Which rows take the balanced-load kernel: by default rows of 128 bytes and wider (measured on B200: +42 % on
-// cfg3, -2 % on cfg4 where the gather already sits on the random-row DRAM ceiling; 64-byte rows
-// lose, the shared-memory staging costs them the L1 hits on the Zipf head).  Never for sharded
-// tables: with rows behind NVLink it measured 527 instead of 331 us per step on 2 GPUs.
-// CTRFE_BAL=0: never, CTRFE_BAL=2: also 64-byte rows, CTRFE_BAL=3: also rows of 256 / 512 bytes and
-// the selecting (MAX) form -- measured slower on cfg5 (200-row sequences of 256-byte rows: only the
-// lane group that owns the current rows adds, 334 vs 219 us per step), kept for A/B runs.
+// Which rows take the balanced-load kernel (fused_pool_bal_kernel).  None by default: once the
+// 16-bit kernels ran eight CTAs per SM the warp-level kernel overtook it on cfg3 (198 vs 219 us
+// per step; cfg4 on one GPU 602 vs 612), 64-byte rows always lost (the staging buffers cost the
+// L1 hits on the Zipf head), rows behind NVLink lost badly (527 vs 331 us on 2 GPUs) and cfg5's
+// long sequences turn it instruction-bound.  CTRFE_BAL=1: 128-byte rows; =2: also 64-byte rows;
+// =3: also 256 / 512-byte rows and the selecting (MAX) form.  Kept for A/B runs; every setting
+// is parity-tested (tests/test_gpu_parity.py::test_every_kernel_variant_passes_the_shape_sweep).
 int bal_mode() {
   static const int mode = [] {
     const char* e = getenv("CTRFE_BAL");
-    return e && e[0] ? atoi(e) : 1;
+    return e && e[0] ? atoi(e) : 0;
   }();
   return mode;
 }

@@ -731,12 +731,12 @@ def test_more_slots_than_one_launch_carries(env):
         _assert_cvm_close(outs[s].cpu().numpy(), want[s], True)
 
 
-@pytest.mark.parametrize("switch", ["CTRFE_BAL=0", "CTRFE_BAL=2", "CTRFE_BAL=3", "CTRFE_NO_FAST=1"])
+@pytest.mark.parametrize("switch", ["CTRFE_BAL=1", "CTRFE_BAL=2", "CTRFE_BAL=3", "CTRFE_NO_FAST=1"])
 def test_every_kernel_variant_passes_the_shape_sweep(env, switch):
     """The library picks its kernel per process (environment switches read once): re-run the
     ragged / long / special-value sweep and the reduced cfg3 / cfg5 runs in a child process with
-    each switch, so the warp-level kernel for every row width (CTRFE_BAL=0), the balanced-load
-    kernel on 64-byte rows (=2) and on 256-byte rows and MAX pools (=3), and the general kernel
+    each switch, so the balanced-load kernel on 128-byte rows (CTRFE_BAL=1), on 64-byte rows (=2)
+    and on 256-byte rows and MAX pools (=3), and the general kernel
     on everything (CTRFE_NO_FAST=1) all meet the same bit-exact bar."""
     import os
     import subprocess
