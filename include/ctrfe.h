@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define CTRFE_VERSION 100 /* 0.1.0 */
+#define CTRFE_VERSION 110 /* 0.1.1: descriptor grew (hot_cache, keymap); plan_launch_ex, grads */
 
 /* ---- status codes ------------------------------------------------------------------ */
 enum {
