@@ -747,3 +747,43 @@ def test_every_kernel_variant_passes_the_shape_sweep(env, switch):
                         "-k", "specialised or config3 or config5 or config4"],
                        capture_output=True, text=True, timeout=900, cwd=root, env=dict(os.environ, **{k: v}))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("lod", [[0, 10], [0, 2, 7, 10]])
+def test_reference_gtest_sequence_pooling_grad_sum_on_gpu(env, lod):
+    """TEST(SequencePoolingGrad, CUDA_SUM) of the reference (sequence_pooling_test.cc:133-145):
+    same fixture, same EXPECT_EQ bar, through ctrfe_sequence_pool_grad."""
+    ops, O, B, dev = env
+    w = 128
+    dout = np.arange((len(lod) - 1) * w, dtype=np.float32).reshape(-1, w)
+    dx = ops.sequence_pool_grad(_t(dout, dev), [lod], "SUM").cpu().numpy()
+    assert dx.shape == (lod[-1], w)
+    for i in range(len(lod) - 1):
+        for r in range(lod[i], lod[i + 1]):
+            np.testing.assert_array_equal(dx[r], dout[i])
+
+
+def test_analyzer_seq_pool1_shape(env):
+    """The reference's end-to-end CTR inference test model in shape
+    (inference/tests/api/analyzer_seq_pool1_tester_helper.h:34,66-71,136-145): 154 slots of
+    pre-embedded LoD float rows, width 11 (2 CVM columns + 9), SUM pool -> cvm -> concat, which
+    seqpool_cvm_concat_fuse_pass turns into one fusion_seqpool_cvm_concat op.  The model file is
+    a download the reference does not ship, so values are random; the fused op must equal the
+    oracle slot by slot."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(154)
+    S, Bsz, w = 154, 16, 11
+    xs, lods = [], []
+    for s in range(S):
+        l = rng.integers(0, 5, Bsz)
+        lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+        x = rng.uniform(0.1, 1, (int(lod[-1]), w)).astype(np.float32)
+        x[:, 0] = rng.integers(1, 9, x.shape[0])
+        x[:, 1] = rng.integers(0, 2, x.shape[0])
+        xs.append(x)
+        lods.append(lod)
+    got = ops.fusion_seqpool_cvm_concat([_t(x, dev) for x in xs], [[l.tolist()] for l in lods], None, "SUM").cpu().numpy()
+    assert got.shape == (Bsz, S * w)
+    ids = [np.arange(x.shape[0], dtype=np.int64) for x in xs]
+    want = O.fused_forward(xs, ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE, concat=True, scale_mode=O.SCALE_RECIPROCAL)
+    _assert_cvm_close(got.reshape(Bsz, S, w), want.reshape(Bsz, S, w), True)

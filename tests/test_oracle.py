@@ -321,3 +321,17 @@ def test_backward_restatements_against_the_reference_formulas():
     np.testing.assert_array_equal(O.embedding_grad(g, ids, 5, padding_idx=2), want)
     with pytest.raises(IndexError):
         O.embedding_grad(g, np.array([0, 1, 5, 0, 0, 0]), 5)
+
+
+@pytest.mark.parametrize("lod", [[0, 10], [0, 2, 7, 10]])
+def test_reference_gtest_sequence_pooling_grad_sum(lod):
+    """The reference's own functor test, replayed on the oracle
+    (operators/math/sequence_pooling_test.cc:20-145): Out@GRAD[i, m] = i * 128 + m, width 128;
+    every row of sequence i of X@GRAD must equal row i of Out@GRAD, exactly."""
+    w = 128
+    dout = np.arange((len(lod) - 1) * w, dtype=np.float32).reshape(-1, w)
+    dx = O.sequence_pool_grad(dout, lod, "SUM")
+    assert dx.shape == (lod[-1], w)
+    for i in range(len(lod) - 1):
+        for r in range(lod[i], lod[i + 1]):
+            np.testing.assert_array_equal(dx[r], dout[i])
