@@ -8,6 +8,7 @@ model file on disk is not touched.  Two rewrites over a `ProgramDesc`
 
   retarget_ops   lookup_table_v2 -> b200_lookup_table_v2, sequence_pool -> b200_sequence_pool,
                  cvm -> b200_cvm: same inputs / outputs / attrs, 1:1.
+  fuse_seqpool_cvm_concat  the reference's own seqpool_cvm_concat_fuse_pass pattern (no gather)
   fuse_front_end every chain  lookup_table_v2(W, Ids_i) -> sequence_pool(pooltype P) -> cvm
                  whose slots share W, P, pad_value and use_cvm becomes ONE
                  ctr_fused_emb_seqpool_cvm(W, Ids@VECTOR) -> Out@VECTOR op writing the cvm
@@ -260,10 +261,83 @@ def fuse_front_end(program) -> int:
     return fused
 
 
+FUSION_CONCAT_OP = "b200_fusion_seqpool_cvm_concat"
+
+
+def fuse_seqpool_cvm_concat(program) -> int:
+    """The reference's seqpool_cvm_concat_fuse_pass on a ProgramDesc
+    (framework/ir/seqpool_cvm_concat_fuse_pass.cc:102-198): a concat(axis=1) whose every input is
+    the Y of a cvm(use_cvm=true) fed by the Out of a sequence_pool -- all with one pooltype out of
+    SUM / AVERAGE / SQRT (the pass itself matches SUM only; the fused op takes all three,
+    fusion_seqpool_cvm_concat_op.cc:132-157) and one CVM input -- becomes one
+    b200_fusion_seqpool_cvm_concat(X = the pools' inputs, CVM) -> the concat's Out, when nobody
+    else reads the intermediate variables.  Returns the number of concats fused."""
+    fused = 0
+    for blk in program.blocks:
+        use = _consumers(blk)
+        producer = {}
+        for i, op in enumerate(blk.ops):
+            for v in op.outputs:
+                for a in v.arguments:
+                    producer[a] = i
+        dead = set()
+        inserts = {}
+        for ki, cat in enumerate(blk.ops):
+            if cat.type != "concat" or int(op_attr(cat, "axis", 0)) != 1:
+                continue
+            xs, pools, cvms, cvm_in, pooltype, ok = [], [], [], None, None, True
+            for y in op_input(cat, "X"):
+                ci = producer.get(y)
+                if ci is None or blk.ops[ci].type != "cvm" or not op_attr(blk.ops[ci], "use_cvm", True) \
+                        or use.get(y, []) != [ki]:
+                    ok = False
+                    break
+                cvm = blk.ops[ci]
+                x = op_input(cvm, "X")
+                pi = producer.get(x[0]) if len(x) == 1 else None
+                if pi is None or blk.ops[pi].type != "sequence_pool" or use.get(x[0], []) != [ci]:
+                    ok = False
+                    break
+                pool = blk.ops[pi]
+                pt = op_attr(pool, "pooltype", "AVERAGE")
+                idx = op_output(pool, "MaxIndex")
+                c_in = op_input(cvm, "CVM")
+                if pt not in ("SUM", "AVERAGE", "SQRT") or (pooltype not in (None, pt)) or (idx and use.get(idx[0])) \
+                        or len(c_in) != 1 or (cvm_in not in (None, c_in[0])) or len(op_input(pool, "X")) != 1:
+                    ok = False
+                    break
+                pooltype, cvm_in = pt, c_in[0]
+                xs.append(op_input(pool, "X")[0])
+                pools.append(pi)
+                cvms.append(ci)
+            if not ok or not xs:
+                continue
+            op = make_op(FUSION_CONCAT_OP, {"X": xs, "CVM": [cvm_in]}, {"Out": op_output(cat, "Out")},
+                         [("pooltype", STRING, pooltype), ("use_cvm", BOOLEAN, True), ("axis", INT, 1)])
+            inserts[ki] = op
+            dead.update(pools + cvms + [ki])
+            fused += 1
+        if not inserts:
+            continue
+        new_ops = []
+        for i, op in enumerate(blk.ops):
+            if i in inserts:
+                new_ops.append(inserts[i])
+            if i not in dead:
+                cp = OpDesc()
+                cp.CopyFrom(op)
+                new_ops.append(cp)
+        del blk.ops[:]
+        for op in new_ops:
+            blk.ops.add().CopyFrom(op)
+    return fused
+
+
 def rewrite_program_bytes(pdmodel: bytes, fuse: bool = True) -> Tuple[bytes, Dict[str, int]]:
     """Parses a serialized ProgramDesc (`*.pdmodel`), applies the rewrites, serializes it again."""
     prog = ProgramDesc()
     prog.ParseFromString(pdmodel)
-    stats = {"fused_chains": fuse_front_end(prog) if fuse else 0}
+    stats = {"fused_chains": fuse_front_end(prog) if fuse else 0,
+             "fused_concats": fuse_seqpool_cvm_concat(prog) if fuse else 0}
     stats["retargeted_ops"] = retarget_ops(prog)
     return prog.SerializeToString(), stats

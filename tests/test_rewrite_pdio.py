@@ -40,7 +40,7 @@ def test_fuse_front_end_structure():
     prog = _front_end_program(4)
     raw = prog.SerializeToString()
     out, stats = R.rewrite_program_bytes(raw)
-    assert stats == {"fused_chains": 4, "retargeted_ops": 0}
+    assert stats == {"fused_chains": 4, "fused_concats": 0, "retargeted_ops": 0}
     new = R.ProgramDesc()
     new.ParseFromString(out)
     ops = [o.type for o in new.blocks[0].ops]
@@ -72,11 +72,50 @@ def test_fuse_groups_by_table_and_respects_other_consumers():
 def test_retarget_only():
     prog = _front_end_program(2)
     out, stats = R.rewrite_program_bytes(prog.SerializeToString(), fuse=False)
-    assert stats == {"fused_chains": 0, "retargeted_ops": 6}
+    assert stats == {"fused_chains": 0, "fused_concats": 0, "retargeted_ops": 6}
     new = R.ProgramDesc()
     new.ParseFromString(out)
     op = new.blocks[0].ops[1]
     assert op.type == "b200_sequence_pool" and R.op_attr(op, "pooltype") == "SUM" and R.op_input(op, "X") == ["rows_0"]
+
+
+def _pass_tester_program(second_pool_reads=None):
+    """The graph of TEST(SeqPoolCVMConcatFusePass, basic)
+    (framework/ir/seqpool_cvm_concat_fuse_pass_tester.cc:86-163): three sequence_pool(SUM)
+    a,b,c -> (MaxIndex d,f,h; Out e,g,i) -> cvm(use_cvm, CVM=n) -> j,k,l -> concat(axis 1) -> m."""
+    prog = R.ProgramDesc()
+    blk = prog.blocks.add()
+    blk.idx, blk.parent_idx = 0, -1
+    for x, idx, out in (("a", "d", "e"), ("b", "f", "g"), ("c", "h", "i")):
+        blk.ops.add().CopyFrom(R.make_op("sequence_pool", {"X": [x]}, {"MaxIndex": [idx], "Out": [out]},
+                                         [("pooltype", R.STRING, "SUM")]))
+    for x, y in (("e", "j"), ("g", "k"), ("i", "l")):
+        blk.ops.add().CopyFrom(R.make_op("cvm", {"X": [x], "CVM": ["n"]}, {"Y": [y]}, [("use_cvm", R.BOOLEAN, True)]))
+    blk.ops.add().CopyFrom(R.make_op("concat", {"X": ["j", "k", "l"]}, {"Out": ["m"]}, [("axis", R.INT, 1)]))
+    if second_pool_reads:
+        blk.ops.add().CopyFrom(R.make_op("scale", {"X": [second_pool_reads]}, {"Out": ["z"]}))
+    return prog
+
+
+def test_reference_fuse_pass_pattern():
+    """Same expectations as the reference's pass tester: seven ops become one
+    fusion op (its 16 removed + 1 added graph nodes are 6 ops + concat and their 9 intermediate
+    variables), inputs in concat order, CVM carried, axis kept."""
+    prog = _pass_tester_program()
+    assert R.fuse_seqpool_cvm_concat(prog) == 1
+    ops = prog.blocks[0].ops
+    assert [o.type for o in ops] == [R.FUSION_CONCAT_OP]
+    f = ops[0]
+    assert R.op_input(f, "X") == ["a", "b", "c"] and R.op_input(f, "CVM") == ["n"] and R.op_output(f, "Out") == ["m"]
+    assert (R.op_attr(f, "pooltype"), R.op_attr(f, "use_cvm"), R.op_attr(f, "axis")) == ("SUM", True, 1)
+    # an intermediate with a second reader keeps the whole concat as it was (then retargeted 1:1)
+    prog = _pass_tester_program(second_pool_reads="g")
+    assert R.fuse_seqpool_cvm_concat(prog) == 0
+    out, stats = R.rewrite_program_bytes(prog.SerializeToString())
+    assert stats == {"fused_chains": 0, "fused_concats": 0, "retargeted_ops": 6}
+    # through the byte-level entry
+    out, stats = R.rewrite_program_bytes(_pass_tester_program().SerializeToString())
+    assert stats == {"fused_chains": 0, "fused_concats": 1, "retargeted_ops": 0}
 
 
 # ------------------------------------------------------------------ the tensor stream
