@@ -166,6 +166,79 @@ PD_BUILD_OP(ctr_fused_emb_seqpool_cvm)
     .SetInferDtypeFn(PD_INFER_DTYPE(CtrFusedInferDtype));
 
 // ---------------------------------------------------------------------------------------
+// b200_fusion_seqpool_cvm_concat  (FusionSeqPoolCVMConcatOpMaker,
+// fused/fusion_seqpool_cvm_concat_op.cc:76-95): X (duplicable, pre-embedded LoD rows), CVM ->
+// Out [B, S*w]; what rewrite.fuse_seqpool_cvm_concat emits.  The jit kernel's reciprocal
+// scaling (refer.h:381-389), use_cvm must be true and axis 1 as the reference enforces.
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200FusionSeqpoolCvmConcat(const std::vector<paddle::Tensor>& xs, const paddle::Tensor& cvm,
+                                                       const std::string& pooltype, bool use_cvm, int axis) {
+  PD_CHECK(axis == 1, "fusion_seqpool_cvm_concat only supports concat axis=1 yet.");
+  PD_CHECK(use_cvm, "fusion_seqpool_cvm_concat only supports use_cvm is true yet.");
+  PD_CHECK(!xs.empty(), "Input(X) of fusion_seqpool_cvm_concat is empty");
+  NeedGpu(xs[0], "X");
+  const int64_t w = xs[0].numel() / xs[0].shape()[0];
+  const int64_t n = static_cast<int64_t>(xs.size());
+  const auto& lod0 = LodOf(xs[0]);
+  PD_CHECK(!lod0.empty(), "Input(X) must carry LoD");
+  const int64_t bs = static_cast<int64_t>(lod0[0].size()) - 1;
+  auto out = paddle::empty({bs, n * w}, xs[0].dtype(), xs[0].place());
+  const int es = xs[0].dtype() == paddle::DataType::FLOAT32 ? 4 : 2;
+  std::vector<ctrfe_slot> slots(xs.size());
+  for (size_t s = 0; s < xs.size(); ++s) {
+    const auto& lod = LodOf(xs[s]);
+    PD_CHECK(!lod.empty() && static_cast<int64_t>(lod[0].size()) - 1 == bs, "Batchsize of all inputs should be equal.");
+    PD_CHECK(xs[s].numel() / xs[s].shape()[0] == w, "Width of all inputs should be equal.");
+    ctrfe_slot& sl = slots[s];
+    sl.table = Raw(xs[s]);
+    sl.table_rows = xs[s].shape()[0];
+    sl.ids = nullptr;  // dense rows: row index = position
+    sl.lod = reinterpret_cast<const uint64_t*>(lod[0].data());
+    sl.n_seg = bs;
+    sl.out = static_cast<char*>(RawMut(out)) + static_cast<int64_t>(s) * w * es;
+    sl.out_ld = n * w;
+    sl.pooltype = PoolCode(pooltype);
+    sl.ids_dtype = CTRFE_I64;
+  }
+  ctrfe_fused_desc d{};
+  d.n_slots = static_cast<int32_t>(slots.size());
+  d.dtype = DtypeCode(xs[0].dtype());
+  d.slots = slots.data();
+  d.dim = w;
+  d.padding_idx = -1;
+  d.pad_value = 0.0f;
+  d.cvm_mode = CTRFE_CVM_USE;
+  d.cvm_offset = 2;
+  d.scale_mode = CTRFE_SCALE_RECIPROCAL;
+  d.init_mode = CTRFE_INIT_ZERO;
+  d.lod_location = CTRFE_LOD_HOST;
+  Check(ctrfe_fused_forward(CtxFor(xs[0]), &d, xs[0].stream()));
+  return {out};
+}
+
+std::vector<std::vector<int64_t>> B200FusionSeqpoolCvmConcatInferShape(const std::vector<std::vector<int64_t>>& x_shapes,
+                                                                       const std::vector<int64_t>& cvm_shape,
+                                                                       const std::string& pooltype, bool use_cvm,
+                                                                       int axis) {
+  int64_t w = 1;
+  for (size_t i = 1; i < x_shapes[0].size(); ++i) w *= x_shapes[0][i];
+  return {{-1, static_cast<int64_t>(x_shapes.size()) * w}};  // batch comes from the LoD at run time
+}
+
+std::vector<paddle::DataType> B200FusionSeqpoolCvmConcatInferDtype(const std::vector<paddle::DataType>& x_dtypes,
+                                                                   const paddle::DataType& cvm_dtype) {
+  return {x_dtypes[0]};
+}
+
+PD_BUILD_OP(b200_fusion_seqpool_cvm_concat)
+    .Inputs({paddle::Vec("X"), "CVM"})
+    .Outputs({"Out"})
+    .Attrs({"pooltype: std::string", "use_cvm: bool", "axis: int"})
+    .SetKernelFn(PD_KERNEL(B200FusionSeqpoolCvmConcat))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200FusionSeqpoolCvmConcatInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200FusionSeqpoolCvmConcatInferDtype));
+
+// ---------------------------------------------------------------------------------------
 // b200_lookup_table_v2  (LookupTableV2OpMaker, lookup_table_v2_op.cc:69-104)
 // ---------------------------------------------------------------------------------------
 std::vector<paddle::Tensor> B200LookupTableV2(const paddle::Tensor& w, const paddle::Tensor& ids,
