@@ -6,9 +6,9 @@
            fed exactly the rows a sample touches.
 * lengths  min(Poisson(L), 4L) with a deterministic 2 % of segments forced empty;
            L >= 100: round(LogNormal(ln L - 0.125, 0.5)) clipped to [0, 1024].
-* ids      rank r ~ Zipf(alpha = 1.05) on [1, N] drawn by inverse CDF of the continuous
-           power law on [0.5, N + 0.5) and rounded (P(r=1) = 0.087 at N = 1e8 against the
-           exact 0.079), then scattered: id = (r * 0x9E3779B97F4A7C15 mod 2^64) mod N.
+* ids      rank r ~ Zipf(alpha = 1.05) on [1, N] by inverse CDF: the exact discrete law for the
+           first 1e4 ranks (P(r=1) = 0.079 at N = 1e8), the continuous power law beyond, then
+           scattered: id = (r * 0x9E3779B97F4A7C15 mod 2^64) mod N.
 
 ids/lengths are drawn on ONE side (numpy) and copied, so both sides see the same batch.
 Bench/test tooling; nothing here is on the product path.
@@ -167,15 +167,48 @@ def draw_lengths(rng: np.random.Generator, n: int, mean_len: float) -> np.ndarra
     return l
 
 
+ZIPF_EXACT_HEAD = 10_000  # ranks drawn from the exact discrete law; beyond: the continuous power law
+
+
+_zipf_cache = {}
+
+
+def _zipf_head(n_rows: int, alpha: float):
+    """cdf of ranks 1..M under P(r) = r^-alpha / H(N, alpha), M = min(ZIPF_EXACT_HEAD, N); the mass
+    beyond M is the midpoint-rule integral of x^-alpha over [M + 0.5, N + 0.5) (relative error of
+    the normaliser < 1e-9 at M = 1e4)."""
+    key = (n_rows, alpha)
+    if key not in _zipf_cache:
+        m = min(ZIPF_EXACT_HEAD, n_rows)
+        w = np.arange(1, m + 1, dtype=np.float64) ** (-alpha)
+        a = 1.0 - alpha
+        tail = ((n_rows + 0.5) ** a - (m + 0.5) ** a) / a if n_rows > m else 0.0
+        z = w.sum() + tail
+        _zipf_cache[key] = (np.cumsum(w) / z, m)
+    return _zipf_cache[key]
+
+
 def zipf_ids(rng: np.random.Generator, k: int, n_rows: int, alpha: float = ALPHA) -> np.ndarray:
-    a = 1.0 - alpha
+    cdf, m = _zipf_head(n_rows, alpha)
     u = rng.random(k)
-    lo, hi = 0.5 ** a, (n_rows + 0.5) ** a
-    x = (lo + u * (hi - lo)) ** (1.0 / a)
-    r = np.clip(np.rint(x), 1, n_rows).astype(np.uint64)
+    r = np.empty(k, dtype=np.uint64)
+    head = u < cdf[-1]
+    r[head] = np.searchsorted(cdf, u[head], side="right") + 1
+    if n_rows > m:
+        a = 1.0 - alpha
+        ut = (u[~head] - cdf[-1]) / (1.0 - cdf[-1])
+        lo, hi = (m + 0.5) ** a, (n_rows + 0.5) ** a
+        x = (lo + ut * (hi - lo)) ** (1.0 / a)
+        r[~head] = np.clip(np.rint(x), m + 1, n_rows).astype(np.uint64)
+    else:
+        r[~head] = m
     with np.errstate(over="ignore"):
         ids = (r * _G) % np.uint64(n_rows)
     return ids.astype(np.int64)
+
+
+def zipf_rank1_probability(n_rows: int, alpha: float = ALPHA) -> float:
+    return float(_zipf_head(n_rows, alpha)[0][0])
 
 
 def hottest_id(n_rows: int) -> int:

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define CTRFE_VERSION 110 /* 0.1.1: descriptor grew (hot_cache, keymap); plan_launch_ex, grads */
+#define CTRFE_VERSION 120 /* 0.2.0: ctrfe_slot.n_ids, LoD checks on the device, plan_launch_many, fp64 cvm, router */
 
 /* ---- status codes ------------------------------------------------------------------ */
 enum {
@@ -72,7 +72,11 @@ enum {
   CTRFE_LOD_HOST = 0,   /* as Paddle holds them (tensor_meta.h:43); uploaded once per call,
                            all slots in ONE async copy, no stream sync (contrast
                            mixed_vector.cc:57-76, which syncs per sequence_pool call) */
-  CTRFE_LOD_DEVICE = 1  /* already resident in HBM; not validated */
+  CTRFE_LOD_DEVICE = 1  /* already resident in HBM (or in pinned host memory the GPU can read); cannot be
+                           validated on the host, so the kernels check every pair of offsets they read
+                           (non-decreasing, below 2^31, last <= n_ids: the CheckLoD rules,
+                           framework/lod_tensor.cc:116-142), pool an offending sequence as empty and
+                           record it for ctrfe_check_ids */
 };
 
 /* Opaque per-device context: pinned staging ring, device scratch, the bad-id flag. */
@@ -97,6 +101,10 @@ typedef struct ctrfe_slot {
   int64_t out_ld;
   int32_t pooltype;      /* CTRFE_POOL_* ("pooltype" attr) */
   int32_t ids_dtype;     /* CTRFE_I64 / CTRFE_I32 */
+  int64_t n_ids;         /* entries in `ids` (Ids.numel()); the last LoD offset must not exceed it, so a
+                            LoD longer than the id tensor is an error instead of a read past the end.
+                            Ignored when ids == NULL (table_rows then bounds the LoD, sequence_pool_op.h:52-60).
+                            A slot holds fewer than 2^31 ids. */
 } ctrfe_slot;
 
 /* Hot-row replica cache for the row-sharded mode.  CTR ids are Zipf-distributed: a few
@@ -177,7 +185,11 @@ int ctrfe_ctx_destroy(ctrfe_ctx* ctx);
 /* Bad-id report.  The kernels never fault on an out-of-range id: they treat the row as
  * zero and record the first offender.  This call synchronises `stream`, and returns
  * CTRFE_ERR_BAD_ID (filling slot / position / the id value when non-NULL) if any launch
- * since the last check saw one; the flag is then cleared.
+ * since the last check saw one; the flag is then cleared.  The record carries a tag of the
+ * plan (or one-shot call) that met the id, so with several plans in flight the id value is
+ * read from the right batch (tags are reused after 255 plans / calls).  A malformed
+ * CTRFE_LOD_DEVICE LoD met by a kernel is reported here too, as CTRFE_ERR_ARG with the slot and
+ * the sequence index (the sequence was pooled as empty).
  * Replaces the PADDLE_ENFORCE_LT/GE pair of embedding_kernel.cc:59-76 (the reference GPU
  * kernel has no check at all, embedding_kernel.cu:36-51). */
 int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* position, int64_t* id);
@@ -206,9 +218,17 @@ int ctrfe_plan_launch(ctrfe_plan* plan, void* stream);
  * the launch is an ordinary stream-ordered one.  No reference counterpart. */
 enum { CTRFE_LAUNCH_OVERLAP_PREVIOUS = 1 };
 int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags);
+/* n plans of one context launched back to back on `stream` in one call, with the same flags for
+ * each (CTRFE_LAUNCH_OVERLAP_PREVIOUS: every launch may start while the one before it drains) --
+ * the serving loop's inner step without a host-language call per batch.  No reference
+ * counterpart (the reference launches per op, per slot). */
+int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32_t flags);
 int ctrfe_plan_destroy(ctrfe_plan* plan);
 /* Number of kernels one ctrfe_plan_launch enqueues (for launch accounting). */
 int ctrfe_plan_num_kernels(const ctrfe_plan* plan);
+/* Name and template arguments of the kernel launch i of the plan runs (for profiles and bench
+ * records); "" when i is out of range.  Valid until the plan is destroyed. */
+const char* ctrfe_plan_kernel_name(const ctrfe_plan* plan, int i);
 
 /* ---- the fused front end without any allocation ------------------------------------
  * No counterpart in the reference.  Same computation and argument rules as
@@ -228,6 +248,9 @@ int ctrfe_plan_num_kernels(const ctrfe_plan* plan);
  *     example on two streams) race on it: serialise them.
  *   - The first call on a device looks up the array's device address; make that call before
  *     any stream capture starts.
+ *   - The LoD offsets are copied asynchronously straight from the caller's arrays: when those
+ *     live in pinned memory the copy really is asynchronous, so leave them untouched until
+ *     `stream` has reached the launch (with pageable memory the driver stages them first).
  *   - bad_id_key_host (may be NULL): host address that receives, once `stream` has reached
  *     this point, ~0 when every id was in range, else (slot << 44 | position) of the first
  *     offender (the row was treated as zeros, as ctrfe_check_ids documents). */

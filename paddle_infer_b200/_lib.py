@@ -24,7 +24,7 @@ LOD_HOST, LOD_DEVICE = 0, 1
 class Slot(C.Structure):
     _fields_ = [("table", C.c_void_p), ("table_rows", C.c_int64), ("ids", C.c_void_p),
                 ("lod", C.c_void_p), ("n_seg", C.c_int64), ("out", C.c_void_p),
-                ("out_ld", C.c_int64), ("pooltype", C.c_int32), ("ids_dtype", C.c_int32)]
+                ("out_ld", C.c_int64), ("pooltype", C.c_int32), ("ids_dtype", C.c_int32), ("n_ids", C.c_int64)]
 
 
 class HotCache(C.Structure):
@@ -70,7 +70,7 @@ _lib = None
 EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
-    "ctrfe_plan_num_kernels", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
+    "ctrfe_plan_num_kernels", "ctrfe_plan_launch_many", "ctrfe_plan_kernel_name", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
     "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build", "ctrfe_keymap_build",
@@ -97,6 +97,9 @@ def lib():
         L.ctrfe_plan_launch_ex.argtypes = [vp, vp, C.c_uint32]
         L.ctrfe_plan_destroy.argtypes = [vp]
         L.ctrfe_plan_num_kernels.argtypes = [vp]
+        L.ctrfe_plan_launch_many.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_uint32]
+        L.ctrfe_plan_kernel_name.argtypes = [vp, C.c_int]
+        L.ctrfe_plan_kernel_name.restype = C.c_char_p
         L.ctrfe_embedding.argtypes = [vp, vp, i64, i64, vp, i32, i64, i64, vp, vp]
         L.ctrfe_sequence_pool.argtypes = [vp, vp, i32, i64, vp, i64, i32, C.c_float, vp, vp, vp]
         L.ctrfe_cvm.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp]

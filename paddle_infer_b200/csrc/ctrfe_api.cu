@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 #include <utility>
 #include <vector>
 
@@ -60,8 +61,11 @@ struct ctrfe_ctx {
   // LoD image of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
   char* scratch = nullptr;
   size_t scratch_cap = 0;
-  std::vector<IdSource> last_ids;  // slots of the most recent fused launch
-  const void* last_ids_owner = nullptr;  // identity tag only (never dereferenced): skip re-copying
+  // Every plan and every one-shot call gets a tag (1..255, reused cyclically) that its launches OR
+  // into the error keys they record, so ctrfe_check_ids can fetch the offending id from the batch
+  // that met it even with several plans in flight.
+  std::vector<IdSource> tag_ids[256];
+  unsigned next_tag = 1;
   int sm_count = 148;
 };
 
@@ -82,6 +86,8 @@ struct ctrfe_plan {
   bool hot = false;      // sharded mode with a hot-row replica cache
   std::vector<char> all_max;  // per launch: every slot pools with MAX (selecting launches only)
   std::vector<IdSource> id_src;
+  unsigned tag = 0;
+  std::vector<std::string> kernel_names;  // per launch, for ctrfe_plan_kernel_name
 };
 
 namespace {
@@ -109,6 +115,12 @@ int elem_size(int dtype) {
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+unsigned take_tag(ctrfe_ctx* ctx) {
+  const unsigned t = ctx->next_tag;
+  ctx->next_tag = t % 255u + 1u;
+  return t;
+}
 
 int stage_acquire(ctrfe_ctx* ctx, size_t bytes, Staging** out) {
   Staging& s = ctx->ring[ctx->ring_next];
@@ -147,6 +159,7 @@ int scratch_reserve(ctrfe_ctx* ctx, size_t bytes, cudaStream_t stream) {
 // *lod_bytes = device bytes needed for the host LoDs (0 when they are already on the device).
 int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, size_t* lod_bytes) {
   if (!d || !d->slots || d->n_slots <= 0) return fail(CTRFE_ERR_ARG, "fused: no slots");
+  if (d->n_slots > 4096) return fail(CTRFE_ERR_ARG, "fused: %d slots exceed the limit of 4096 per call", d->n_slots);
   if (d->dtype != CTRFE_F32 && d->dtype != CTRFE_F16 && d->dtype != CTRFE_BF16)
     return fail(CTRFE_ERR_UNSUPPORTED, "fused: dtype %d not supported (f32, f16, bf16)", d->dtype);
   if (d->dim <= 0 || d->dim > (1 << 20)) return fail(CTRFE_ERR_ARG, "fused: bad dim %lld", (long long)d->dim);
@@ -214,6 +227,9 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
                                        (long long)sl.out_ld, d_out);
     if (sl.table_rows < 0 || sl.table_rows >= 0xfffffffeLL)
       return fail(CTRFE_ERR_UNSUPPORTED, "slot %d: table_rows %lld outside [0, 2^32 - 2)", s, (long long)sl.table_rows);
+    if (sl.ids && (sl.n_ids < 0 || sl.n_ids > 0x7fffffffLL))
+      return fail(CTRFE_ERR_ARG, "slot %d: n_ids %lld outside [0, 2^31) (a slot holds fewer than 2^31 ids)", s, (long long)sl.n_ids);
+    if (sl.out_ld * es >= (1LL << 32)) return fail(CTRFE_ERR_ARG, "slot %d: out_ld %lld too large", s, (long long)sl.out_ld);
     if (!sharded && reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
@@ -272,6 +288,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       ctrfe::KParams& k = plan->chunks[c];
       memset(&k, 0, sizeof(k));
       k.err = ctx->err_dev;
+      k.err_tag = static_cast<unsigned long long>(plan->tag) << ctrfe::kErrTagShift;
       k.padding_idx = d->padding_idx;
       k.dim = static_cast<int>(d->dim);
       k.row_bytes = static_cast<int>(row_bytes);
@@ -309,9 +326,11 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     o.ids = sl.ids;
     o.lod = reinterpret_cast<const unsigned long long*>(sl.lod);  // re-pointed for host LoDs
     o.out = static_cast<char*>(sl.out);
-    o.out_ld_bytes = sl.out_ld * es;
+    o.out_ld_bytes = static_cast<unsigned>(sl.out_ld * es);
     o.table_rows = static_cast<unsigned>(sl.table_rows);
     o.n_seg = static_cast<unsigned>(sl.n_seg);
+    // what every LoD offset is checked against: the id count, or -- dense rows -- the rows of X
+    o.n_ids = static_cast<unsigned>(sl.ids ? sl.n_ids : (sl.table_rows > 0x7fffffffLL ? 0x7fffffffLL : sl.table_rows));
     o.pooltype = static_cast<short>(sl.pooltype);
     o.id_kind = static_cast<short>(km ? 3 : (sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2));
     o.slot_index = s;
@@ -327,6 +346,21 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   plan->id_src.resize(d->n_slots);
   for (int s = 0; s < d->n_slots; ++s)
     plan->id_src[s] = IdSource{d->slots[s].ids, d->slots[s].ids_dtype == CTRFE_I32};
+  // the kernel each launch of this plan runs (mirrors launch_plan), for profiles and bench records
+  plan->kernel_names.clear();
+  for (size_t c = 0; c < plan->chunks.size(); ++c) {
+    static const char* const dtn[] = {"f32", "f16", "bf16"};
+    char buf[160];
+    const bool sh = plan->chunks[c].n_shards > 0;
+    if (plan->fast && plan->modes[c] == ctrfe::kModeAdd)
+      snprintf(buf, sizeof(buf), "ctrfe::fused_pool_fast_kernel<%s, %d-byte rows, cvm=%d, sharded=%d, hot=%d>", dtn[plan->dtype],
+               16 << plan->g_shift, plan->cvm_use ? 1 : 0, sh ? 1 : 0, sh && plan->chunks[c].hot_rows ? 1 : 0);
+    else
+      snprintf(buf, sizeof(buf), "ctrfe::fused_pool_kernel<%s, vect=%d, lanes=%d, %s, %d-byte lanes, sharded=%d>", dtn[plan->dtype],
+               plan->vect ? 1 : 0, 1 << plan->g_shift, plan->modes[c] == ctrfe::kModeSelect ? "select" : "add",
+               plan->chunk_bytes, sh ? 1 : 0);
+    plan->kernel_names.emplace_back(buf);
+  }
   *lod_bytes = d->lod_location == CTRFE_LOD_HOST ? lb : 0;
   return CTRFE_OK;
 }
@@ -354,8 +388,12 @@ int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_i
         prev = v;
       }
       if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
-      if (prev > (1ull << 43)) return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large", s,
-                                           (unsigned long long)prev);
+      if (prev >= (1ull << 31))
+        return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large (a slot holds fewer than 2^31 ids)", s,
+                    (unsigned long long)prev);
+      if (sl.ids && static_cast<int64_t>(prev) > sl.n_ids)
+        return fail(CTRFE_ERR_ARG, "slot %d: the last LoD offset (%llu) exceeds the number of ids (%lld)", s,
+                    (unsigned long long)prev, (long long)sl.n_ids);
       if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows)
         return fail(CTRFE_ERR_ARG,
                     "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)",
@@ -421,38 +459,9 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p, overlap);
 }
 
-// Which rows take the balanced-load kernel (fused_pool_bal_kernel).  None by default: once the
-// 16-bit kernels ran eight CTAs per SM the warp-level kernel overtook it on cfg3 (198 vs 219 us
-// per step; cfg4 on one GPU 602 vs 612), 64-byte rows always lost (the staging buffers cost the
-// L1 hits on the Zipf head), rows behind NVLink lost badly (527 vs 331 us on 2 GPUs) and cfg5's
-// long sequences turn it instruction-bound.  CTRFE_BAL=1: 128-byte rows; =2: also 64-byte rows;
-// =3: also 256 / 512-byte rows and the selecting (MAX) form.  Kept for A/B runs; every setting
-// is parity-tested (tests/test_gpu_parity.py::test_every_kernel_variant_passes_the_shape_sweep).
-int bal_mode() {
-  static const int mode = [] {
-    const char* e = getenv("CTRFE_BAL");
-    return e && e[0] ? atoi(e) : 0;
-  }();
-  return mode;
-}
-
 template <int DT, bool CVM, bool SH, bool HOT>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   using namespace ctrfe;
-  if constexpr (!SH) {
-    if ((gs == 3 && bal_mode() >= 1) || (gs == 2 && bal_mode() >= 2) || (gs >= 4 && bal_mode() >= 3)) {
-      // a warp takes M times the segments it takes in the other kernels
-      const int m = gs == 2 ? kBalM64 : (gs == 3 ? kBalM128 : 1);
-      const dim3 gb((grid.x + m - 1) / m, grid.y, 1);
-      switch (gs) {
-        case 2: launch_k(fused_pool_bal_kernel<DT, 2, CVM, false, false, kBalM64>, gb, st, p, overlap); break;
-        case 3: launch_k(fused_pool_bal_kernel<DT, 3, CVM, false, false, kBalM128>, gb, st, p, overlap); break;
-        case 4: launch_k(fused_pool_bal_kernel<DT, 4, CVM, false, false, 1>, gb, st, p, overlap); break;
-        default: launch_k(fused_pool_bal_kernel<DT, 5, CVM, false, false, 1>, gb, st, p, overlap); break;
-      }
-      return;
-    }
-  }
   switch (gs) {
     case 0: launch_k(fused_pool_fast_kernel<DT, 0, CVM, SH, HOT>, grid, st, p, overlap); break;
     case 1: launch_k(fused_pool_fast_kernel<DT, 1, CVM, SH, HOT>, grid, st, p, overlap); break;
@@ -460,17 +469,6 @@ void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, 
     case 3: launch_k(fused_pool_fast_kernel<DT, 3, CVM, SH, HOT>, grid, st, p, overlap); break;
     case 4: launch_k(fused_pool_fast_kernel<DT, 4, CVM, SH, HOT>, grid, st, p, overlap); break;
     default: launch_k(fused_pool_fast_kernel<DT, 5, CVM, SH, HOT>, grid, st, p, overlap); break;
-  }
-}
-
-// MAX over rows of 128 bytes and wider, no CVM, unsharded: the balanced-load kernel's selecting form
-template <int DT>
-void launch_bal_max(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
-  using namespace ctrfe;
-  switch (gs) {
-    case 3: launch_k(fused_pool_bal_kernel<DT, 3, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
-    case 4: launch_k(fused_pool_bal_kernel<DT, 4, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
-    default: launch_k(fused_pool_bal_kernel<DT, 5, false, false, false, 1, kModeSelect>, grid, st, p, overlap); break;
   }
 }
 
@@ -493,15 +491,6 @@ int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = fa
     // the launches of one plan work on different slots: the second may always start while the
     // first drains; the first does so only if the caller said it may (overlap_first)
     const bool overlap = overlap_first || c > 0;
-    if (plan.fast && m == ctrfe::kModeSelect && plan.all_max[c] && !plan.cvm_use && plan.g_shift >= 3 &&
-        plan.chunks[c].n_shards == 0 && bal_mode() >= 3) {
-      switch (plan.dtype) {
-        case CTRFE_F32: launch_bal_max<CTRFE_F32>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
-        case CTRFE_F16: launch_bal_max<CTRFE_F16>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
-        default: launch_bal_max<CTRFE_BF16>(plan.g_shift, plan.grids[c], st, plan.chunks[c], overlap); break;
-      }
-      continue;
-    }
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
         case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
@@ -558,9 +547,14 @@ int ctrfe_ctx_create(int device, ctrfe_ctx** out) {
   auto* c = new ctrfe_ctx();
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&c->err_dev), 8);
-  if (e == cudaSuccess) e = cudaMemset(c->err_dev, 0xff, 8);
-  if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), 16, cudaHostAllocDefault);
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&c->err_dev), 16);
+  if (e == cudaSuccess) e = cudaMemset(c->err_dev, 0xff, 16);
+  if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), 32, cudaHostAllocDefault);
+  if (e == cudaSuccess) {  // the CVM log table of this device (idempotent: every context refills the same values)
+    ctrfe::cvm_table_fill_kernel<<<(ctrfe::kCvmTab + 255) / 256, 256>>>();
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  }
   if (e != cudaSuccess) {
     ctrfe_ctx_destroy(c);
     return fail(CTRFE_ERR_CUDA, "ctx_create: %s", cudaGetErrorString(e));
@@ -588,16 +582,30 @@ int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* positi
   if (!ctx) return fail(CTRFE_ERR_ARG, "check_ids: null ctx");
   DeviceGuard g(ctx->device);
   auto st = static_cast<cudaStream_t>(stream);
-  CU(cudaMemcpyAsync(ctx->err_host, ctx->err_dev, 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(ctx->err_host, ctx->err_dev, 16, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  const unsigned long long key = ctx->err_host[0];
-  if (key == ~0ull) return CTRFE_OK;
-  CU(cudaMemsetAsync(ctx->err_dev, 0xff, 8, st));
-  const int64_t s = static_cast<int64_t>(key >> 44);
-  const int64_t pos = static_cast<int64_t>(key & ((1ull << 44) - 1));
+  const unsigned long long key = ctx->err_host[0], lod_key = ctx->err_host[1];
+  if (key == ~0ull && lod_key == ~0ull) return CTRFE_OK;
+  CU(cudaMemsetAsync(ctx->err_dev, 0xff, 16, st));
+  constexpr unsigned long long kPosMask = (1ull << ctrfe::kErrSlotShift) - 1;
+  constexpr unsigned long long kSlotMask = (1ull << (ctrfe::kErrTagShift - ctrfe::kErrSlotShift)) - 1;
+  if (lod_key != ~0ull) {  // a kernel met a malformed CTRFE_LOD_DEVICE LoD (the CheckLoD rules, lod_tensor.cc:116-142)
+    const int64_t s = static_cast<int64_t>((lod_key >> ctrfe::kErrSlotShift) & kSlotMask);
+    const int64_t seq = static_cast<int64_t>(lod_key & kPosMask);
+    if (slot) *slot = s;
+    if (position) *position = seq;
+    if (id) *id = -1;
+    return fail(CTRFE_ERR_ARG,
+                "slot %lld: the LoD offsets of sequence %lld are decreasing or exceed the number of ids "
+                "(the sequence was pooled as empty)", (long long)s, (long long)seq);
+  }
+  const unsigned tag = static_cast<unsigned>(key >> ctrfe::kErrTagShift);
+  const int64_t s = static_cast<int64_t>((key >> ctrfe::kErrSlotShift) & kSlotMask);
+  const int64_t pos = static_cast<int64_t>(key & kPosMask);
   long long bad = -1;
-  if (s < static_cast<int64_t>(ctx->last_ids.size()) && ctx->last_ids[s].ids) {
-    const IdSource& src = ctx->last_ids[s];
+  const std::vector<IdSource>& srcs = ctx->tag_ids[tag & 255u];
+  if (s < static_cast<int64_t>(srcs.size()) && srcs[s].ids) {
+    const IdSource& src = srcs[s];
     if (src.ids_i32) {
       int v = 0;
       CU(cudaMemcpyAsync(&v, static_cast<const int*>(src.ids) + pos, 4, cudaMemcpyDeviceToHost, st));
@@ -621,9 +629,11 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
   if (!ctx || !out) return fail(CTRFE_ERR_ARG, "plan_create: null ctx / out");
   DeviceGuard g(ctx->device);
   auto* plan = new ctrfe_plan();
+  plan->tag = take_tag(ctx);
   size_t bytes = 0;
   int rc = plan_geometry(ctx, desc, plan, &bytes);
   if (rc) { delete plan; return rc; }
+  ctx->tag_ids[plan->tag] = plan->id_src;
   if (bytes) {
     char* dev = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
@@ -642,10 +652,6 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
 int ctrfe_plan_launch(ctrfe_plan* plan, void* stream) {
   if (!plan) return fail(CTRFE_ERR_ARG, "plan_launch: null plan");
   DeviceGuard g(plan->ctx->device);
-  if (plan->ctx->last_ids_owner != plan) {
-    plan->ctx->last_ids = plan->id_src;
-    plan->ctx->last_ids_owner = plan;
-  }
   return launch_plan(*plan, static_cast<cudaStream_t>(stream));
 }
 
@@ -653,17 +659,28 @@ int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags) {
   if (!plan) return fail(CTRFE_ERR_ARG, "plan_launch_ex: null plan");
   if (flags & ~static_cast<uint32_t>(CTRFE_LAUNCH_OVERLAP_PREVIOUS)) return fail(CTRFE_ERR_ARG, "plan_launch_ex: unknown flag");
   DeviceGuard g(plan->ctx->device);
-  if (plan->ctx->last_ids_owner != plan) {
-    plan->ctx->last_ids = plan->id_src;
-    plan->ctx->last_ids_owner = plan;
-  }
   return launch_plan(*plan, static_cast<cudaStream_t>(stream), (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0);
+}
+
+int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32_t flags) {
+  if (!plans || n < 0) return fail(CTRFE_ERR_ARG, "plan_launch_many: bad argument");
+  if (flags & ~static_cast<uint32_t>(CTRFE_LAUNCH_OVERLAP_PREVIOUS)) return fail(CTRFE_ERR_ARG, "plan_launch_many: unknown flag");
+  if (n == 0) return CTRFE_OK;
+  for (int i = 0; i < n; ++i)
+    if (!plans[i] || plans[i]->ctx != plans[0]->ctx) return fail(CTRFE_ERR_ARG, "plan_launch_many: plan %d is null or of another context", i);
+  DeviceGuard g(plans[0]->ctx->device);
+  const bool overlap = (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0;
+  auto st = static_cast<cudaStream_t>(stream);
+  for (int i = 0; i < n; ++i) {
+    const int rc = launch_plan(*plans[i], st, overlap);
+    if (rc) return rc;
+  }
+  return CTRFE_OK;
 }
 
 int ctrfe_plan_destroy(ctrfe_plan* plan) {
   if (!plan) return CTRFE_OK;
   DeviceGuard g(plan->ctx->device);
-  if (plan->ctx->last_ids_owner == plan) plan->ctx->last_ids_owner = nullptr;
   if (plan->owns_dev && plan->dev) {
     cudaDeviceSynchronize();
     cudaFree(plan->dev);
@@ -674,11 +691,17 @@ int ctrfe_plan_destroy(ctrfe_plan* plan) {
 
 int ctrfe_plan_num_kernels(const ctrfe_plan* plan) { return plan ? static_cast<int>(plan->chunks.size()) : 0; }
 
+const char* ctrfe_plan_kernel_name(const ctrfe_plan* plan, int i) {
+  if (!plan || i < 0 || i >= static_cast<int>(plan->kernel_names.size())) return "";
+  return plan->kernel_names[i].c_str();
+}
+
 int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream) {
   if (!ctx) return fail(CTRFE_ERR_ARG, "fused_forward: null ctx");
   DeviceGuard g(ctx->device);
   auto st = static_cast<cudaStream_t>(stream);
   ctrfe_plan plan;
+  plan.tag = take_tag(ctx);
   size_t bytes = 0;
   int rc = plan_geometry(ctx, desc, &plan, &bytes);
   if (rc) return rc;
@@ -686,8 +709,7 @@ int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stre
   if (rc) return rc;
   rc = plan_upload(ctx, desc, st, ctx->scratch, bytes, &plan);
   if (rc) return rc;
-  ctx->last_ids.swap(plan.id_src);
-  ctx->last_ids_owner = nullptr;
+  ctx->tag_ids[plan.tag].swap(plan.id_src);
   return launch_plan(plan, st);
 }
 
@@ -711,8 +733,7 @@ int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64
   const long long cap = static_cast<long long>(ctx->sm_count) * 8 * 4;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  ctx->last_ids.assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
-  ctx->last_ids_owner = nullptr;
+  ctx->tag_ids[0].assign(1, IdSource{ids, ids_dtype == CTRFE_I32});  // the unfused ops record untagged keys
   const char* t = static_cast<const char*>(table);
   char* o = static_cast<char*>(out);
   const int i32 = ids_dtype == CTRFE_I32;
@@ -783,8 +804,8 @@ int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t wi
 int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_t width, int32_t use_cvm,
               void* y, void* stream) {
   if (!ctx) return fail(CTRFE_ERR_ARG, "cvm: null ctx");
-  if (dtype != CTRFE_F32 && dtype != CTRFE_F16 && dtype != CTRFE_BF16)
-    return fail(CTRFE_ERR_UNSUPPORTED, "cvm: dtype %d not supported (f32, f16, bf16)", dtype);
+  if (dtype != CTRFE_F32 && dtype != CTRFE_F16 && dtype != CTRFE_BF16 && dtype != CTRFE_F64)
+    return fail(CTRFE_ERR_UNSUPPORTED, "cvm: dtype %d not supported (f32, f64, f16, bf16)", dtype);
   if (width < 2) return fail(CTRFE_ERR_ARG, "cvm: Input(X) needs at least the show and click columns (width=%lld)", (long long)width);
   if (rows < 0) return fail(CTRFE_ERR_ARG, "cvm: negative rows");
   const long long wo = use_cvm ? width : width - 2;
@@ -797,6 +818,9 @@ int ctrfe_cvm(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t rows, int64_
   const char* xc = static_cast<const char*>(x);
   char* yc = static_cast<char*>(y);
   switch (dtype) {
+    case CTRFE_F64:
+      ctrfe::cvm_f64_kernel<<<blocks, 256, 0, st>>>(static_cast<const double*>(x), rows, (int)width, use_cvm, static_cast<double*>(y));
+      break;
     case CTRFE_F32: ctrfe::cvm_kernel<CTRFE_F32><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
     case CTRFE_F16: ctrfe::cvm_kernel<CTRFE_F16><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
     default: ctrfe::cvm_kernel<CTRFE_BF16><<<blocks, 256, 0, st>>>(xc, rows, (int)width, use_cvm, yc); break;
@@ -813,6 +837,8 @@ int ctrfe_keymap_build(ctrfe_ctx* ctx, const uint64_t* keys, int64_t n, uint64_t
   if (n == 0) return CTRFE_OK;
   DeviceGuard g(ctx->device);
   const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+  // rows start at all ones so that duplicate keys resolve to their FIRST occurrence (atomicMin)
+  CU(cudaMemsetAsync(map_rows, 0xff, sizeof(uint32_t) << log2_slots, static_cast<cudaStream_t>(stream)));
   ctrfe::keymap_insert_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const unsigned long long*>(keys), n, reinterpret_cast<unsigned long long*>(map_keys), map_rows,
       (1u << log2_slots) - 1u, 64 - log2_slots, n_unplaced);
@@ -906,8 +932,7 @@ int ctrfe_embedding_grad(ctrfe_ctx* ctx, const float* dout, const void* ids, int
   auto st = static_cast<cudaStream_t>(stream);
   CU(cudaMemsetAsync(dw, 0, static_cast<size_t>(table_rows) * dim * sizeof(float), st));
   if (n_ids > 0) {
-    ctx->last_ids.assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
-    ctx->last_ids_owner = nullptr;
+    ctx->tag_ids[0].assign(1, IdSource{ids, ids_dtype == CTRFE_I32});
     const long long total = n_ids * dim;
     ctrfe::embedding_grad_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
         dout, ids, ids_dtype == CTRFE_I32, n_ids, table_rows, static_cast<int>(dim), padding_idx, dw, ctx->err_dev);
@@ -1196,6 +1221,8 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
     if (sl.ids_dtype != CTRFE_I64 && sl.ids_dtype != CTRFE_I32) return fail(CTRFE_ERR_UNSUPPORTED, "static: slot %d: ids must be int32 or int64", s);
     if (sl.out_ld < d_out) return fail(CTRFE_ERR_ARG, "static: slot %d: out_ld %lld < output width %d", s, (long long)sl.out_ld, d_out);
     if (sl.table_rows < 0 || sl.table_rows >= 0xfffffffeLL) return fail(CTRFE_ERR_UNSUPPORTED, "static: slot %d: table_rows outside [0, 2^32 - 2)", s);
+    if (sl.ids && (sl.n_ids < 0 || sl.n_ids > 0x7fffffffLL)) return fail(CTRFE_ERR_ARG, "static: slot %d: n_ids outside [0, 2^31)", s);
+    if (sl.out_ld * es >= (1LL << 32)) return fail(CTRFE_ERR_ARG, "static: slot %d: out_ld too large", s);
     if (reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     if (sl.n_seg > max_seg) max_seg = sl.n_seg;
     lod_bytes += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
@@ -1205,7 +1232,10 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
       bool mono = true;
       for (int64_t i = 1; i <= sl.n_seg; ++i) { mono &= sl.lod[i] >= prev; prev = sl.lod[i]; }
       if (!mono) return fail(CTRFE_ERR_ARG, "static: slot %d: LoD offsets must be non-decreasing", s);
-      if (prev >= (1ull << 32)) return fail(CTRFE_ERR_ARG, "static: slot %d: a slot holds < 2^32 ids", s);
+      if (prev >= (1ull << 31)) return fail(CTRFE_ERR_ARG, "static: slot %d: a slot holds fewer than 2^31 ids", s);
+      if (sl.ids && static_cast<int64_t>(prev) > sl.n_ids)
+        return fail(CTRFE_ERR_ARG, "static: slot %d: the last LoD offset (%llu) exceeds the number of ids (%lld)", s,
+                    (unsigned long long)prev, (long long)sl.n_ids);
       if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows) return fail(CTRFE_ERR_ARG, "static: slot %d: last LoD offset exceeds the rows of X", s);
     }
   }
@@ -1220,7 +1250,7 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
   unsigned char* lod_img = scratch + CTRFE_STATIC_FLAG_BYTES;
 
   // the flag starts at "no bad id" (all ones) on every call; the LoD image is overwritten
-  CU(cudaMemsetAsync(flag, 0xff, 8, st));
+  CU(cudaMemsetAsync(flag, 0xff, 16, st));  // both error words (bad id, bad LoD pair)
 
   ctrfe::KParams k;  // 3.7 KB, on the stack
   memset(&k, 0, sizeof(k));
@@ -1247,9 +1277,10 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
     o.ids = sl.ids;
     o.lod = reinterpret_cast<const unsigned long long*>(lod_img + off);
     o.out = static_cast<char*>(sl.out);
-    o.out_ld_bytes = sl.out_ld * es;
+    o.out_ld_bytes = static_cast<unsigned>(sl.out_ld * es);
     o.table_rows = static_cast<unsigned>(sl.table_rows);
     o.n_seg = static_cast<unsigned>(sl.n_seg);
+    o.n_ids = static_cast<unsigned>(sl.ids ? sl.n_ids : (sl.table_rows > 0x7fffffffLL ? 0x7fffffffLL : sl.table_rows));
     o.pooltype = static_cast<short>(sl.pooltype);
     o.id_kind = static_cast<short>(sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2);
     o.slot_index = s;

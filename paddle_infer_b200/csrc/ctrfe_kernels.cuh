@@ -37,7 +37,10 @@ namespace ctrfe {
 #define CTRFE_MINB16 8
 #endif
 
-constexpr int kThreads = 256;          // threads per CTA of the pooling kernel
+#ifndef CTRFE_THREADS
+#define CTRFE_THREADS 256
+#endif
+constexpr int kThreads = CTRFE_THREADS; // threads per CTA of the pooling kernel
 constexpr int kUnroll = 4;             // row loads in flight per lane
 constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters (block <= 4 KB)
 constexpr int kMaxShards = 8;           // GPUs of one NVSwitch box
@@ -55,16 +58,25 @@ struct SlotK {
   const void* ids;                 // int64 / int32
   const unsigned long long* lod;   // device offsets [n_seg + 1]
   char* out;
-  long long out_ld_bytes;          // bytes between consecutive output rows
+  unsigned int out_ld_bytes;       // bytes between consecutive output rows (< 2^32)
   unsigned int table_rows;         // < 2^32 - 2
   unsigned int n_seg;
+  unsigned int n_ids;              // entries in ids (dense rows: table_rows); every LoD offset must be <= it (< 2^31)
   short pooltype;
   short id_kind;                   // 0 int64, 1 int32, 2 dense (row index = position), 3 uint64 feasign keys (key map)
   int slot_index;                  // position in the caller's slot array (bad-id report)
 };
+static_assert(sizeof(SlotK) == 56, "slot descriptor layout");
+
+// Error records: err[0] = min over keys of out-of-range ids, err[1] = min over keys of malformed
+// LoD pairs met by a kernel; ~0 = none.  key = tag << 56 | slot << 44 | position (or sequence),
+// tag = the plan / call the launch belongs to (0 for the static entry point).
+constexpr int kErrSlotShift = 44;
+constexpr int kErrTagShift = 56;
 
 struct KParams {
-  unsigned long long* err;   // [0]: min over (slot << 44 | position) of bad ids, ~0 = none
+  unsigned long long* err;   // [2], see above
+  unsigned long long err_tag;  // tag << kErrTagShift, OR-ed into every key this launch records
   long long padding_idx;
   int dim;
   int row_bytes;
@@ -97,6 +109,23 @@ struct KParams {
 static_assert(sizeof(KParams) <= 4096, "kernel parameter block must stay within 4 KB");
 
 __device__ __forceinline__ uint4 ldg128(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+__device__ __forceinline__ unsigned long long err_key(const KParams& kp, const SlotK* slp, unsigned long long pos) {
+  return kp.err_tag | (static_cast<unsigned long long>(slp->slot_index) << kErrSlotShift) | pos;
+}
+
+// The [start, end) id range of sequence `seg`, with the CheckLoD rules (framework/lod_tensor.cc:
+// 116-142) applied to the pair that is read: non-decreasing and inside the id array (n_ids < 2^31,
+// so one 64-bit compare also rejects offsets with a non-zero high word).  An offending sequence
+// is pooled as empty and recorded in err[1]; the kernel never reads past the ids it was given.
+__device__ __forceinline__ void seg_bounds(const KParams& kp, const SlotK* slp, unsigned seg, uint32_t& start, int& len) {
+  const unsigned long long a = __ldg(slp->lod + seg);
+  const unsigned long long b = __ldg(slp->lod + seg + 1);
+  const bool ok = a <= b && b <= static_cast<unsigned long long>(slp->n_ids);
+  start = static_cast<uint32_t>(a);
+  len = ok ? static_cast<int>(static_cast<uint32_t>(b) - static_cast<uint32_t>(a)) : 0;
+  if (!ok) atomicMin(kp.err + 1, err_key(kp, slp, seg));
+}
 
 template <int DT>
 __device__ __forceinline__ float elem_to_float(uint32_t bits16_or_32) {
@@ -212,6 +241,29 @@ __device__ __forceinline__ double cvm_log1(float x) {
   return log(a);  // zero, negative, inf, NaN: the library's special-case results
 }
 
+// log(x + 1) for the show / click sums CTR data actually carries: small non-negative integers.
+// g_cvm_log_tab[n] holds cvm_log1(float(n)) -- filled on the device by cvm_table_fill_kernel with
+// the very routine above, so a table hit returns the same bits as the evaluation it replaces
+// (tests/test_gpu_parity.py compares both paths); anything else falls through to cvm_log1.
+// The fp64 evaluation was 37 % of the specialised kernel's instruction stream.
+constexpr int kCvmTab = 4096;
+__device__ double g_cvm_log_tab[kCvmTab];
+
+__global__ void cvm_table_fill_kernel() {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n < kCvmTab) g_cvm_log_tab[n] = cvm_log1(static_cast<float>(n));
+}
+
+__device__ __forceinline__ double cvm_log1_tab(float x) {
+#ifndef CTRFE_NO_CVM_TABLE
+  if (x >= 0.0f && x < static_cast<float>(kCvmTab)) {
+    const int n = static_cast<int>(x);
+    if (static_cast<float>(n) == x) return __ldg(&g_cvm_log_tab[n]);
+  }
+#endif
+  return cvm_log1(x);
+}
+
 // Pin a value in a register: stops ptxas from re-deriving it from the (dynamically indexed)
 // parameter bank inside the row loop.
 #define CTRFE_KEEP64(x) asm volatile("" : "+l"(x))
@@ -263,9 +315,11 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
 
   long long start = 0, end = 0;
   if (seg_ok) {
-    const unsigned long long* __restrict__ lod = slp->lod;
-    start = static_cast<long long>(__ldg(lod + seg));
-    end = static_cast<long long>(__ldg(lod + seg + 1));
+    uint32_t s0;
+    int l0;
+    seg_bounds(kp, slp, seg, s0, l0);
+    start = static_cast<long long>(s0);
+    end = start + l0;
   }
   const int seg_len = static_cast<int>(end - start);  // rows of the sequence (for the scale)
   if (selecting && seg_len > 0) {  // LAST / FIRST read exactly one row
@@ -339,8 +393,7 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
     const bool in_range = hi == 0u && lo < table_rows;  // table_rows < 2^32 - 2
     const bool is_pad = pad_on && lo == pad_lo && hi == pad_hi;
     if (!in_range && !is_pad && tile == 0) {
-      atomicMin(kp.err, (static_cast<unsigned long long>(slp->slot_index) << 44) |
-                            static_cast<unsigned long long>(start + off));
+      atomicMin(kp.err, err_key(kp, slp, static_cast<unsigned long long>(start + off)));
     }
     return (in_range && !is_pad) ? lo : kZero;
   };
@@ -519,7 +572,7 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
 
   if (!(seg_ok && col_ok)) return;
   const int skip = kp.cvm_mode == CTRFE_CVM_STRIP ? kp.cvm_offset : 0;
-  char* orow = slp->out + static_cast<long long>(seg) * slp->out_ld_bytes;
+  char* orow = slp->out + static_cast<unsigned long long>(seg) * slp->out_ld_bytes;
 
   uint32_t packed[RW];
 #pragma unroll
@@ -671,6 +724,23 @@ __global__ void cvm_kernel(const char* __restrict__ x, long long rows, int width
   else *reinterpret_cast<unsigned short*>(q) = static_cast<unsigned short>(b);
 }
 
+// cvm on double rows (the reference registers CVMCUDAKernel<double>, cvm_op.cu:192-194): everything
+// in fp64 with the library log, as CvmComputeKernel<double> does (cvm_op.cu:28-47).
+__global__ void cvm_f64_kernel(const double* __restrict__ x, long long rows, int width, int use_cvm, double* __restrict__ y) {
+  const int wo = use_cvm ? width : width - 2;
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= rows * wo) return;
+  const long long r = t / wo;
+  const int c = static_cast<int>(t - r * wo);
+  const double* xr = x + r * width;
+  double v;
+  if (!use_cvm) v = xr[c + 2];
+  else if (c >= 2) v = xr[c];
+  else if (c == 0) v = log(xr[0] + 1.0);
+  else v = log(xr[1] + 1.0) - log(xr[0] + 1.0);
+  y[t] = v;
+}
+
 // Fills a feasign key map: keys[i] -> row i.  Open addressing, linear probing, 0 = empty slot
 // (key 0 is the padding feasign and is never stored).  A key that finds no slot within
 // kKeyProbes is counted in *n_unplaced (the caller rebuilds with more slots).
@@ -684,7 +754,7 @@ __global__ void keymap_insert_kernel(const unsigned long long* __restrict__ keys
   for (int pr = 0; pr < kKeyProbes; ++pr) {
     const unsigned long long old = atomicCAS(map_keys + h, 0ull, key);
     if (old == 0ull || old == key) {
-      map_rows[h] = static_cast<unsigned>(i);
+      atomicMin(map_rows + h, static_cast<unsigned>(i));  // duplicate keys: the first occurrence wins, whatever the schedule
       return;
     }
     h = (h + 1u) & mask;

@@ -67,6 +67,8 @@ class Context:
         rc = B.lib().ctrfe_check_ids(self.handle, self.stream(), C.byref(s), C.byref(p), C.byref(i))
         if rc == B.ERR_BAD_ID:
             raise B.BadIdError(B.lib().ctrfe_last_error().decode(), s.value, p.value, i.value)
+        if rc == B.ERR_ARG:  # a kernel met a malformed device-resident LoD (framework CheckLoD)
+            raise InvalidArgument(B.lib().ctrfe_last_error().decode())
         B.check(rc)
 
     def close(self):
@@ -196,8 +198,8 @@ def cvm(X: torch.Tensor, CVM: Optional[torch.Tensor] = None, use_cvm: bool = Tru
     _need_cuda(X, "X")
     if X.dim() != 2:
         raise InvalidArgument(f"Input(X)'s rank should be 2, but got {X.dim()}")
-    if X.dtype not in (torch.float32, torch.float16, torch.bfloat16):
-        raise Unimplemented(f"cvm: dtype {X.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    if X.dtype not in _DT:
+        raise Unimplemented(f"cvm: dtype {X.dtype} has no sm_100a kernel (float32/float64/float16/bfloat16)")
     ctx = ctx or default_context(X.device)
     X = X.contiguous()
     rows, w = X.shape
@@ -317,6 +319,9 @@ class FusedPlan:
     def num_kernels(self) -> int:
         return B.lib().ctrfe_plan_num_kernels(self.handle)
 
+    def kernel_names(self) -> List[str]:
+        return [B.lib().ctrfe_plan_kernel_name(self.handle, i).decode() for i in range(self.num_kernels())]
+
     def close(self):
         if self.handle:
             B.lib().ctrfe_plan_destroy(self.handle)
@@ -327,6 +332,16 @@ class FusedPlan:
             self.close()
         except Exception:
             pass
+
+
+def launch_many(plans: Sequence[FusedPlan], overlap_previous: bool = False) -> None:
+    """Launch several prepared batches back to back with ONE call into the library
+    (ctrfe_plan_launch_many): the inner step of a serving loop without a Python call per batch."""
+    if not plans:
+        return
+    arr = (C.c_void_p * len(plans))(*[p.handle.value for p in plans])
+    B.check(B.lib().ctrfe_plan_launch_many(arr, len(plans), plans[0].ctx.stream(),
+                                           B.LAUNCH_OVERLAP_PREVIOUS if overlap_previous else 0))
 
 
 class _TableRef:
@@ -358,7 +373,7 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
         i = ids[s]
         slots[s] = B.Slot(t.data_ptr(), t.shape[0], i.data_ptr() if i is not None else None, lod_ptr, n_seg,
                           outs[s].data_ptr(), out_ld, B.POOLTYPES[pooltypes[s]],
-                          _IDT[i.dtype] if i is not None else B.I64)
+                          _IDT[i.dtype] if i is not None else B.I64, i.numel() if i is not None else 0)
     desc = B.FusedDesc(S, dtype, slots, dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset, scale_mode,
                        init_mode, B.LOD_DEVICE if lod_on_device else B.LOD_HOST, 0)
     if sharded is not None:
@@ -603,8 +618,10 @@ class HostFrontEnd:
     host buffers and writes the pooled rows into the pinned output, over PCIe, inside the one
     launch -- no staging copies, and the transfers overlap the table gathers by construction.
     The buffers must be pinned (cudaHostAlloc / torch pin_memory) so the device can address
-    them; LoD offsets are then not validated on the host (as with CTRFE_LOD_DEVICE).  A serving
-    loop that reuses its I/O buffers binds them once (bind()) and then only launches.
+    them; the LoD offsets are then checked by the kernel itself, pair by pair as it reads them
+    (CTRFE_LOD_DEVICE: non-decreasing, inside the id buffer), and an offending sequence is pooled
+    as empty and reported by ctx.check_ids().  A serving loop that reuses its I/O buffers binds
+    them once (bind()) and then only launches; a bound id buffer is used up to its full length.
     mode="copy": explicit H2D copies of the ids, host-validated LoD upload, launch, D2H copy."""
 
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
@@ -660,7 +677,7 @@ class HostFrontEnd:
             t = self.tables[s]
             slots[s] = B.Slot(t.data_ptr(), t.shape[0], ids_host[s].data_ptr(), lods_host[s].data_ptr(),
                               lods_host[s].numel() - 1, outs[s].data_ptr(), ld, B.POOLTYPES[self.pools[s]],
-                              _IDT[ids_host[s].dtype])
+                              _IDT[ids_host[s].dtype], ids_host[s].numel())
         desc = B.FusedDesc(S, _DT[self._dtype], slots, self.dim, int(self.kw["padding_idx"]),
                            float(self.kw["pad_value"]), cvm_mode, self.kw["cvm_offset"], B.SCALE_DIVIDE,
                            B.INIT_ZERO, B.LOD_DEVICE, 0)

@@ -95,6 +95,7 @@ int main(void) {
     slots[s].out_ld = D;
     slots[s].pooltype = pooltypes[s];
     slots[s].ids_dtype = CTRFE_I64;
+    slots[s].n_ids = (int64_t)(sizeof(ids[s]) / sizeof(ids[s][0]));
   }
   ctrfe_fused_desc desc;
   memset(&desc, 0, sizeof(desc));

@@ -62,8 +62,8 @@ def test_python_enums_match_header(built):
 
 
 def test_struct_layouts_match_header(built):
-    # ctrfe_slot: 7 x 8-byte fields + 2 x int32; ctrfe_fused_desc: see header
-    assert C.sizeof(built.Slot) == 64
+    # ctrfe_slot: 7 x 8-byte fields + 2 x int32 + n_ids; ctrfe_fused_desc: see header
+    assert C.sizeof(built.Slot) == 72 and built.Slot.n_ids.offset == 64
     assert C.sizeof(built.FusedDesc) == 88 and built.FusedDesc.hot_cache.offset == 72
     assert built.FusedDesc.keymap.offset == 80
     assert C.sizeof(built.KeyMap) == 32 and built.KeyMap.n_keys.offset == 24

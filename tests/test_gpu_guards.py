@@ -1,0 +1,151 @@
+"""Guards against silent wrong answers, exercised on the GPU through the C ABI: LoD checks the
+kernels apply to device-resident offsets (framework CheckLoD, lod_tensor.cc:116-142), the
+id-count bound, bad-id attribution with several plans in flight, duplicate feasign keys, the
+fp64 cvm the reference registers (cvm_op.cu:192-194) and the many-plans launch call."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def env():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import __graft_entry__ as g
+    g.build()
+    from oracle import oracle as O
+    from paddle_infer_b200 import _lib as B
+    from paddle_infer_b200 import ops
+    return ops, O, B, torch.device("cuda:0")
+
+
+def _case(rng, n_seg, N, D, max_len=6):
+    table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+    table[:, 0] = rng.integers(0, 16, N)
+    table[:, 1] = np.minimum(table[:, 0], rng.integers(0, 16, N))
+    l = rng.integers(0, max_len + 1, n_seg)
+    lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+    ids = rng.integers(0, N, int(lod[-1])).astype(np.int64)
+    return table, ids, lod
+
+
+@pytest.mark.parametrize("D", [16, 11])  # the specialised kernel and the general one
+def test_device_lod_is_checked_by_the_kernel(env, D):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(7 + D)
+    table, ids, lod = _case(rng, 300, 1000, D)
+    tt, it = torch.from_numpy(table).to(dev), torch.from_numpy(ids).to(dev)
+    good = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [lod], "SUM", use_cvm=None)[0].cpu().numpy()
+    # (1) a decreasing pair in the middle: that sequence (and the one after it, whose start now
+    # exceeds its end... or not) is pooled as empty, everything else is untouched
+    bad = lod.astype(np.int64).copy()
+    k = 150
+    bad[k] = bad[k + 1] + 5  # sequence k-1 grows past k's end, sequence k: start > end
+    lod_dev = torch.from_numpy(bad).to(dev)
+    out = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [lod_dev], "SUM", use_cvm=None, pad_value=0.25, check=False)[0]
+    with pytest.raises(ops.InvalidArgument, match="LoD offsets of sequence 150"):
+        ops.default_context(dev).check_ids()
+    o = out.cpu().numpy()
+    np.testing.assert_array_equal(o[:k - 1], good[:k - 1])
+    np.testing.assert_array_equal(o[k + 1:], good[k + 1:])
+    assert (o[k] == 0.25).all()  # pooled as an empty sequence
+    ops.default_context(dev).check_ids()  # the record was cleared
+    # (2) the last offset beyond the id tensor: no read past the end, reported
+    over = lod.astype(np.int64).copy()
+    over[-1] += 1000
+    out = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [torch.from_numpy(over).to(dev)], "SUM", use_cvm=None, check=False)[0]
+    with pytest.raises(ops.InvalidArgument, match="sequence 299"):
+        ops.default_context(dev).check_ids()
+    np.testing.assert_array_equal(out.cpu().numpy()[:299], good[:299])
+    # (3) an offset with a non-zero high word
+    big = lod.astype(np.int64).copy()
+    big[10] += 1 << 32
+    ops.ctr_fused_emb_seqpool_cvm(tt, [it], [torch.from_numpy(big).to(dev)], "SUM", use_cvm=None, check=False)
+    with pytest.raises(ops.InvalidArgument):
+        ops.default_context(dev).check_ids()
+    # host LoD: the same faults are refused before anything is launched
+    for l in (bad, over, big):
+        with pytest.raises(B.CtrfeError):
+            ops.ctr_fused_emb_seqpool_cvm(tt, [it], [l.astype(np.uint64)], "SUM", use_cvm=None)
+
+
+def test_bad_id_is_attributed_to_the_plan_that_met_it(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(11)
+    N, D = 500, 16
+    table, ids_a, lod_a = _case(rng, 200, N, D)
+    _, ids_b, lod_b = _case(rng, 200, N, D)
+    ids_a = ids_a.copy()
+    pos = int(lod_a[100]) if lod_a[101] > lod_a[100] else int(lod_a[np.nonzero(np.diff(lod_a.astype(np.int64)))[0][0]])
+    ids_a[pos] = N + 77
+    tt = torch.from_numpy(table).to(dev)
+    pa = ops.ctr_fused_emb_seqpool_cvm(tt, [torch.from_numpy(ids_a).to(dev)], [lod_a], "SUM", plan_only=True)
+    pb = ops.ctr_fused_emb_seqpool_cvm(tt, [torch.from_numpy(ids_b).to(dev)], [lod_b], "SUM", plan_only=True)
+    pa.launch()
+    pb.launch()  # the LAST launched plan is the clean one
+    with pytest.raises(ValueError) as e:
+        pa.ctx.check_ids()
+    assert e.value.slot == 0 and e.value.position == pos and e.value.id_value == N + 77
+    pa.close(), pb.close()
+
+
+def test_duplicate_feasign_keys_resolve_to_the_first_occurrence(env):
+    ops, O, B, dev = env
+    n = 50_000
+    rng = np.random.default_rng(3)
+    keys = rng.integers(1, 1 << 62, n).astype(np.int64)
+    keys[n // 2:] = keys[: n - n // 2]  # every key twice
+    for _ in range(3):
+        km = ops.KeyMap(torch.from_numpy(keys).to(dev))
+        W = torch.arange(n, dtype=torch.float32, device=dev).view(n, 1).repeat(1, 4).contiguous()
+        out = ops.pull_box_sparse(km, W, [torch.from_numpy(keys).to(dev)])[0].cpu().numpy()
+        want = np.concatenate([np.arange(n // 2), np.arange(n - n // 2)]).astype(np.float32)
+        np.testing.assert_array_equal(out[:, 0], want)
+
+
+def test_cvm_fp64_matches_numpy(env):
+    """cvm on double rows: y0 = log(x0 + 1), y1 = log(x1 + 1) - y0 in fp64 (cvm_op.h:25-41 with
+    T = double; the numpy statement of test_cvm_op.py:31-36)."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(5)
+    x = rng.uniform(0, 1, (37, 11))
+    for use_cvm in (True, False):
+        y = ops.cvm(torch.from_numpy(x).to(dev), None, use_cvm).cpu().numpy()
+        if use_cvm:
+            want = x.copy()
+            want[:, 0] = np.log(x[:, 0] + 1)
+            want[:, 1] = np.log(x[:, 1] + 1) - want[:, 0]
+            np.testing.assert_allclose(y, want, rtol=1e-14, atol=1e-15)
+            np.testing.assert_array_equal(y[:, 2:], x[:, 2:])
+        else:
+            np.testing.assert_array_equal(y, x[:, 2:])
+
+
+def test_launch_many_equals_single_launches(env):
+    ops, O, B, dev = env
+    rng = np.random.default_rng(9)
+    table, _, _ = _case(rng, 1, 2000, 16)
+    tt = torch.from_numpy(table).to(dev)
+    plans, singles = [], []
+    for b in range(5):
+        _, ids, lod = _case(rng, 257 + b, 2000, 16)
+        it = torch.from_numpy(ids).to(dev)
+        plans.append(ops.ctr_fused_emb_seqpool_cvm(tt, [it, it], [lod, lod], ["SUM", "SQRT"], plan_only=True))
+        singles.append(ops.ctr_fused_emb_seqpool_cvm(tt, [it, it], [lod, lod], ["SUM", "SQRT"]))
+    for flags in (0, B.LAUNCH_OVERLAP_PREVIOUS):
+        for p in plans:
+            for o in p.outs:
+                o.fill_(float("nan"))
+        ops.launch_many(plans, overlap_previous=bool(flags))
+        torch.cuda.synchronize()
+        for p, want in zip(plans, singles):
+            for g, w in zip(p.outs, want):
+                assert torch.equal(g, w)
+    assert plans[0].kernel_names() and "fused_pool" in plans[0].kernel_names()[0]
+    for p in plans:
+        p.close()

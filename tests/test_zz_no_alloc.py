@@ -39,7 +39,7 @@ def _call_both(B, ops, dev, rng, S, Bsz, N, D, max_len, pooltype, use_cvm):
     slots = (B.Slot * S)()
     for s in range(S):
         slots[s] = B.Slot(tt.data_ptr(), N, ids_t[s].data_ptr(), lods[s].ctypes.data, Bsz,
-                          got.data_ptr() + s * d_out * 4, S * d_out, B.POOLTYPES[pooltype], B.I64)
+                          got.data_ptr() + s * d_out * 4, S * d_out, B.POOLTYPES[pooltype], B.I64, ids_t[s].numel())
     cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
     desc = B.FusedDesc(S, B.F32, slots, D, -1, 0.0, cvm_mode, 2, B.SCALE_DIVIDE, B.INIT_ZERO, B.LOD_HOST, 0)
     key = torch.zeros(1, dtype=torch.int64).pin_memory()
@@ -71,7 +71,7 @@ def test_static_entry_matches_the_ordinary_one_twice_in_a_row():
     lod = np.array([0, 3], np.uint64)
     out = torch.empty(1, 8, device=dev)
     slots = (B.Slot * 1)(B.Slot(table.data_ptr(), 10, ids.data_ptr(), lod.ctypes.data, 1, out.data_ptr(), 8,
-                                B.POOL_SUM, B.I64))
+                                B.POOL_SUM, B.I64, 3))
     desc = B.FusedDesc(1, B.F32, slots, 8, -1, 0.0, B.CVM_NONE, 2, B.SCALE_DIVIDE, B.INIT_ZERO, B.LOD_HOST, 0)
     key = torch.zeros(1, dtype=torch.int64).pin_memory()
     assert B.lib().ctrfe_fused_forward_static(C.byref(desc), torch.cuda.current_stream(dev).cuda_stream,
@@ -84,7 +84,7 @@ def test_static_entry_matches_the_ordinary_one_twice_in_a_row():
     big_lod = np.zeros(n_big + 1, np.uint64)
     big_out = torch.empty(n_big, 8, device=dev)
     slots = (B.Slot * 1)(B.Slot(table.data_ptr(), 10, ids.data_ptr(), big_lod.ctypes.data, n_big, big_out.data_ptr(), 8,
-                                B.POOL_SUM, B.I64))
+                                B.POOL_SUM, B.I64, 3))
     desc = B.FusedDesc(1, B.F32, slots, 8, -1, 0.0, B.CVM_NONE, 2, B.SCALE_DIVIDE, B.INIT_ZERO, B.LOD_HOST, 0)
     rc = B.lib().ctrfe_fused_forward_static(C.byref(desc), torch.cuda.current_stream(dev).cuda_stream, None)
     assert rc == B.ERR_ARG and b"static scratch" in B.lib().ctrfe_last_error()
