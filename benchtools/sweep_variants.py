@@ -20,18 +20,15 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 BASE = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
         "-ftz=true", "-fmad=false"]
 
+# name -> (extra nvcc flags, environment for the run)
 VARIANTS = {
-    "r1_notab": ["-DCTRFE_NO_CVM_TABLE"],
-    "base": [],
-    "t128": ["-DCTRFE_THREADS=128", "-DCTRFE_MINB32=16", "-DCTRFE_MINB16=16"],
-    "mt2": ["-DCTRFE_MT=2"],
-    "mt2_r40": ["-DCTRFE_MT=2", "-DCTRFE_MINB32=6", "-DCTRFE_MINB16=6"],
-    "mt3_r40": ["-DCTRFE_MT=3", "-DCTRFE_MINB32=6", "-DCTRFE_MINB16=6"],
-    "mt4": ["-DCTRFE_MT=4"],
-    "mt4_r40": ["-DCTRFE_MT=4", "-DCTRFE_MINB32=6", "-DCTRFE_MINB16=6"],
-    "mt2_t128": ["-DCTRFE_MT=2", "-DCTRFE_THREADS=128", "-DCTRFE_MINB32=16", "-DCTRFE_MINB16=16"],
-    "mt2_t128_r40": ["-DCTRFE_MT=2", "-DCTRFE_THREADS=128", "-DCTRFE_MINB32=12", "-DCTRFE_MINB16=12"],
-    "mt4_t128_r40": ["-DCTRFE_MT=4", "-DCTRFE_THREADS=128", "-DCTRFE_MINB32=12", "-DCTRFE_MINB16=12"],
+    "base": ([], {}),
+    "ldg128": ([], {"CTRFE_LDG256": "0"}),          # 128-bit lanes for every row width (the round-1 kernels)
+    "ldg256_all": ([], {"CTRFE_LDG256": "1"}),      # 256-bit lanes also for 32- / 64-byte rows
+    "w8_8": (["-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
+    "w6_6": (["-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
+    "w5_4": (["-DCTRFE_MINB_WIDE32=5", "-DCTRFE_MINB_WIDE16=4"], {}),
+    "w4_3": (["-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=3"], {}),
 }
 
 
@@ -39,7 +36,9 @@ def build(names):
     os.makedirs(OUT, exist_ok=True)
     procs = []
     for n in names:
-        cmd = [NVCC, *BASE, *VARIANTS[n], "-o", os.path.join(OUT, f"libctrfe_{n}.so"),
+        if not VARIANTS[n][0] and n != "base":
+            continue  # an environment-only variant runs the base build
+        cmd = [NVCC, *BASE, *VARIANTS[n][0], "-o", os.path.join(OUT, f"libctrfe_{n}.so"),
                os.path.join(ROOT, "paddle_infer_b200", "csrc", "ctrfe_api.cu")]
         procs.append((n, subprocess.Popen(cmd, cwd=ROOT)))
         if len(procs) >= 6:
@@ -54,10 +53,10 @@ def run(workloads, names, steps):
     rows = []
     for wl in workloads:
         for n in names:
-            lib = os.path.join(OUT, f"libctrfe_{n}.so")
+            lib = os.path.join(OUT, f"libctrfe_{n if VARIANTS[n][0] else 'base'}.so")
             if not os.path.exists(lib):
                 continue
-            env = dict(os.environ, CTRFE_LIB=lib)
+            env = dict(os.environ, CTRFE_LIB=lib, **VARIANTS[n][1])
             cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", wl, "--steps", str(steps), "--warmup", "20",
                    "--no-cpu-baseline", "--e2e-steps", "3"]
             p = subprocess.run(cmd, env=env, capture_output=True, text=True, cwd=ROOT)

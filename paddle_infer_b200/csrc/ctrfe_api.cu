@@ -233,30 +233,45 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     if (!sharded && reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
     lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
   }
-  // lane chunk: 32 bytes (one 256-bit load) for fp32 rows that allow it, else 16, else one element
-  int cb = 16;
-  // 256-bit lanes halve the instruction count but also the warps in flight; on B200 the
-  // 128-bit mapping measured faster for short sequences (profiles/), so 32-byte lanes are opt-in.
-  const char* use256 = getenv("CTRFE_LDG256");
-  if (v && !sharded && d->dtype == CTRFE_F32 && row_bytes % 32 == 0 && use256 && use256[0] == '1') {
-    cb = 32;
-    for (int s = 0; s < d->n_slots; ++s)
-      if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
-  }
-  plan->chunk_bytes = cb;
-  // the specialised kernel: exact 16*G-byte rows, zero-initialised accumulating pools, no
+  // the specialised kernel: rows of exactly 16 << k bytes, zero-initialised accumulating pools, no
   // padding_idx, aligned outputs (CTRFE_NO_FAST=1 forces the general kernel, for A/B runs)
+  bool has_select = false;
   {
     const char* nofast = getenv("CTRFE_NO_FAST");
-    bool f = v && cb == 16 && row_bytes <= 512 && (row_bytes & (row_bytes - 1)) == 0 && d->padding_idx == -1 &&
+    bool f = v && row_bytes <= 1024 && (row_bytes & (row_bytes - 1)) == 0 && d->padding_idx == -1 &&
              d->init_mode == CTRFE_INIT_ZERO && d->cvm_mode != CTRFE_CVM_STRIP && !km && !(nofast && nofast[0] == '1');
-    for (int s = 0; f && s < d->n_slots; ++s) {
+    for (int s = 0; s < d->n_slots; ++s) {
       const ctrfe_slot& sl = d->slots[s];
+      if (sl.pooltype >= CTRFE_POOL_LAST) has_select = true;
       if (!sl.ids || sl.ids_dtype != CTRFE_I64 || reinterpret_cast<uintptr_t>(sl.out) % 16 != 0 || (sl.out_ld * es) % 16 != 0) f = false;
     }
     plan->fast = f;
     plan->cvm_use = d->cvm_mode == CTRFE_CVM_USE;
   }
+  // Bytes of a row one lane holds: 16 (one 128-bit load), or 32 (one 256-bit load) for rows of 128
+  // bytes and wider -- random rows of that width sustain 5.3 - 6.5 TB/s through 256-bit loads against
+  // 3.8 TB/s through 128-bit ones on B200 (profiles/r2_gather_sweep.txt); 64-byte rows gain nothing and
+  // lose warps.  CTRFE_LDG256=0 keeps 128-bit lanes, =1 also gives wide lanes to 32- and 64-byte rows.
+  // In the sharded mode only the specialised kernel has the wide form.
+  int cb = 16;
+  {
+    const char* use256 = getenv("CTRFE_LDG256");
+    const long long min_row = (use256 && use256[0] == '1') ? 32 : 128;
+    if (v && row_bytes % 32 == 0 && row_bytes >= min_row && !(use256 && use256[0] == '0') &&
+        (!sharded || (plan->fast && !has_select))) {
+      cb = 32;
+      if (sharded) {
+        for (int g = 0; g < d->n_shards; ++g)
+          if (reinterpret_cast<uintptr_t>(d->shard_tables[g]) % 32 != 0) cb = 16;
+        if (d->hot_cache && d->hot_cache->rows && reinterpret_cast<uintptr_t>(d->hot_cache->rows) % 32 != 0) cb = 16;
+      } else {
+        for (int s = 0; s < d->n_slots; ++s)
+          if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
+      }
+    }
+    if (cb == 16 && row_bytes > 512) plan->fast = false;  // 128-bit lanes cover at most 512 bytes with one warp
+  }
+  plan->chunk_bytes = cb;
   const long long units = v ? row_bytes / cb : d->dim;  // lane-sized pieces per row
   int g_shift = 5;                                      // the scalar fallback always uses whole warps
   if (v) { g_shift = 0; while ((1 << g_shift) < units && g_shift < 5) ++g_shift; }
@@ -353,8 +368,9 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     char buf[160];
     const bool sh = plan->chunks[c].n_shards > 0;
     if (plan->fast && plan->modes[c] == ctrfe::kModeAdd)
-      snprintf(buf, sizeof(buf), "ctrfe::fused_pool_fast_kernel<%s, %d-byte rows, cvm=%d, sharded=%d, hot=%d>", dtn[plan->dtype],
-               16 << plan->g_shift, plan->cvm_use ? 1 : 0, sh ? 1 : 0, sh && plan->chunks[c].hot_rows ? 1 : 0);
+      snprintf(buf, sizeof(buf), "ctrfe::fused_pool_fast_kernel<%s, %d-byte rows, cvm=%d, sharded=%d, hot=%d, %d-byte lanes>",
+               dtn[plan->dtype], plan->chunk_bytes << plan->g_shift, plan->cvm_use ? 1 : 0, sh ? 1 : 0,
+               sh && plan->chunks[c].hot_rows ? 1 : 0, plan->chunk_bytes);
     else
       snprintf(buf, sizeof(buf), "ctrfe::fused_pool_kernel<%s, vect=%d, lanes=%d, %s, %d-byte lanes, sharded=%d>", dtn[plan->dtype],
                plan->vect ? 1 : 0, 1 << plan->g_shift, plan->modes[c] == ctrfe::kModeSelect ? "select" : "add",
@@ -448,41 +464,45 @@ void launch_fused_t(int mode, bool vect, int gs, int cb, dim3 grid, cudaStream_t
     else launch_fused_tm<DT, ctrfe::kModeAdd, 16, true>(vect, gs, grid, st, p, overlap);
     return;
   }
-  if constexpr (DT == CTRFE_F32) {
-    if (cb == 32) {  // 256-bit lanes exist for fp32 rows only
-      if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 32, false>(vect, gs, grid, st, p, overlap);
-      else launch_fused_tm<DT, ctrfe::kModeAdd, 32, false>(vect, gs, grid, st, p, overlap);
-      return;
-    }
+  if (cb == 32) {  // 256-bit lanes
+    if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 32, false>(vect, gs, grid, st, p, overlap);
+    else launch_fused_tm<DT, ctrfe::kModeAdd, 32, false>(vect, gs, grid, st, p, overlap);
+    return;
   }
   if (sel) launch_fused_tm<DT, ctrfe::kModeSelect, 16, false>(vect, gs, grid, st, p, overlap);
   else launch_fused_tm<DT, ctrfe::kModeAdd, 16, false>(vect, gs, grid, st, p, overlap);
 }
 
-template <int DT, bool CVM, bool SH, bool HOT>
+template <int DT, bool CVM, bool SH, bool HOT, int CB>
 void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   using namespace ctrfe;
   switch (gs) {
-    case 0: launch_k(fused_pool_fast_kernel<DT, 0, CVM, SH, HOT>, grid, st, p, overlap); break;
-    case 1: launch_k(fused_pool_fast_kernel<DT, 1, CVM, SH, HOT>, grid, st, p, overlap); break;
-    case 2: launch_k(fused_pool_fast_kernel<DT, 2, CVM, SH, HOT>, grid, st, p, overlap); break;
-    case 3: launch_k(fused_pool_fast_kernel<DT, 3, CVM, SH, HOT>, grid, st, p, overlap); break;
-    case 4: launch_k(fused_pool_fast_kernel<DT, 4, CVM, SH, HOT>, grid, st, p, overlap); break;
-    default: launch_k(fused_pool_fast_kernel<DT, 5, CVM, SH, HOT>, grid, st, p, overlap); break;
+    case 0: launch_k(fused_pool_fast_kernel<DT, 0, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+    case 1: launch_k(fused_pool_fast_kernel<DT, 1, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+    case 2: launch_k(fused_pool_fast_kernel<DT, 2, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+    case 3: launch_k(fused_pool_fast_kernel<DT, 3, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+    case 4: launch_k(fused_pool_fast_kernel<DT, 4, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+    default: launch_k(fused_pool_fast_kernel<DT, 5, CVM, SH, HOT, CB>, grid, st, p, overlap); break;
+  }
+}
+
+template <int DT, int CB>
+void launch_fast_c(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
+  const bool sh = p.n_shards > 0;
+  const bool hot = sh && p.hot_rows != nullptr;
+  if (hot) {
+    if (cvm) launch_fast_g<DT, true, true, true, CB>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, true, true, CB>(gs, grid, st, p, overlap);
+  } else if (cvm) {
+    if (sh) launch_fast_g<DT, true, true, false, CB>(gs, grid, st, p, overlap); else launch_fast_g<DT, true, false, false, CB>(gs, grid, st, p, overlap);
+  } else {
+    if (sh) launch_fast_g<DT, false, true, false, CB>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, false, false, CB>(gs, grid, st, p, overlap);
   }
 }
 
 template <int DT>
-void launch_fast_t(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
-  const bool sh = p.n_shards > 0;
-  const bool hot = sh && p.hot_rows != nullptr;
-  if (hot) {
-    if (cvm) launch_fast_g<DT, true, true, true>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, true, true>(gs, grid, st, p, overlap);
-  } else if (cvm) {
-    if (sh) launch_fast_g<DT, true, true, false>(gs, grid, st, p, overlap); else launch_fast_g<DT, true, false, false>(gs, grid, st, p, overlap);
-  } else {
-    if (sh) launch_fast_g<DT, false, true, false>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, false, false>(gs, grid, st, p, overlap);
-  }
+void launch_fast_t(int gs, int cb, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
+  if (cb == 32) launch_fast_c<DT, 32>(gs, cvm, grid, st, p, overlap);
+  else launch_fast_c<DT, 16>(gs, cvm, grid, st, p, overlap);
 }
 
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = false) {
@@ -493,9 +513,9 @@ int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = fa
     const bool overlap = overlap_first || c > 0;
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
-        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
-        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
-        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
+        case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.chunk_bytes, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
+        case CTRFE_F16: launch_fast_t<CTRFE_F16>(plan.g_shift, plan.chunk_bytes, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
+        default: launch_fast_t<CTRFE_BF16>(plan.g_shift, plan.chunk_bytes, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
       }
       continue;
     }

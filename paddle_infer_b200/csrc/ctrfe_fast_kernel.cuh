@@ -23,14 +23,14 @@ __device__ __forceinline__ void launch_dependents() { asm volatile("griddepcontr
 
 // Epilogue shared by the specialised kernels: pad / scale / CVM / one 128-bit store per lane
 // (same arithmetic as the general kernel).  Every lane of the warp must call it (shuffles).
-template <int DT, int GS, bool CVM>
-__device__ __forceinline__ void finish_segment(const KParams& kp, const SlotK* slp, float (&acc)[Lane<DT, true, 16>::VEC],
+template <int DT, int GS, bool CVM, int CB = 16>
+__device__ __forceinline__ void finish_segment(const KParams& kp, const SlotK* slp, float (&acc)[Lane<DT, true, CB>::VEC],
                                                int len, unsigned seg, unsigned gl, bool seg_ok) {
-  using L = Lane<DT, true, 16>;
+  using L = Lane<DT, true, CB>;
   constexpr int ES = L::ES, VEC = L::VEC, RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
-  const unsigned lane_off = gl * 16u;
+  const unsigned lane_off = gl * static_cast<unsigned>(CB);
   const int pooltype = slp->pooltype;
   if (len == 0) {
 #pragma unroll
@@ -77,14 +77,16 @@ __device__ __forceinline__ void finish_segment(const KParams& kp, const SlotK* s
     else packed[e >> 1] |= b << ((e & 1) * 16);
   }
   char* dst = slp->out + static_cast<unsigned long long>(seg) * slp->out_ld_bytes + lane_off;
-  *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+#pragma unroll
+  for (int q = 0; q < RW / 4; ++q)
+    reinterpret_cast<uint4*>(dst)[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
 }
 
 // Where rows come from and how an id becomes a row index: the slot's table, the shards of a
 // row-sharded table, or the hot-row replicas.
-template <int DT, int GS, bool SHARDED, bool HOT>
+template <int DT, int GS, bool SHARDED, bool HOT, int CB = 16>
 struct RowSource {
-  static constexpr unsigned kRowShift = GS + 4;  // row_bytes = 16 << GS
+  static constexpr unsigned kRowShift = GS + (CB == 32 ? 5 : 4);  // row_bytes = CB << GS
   const KParams& kp;
   const SlotK* slp;
   const unsigned long long* s_shards;  // shared-memory copy of kp.shard_tables (SHARDED)
@@ -93,9 +95,9 @@ struct RowSource {
   unsigned long long hot_base;
 
   __device__ __forceinline__ RowSource(const KParams& kp_, const SlotK* slp_, const unsigned long long* sh, unsigned gl)
-      : kp(kp_), slp(slp_), s_shards(sh), lane_off(gl * 16u),
-        lane_base(reinterpret_cast<unsigned long long>(slp_->table) + gl * 16u),
-        hot_base(HOT ? reinterpret_cast<unsigned long long>(kp_.hot_rows) + gl * 16u : 0ull) {
+      : kp(kp_), slp(slp_), s_shards(sh), lane_off(gl * static_cast<unsigned>(CB)),
+        lane_base(reinterpret_cast<unsigned long long>(slp_->table) + gl * static_cast<unsigned>(CB)),
+        hot_base(HOT ? reinterpret_cast<unsigned long long>(kp_.hot_rows) + gl * static_cast<unsigned>(CB) : 0ull) {
     // keep the lane's base address in registers: left alone, ptxas re-derives it from the
     // parameter block in front of every row load (9 instructions per row)
     asm volatile("" : "+l"(lane_base));
@@ -142,10 +144,10 @@ struct RowSource {
 };
 
 // Adds U loaded rows into the accumulator, in order.
-template <int DT, int U>
-__device__ __forceinline__ void add_rows(float (&acc)[Lane<DT, true, 16>::VEC],
-                                         const uint32_t (&raw)[U][Lane<DT, true, 16>::RW], const bool (&ok)[U]) {
-  using L = Lane<DT, true, 16>;
+template <int DT, int U, int CB = 16>
+__device__ __forceinline__ void add_rows(float (&acc)[Lane<DT, true, CB>::VEC],
+                                         const uint32_t (&raw)[U][Lane<DT, true, CB>::RW], const bool (&ok)[U]) {
+  using L = Lane<DT, true, CB>;
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     if (!ok[u]) continue;
@@ -165,14 +167,14 @@ __device__ __forceinline__ void add_rows(float (&acc)[Lane<DT, true, 16>::VEC],
 
 // The warp-level row loop: lanes of a group fetch G consecutive ids with one request and
 // broadcast them with shuffles; the whole warp walks to its longest sequence.
-template <int DT, int GS, bool SHARDED, bool HOT>
-__device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDED, HOT>& src, uint32_t start, int len,
-                                                  unsigned gl, float (&acc)[Lane<DT, true, 16>::VEC]) {
-  using L = Lane<DT, true, 16>;
+template <int DT, int GS, bool SHARDED, bool HOT, int CB = 16>
+__device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDED, HOT, CB>& src, uint32_t start, int len,
+                                                  unsigned gl, float (&acc)[Lane<DT, true, CB>::VEC]) {
+  using L = Lane<DT, true, CB>;
   constexpr int RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
-  constexpr int U = kUnroll;
+  constexpr int U = kUnroll * 16 / CB;  // the same bytes in flight per lane
   constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
   constexpr int R = G * NI;               // rows consumed per step of the sequence loop
   const int maxlen = __reduce_max_sync(kFull, len);
@@ -203,18 +205,36 @@ __device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDE
         ok[u] = rid != kSkip;
         if (ok[u]) L::load(src.row_ptr(rid), raw[u]);
       }
-      add_rows<DT, U>(acc, raw, ok);
+      add_rows<DT, U, CB>(acc, raw, ok);
     }
 #pragma unroll
     for (int i = 0; i < NI; ++i) cur[i] = nxt[i];
   }
 }
 
-template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false>
-__global__ void __launch_bounds__(kThreads, (DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16))
+// CB: bytes of a row one lane holds.  16: one LDG.E.128 per lane per row.  32: one 256-bit load
+// (LDG.E.ENL2.256).  benchtools/gather_sweep.cu measured what uniform-random rows sustain on B200
+// (profiles/r2_gather_sweep.txt): 128-byte rows 3.75 TB/s through 128-bit lanes against 5.26 TB/s
+// through 256-bit lanes, 256-byte rows 3.79 against 6.52 TB/s (the streaming-copy peak); 64-byte rows
+// 2.82 TB/s either way; one cp.async.bulk per row 2.26 / 4.40 / 5.64 TB/s.  Rows of 128 bytes and
+// wider therefore take CB = 32.
+#ifndef CTRFE_MINB_WIDE32
+#define CTRFE_MINB_WIDE32 6
+#endif
+#ifndef CTRFE_MINB_WIDE16
+#define CTRFE_MINB_WIDE16 5
+#endif
+template <int DT, int CB>
+constexpr int fast_min_blocks() {
+  if (CB == 16) return DT == CTRFE_F32 ? CTRFE_MINB32 : CTRFE_MINB16;
+  return DT == CTRFE_F32 ? CTRFE_MINB_WIDE32 : CTRFE_MINB_WIDE16;
+}
+
+template <int DT, int GS, bool CVM, bool SHARDED, bool HOT = false, int CB = 16>
+__global__ void __launch_bounds__(kThreads, (fast_min_blocks<DT, CB>()))
 fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   launch_dependents();
-  using L = Lane<DT, true, 16>;
+  using L = Lane<DT, true, CB>;
   constexpr int VEC = L::VEC;
   constexpr int G = 1 << GS;
 
@@ -235,12 +255,12 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   int len = 0;
   if (seg_ok) seg_bounds(kp, slp, seg, start, len);
 
-  const RowSource<DT, GS, SHARDED, HOT> src(kp, slp, s_shards, gl);
+  const RowSource<DT, GS, SHARDED, HOT, CB> src(kp, slp, s_shards, gl);
   float acc[VEC];
 #pragma unroll
   for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
-  pool_rows_by_warp<DT, GS, SHARDED, HOT>(src, start, len, gl, acc);
-  finish_segment<DT, GS, CVM>(kp, slp, acc, len, seg, gl, seg_ok);
+  pool_rows_by_warp<DT, GS, SHARDED, HOT, CB>(src, start, len, gl, acc);
+  finish_segment<DT, GS, CVM, CB>(kp, slp, acc, len, seg, gl, seg_ok);
 }
 
 // Fills a hot-row cache: one warp per hot id claims a hash slot (open addressing, linear

@@ -40,7 +40,7 @@ def test_device_lod_is_checked_by_the_kernel(env, D):
     rng = np.random.default_rng(7 + D)
     table, ids, lod = _case(rng, 300, 1000, D)
     tt, it = torch.from_numpy(table).to(dev), torch.from_numpy(ids).to(dev)
-    good = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [lod], "SUM", use_cvm=None)[0].cpu().numpy()
+    good = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [lod], "SUM", use_cvm=None, pad_value=0.25)[0].cpu().numpy()
     # (1) a decreasing pair in the middle: that sequence (and the one after it, whose start now
     # exceeds its end... or not) is pooled as empty, everything else is untouched
     bad = lod.astype(np.int64).copy()
@@ -58,7 +58,8 @@ def test_device_lod_is_checked_by_the_kernel(env, D):
     # (2) the last offset beyond the id tensor: no read past the end, reported
     over = lod.astype(np.int64).copy()
     over[-1] += 1000
-    out = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [torch.from_numpy(over).to(dev)], "SUM", use_cvm=None, check=False)[0]
+    out = ops.ctr_fused_emb_seqpool_cvm(tt, [it], [torch.from_numpy(over).to(dev)], "SUM", use_cvm=None, pad_value=0.25,
+                                        check=False)[0]
     with pytest.raises(ops.InvalidArgument, match="sequence 299"):
         ops.default_context(dev).check_ids()
     np.testing.assert_array_equal(out.cpu().numpy()[:299], good[:299])
