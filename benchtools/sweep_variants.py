@@ -58,7 +58,7 @@ def run(workloads, names, steps):
                 continue
             env = dict(os.environ, CTRFE_LIB=lib, **VARIANTS[n][1])
             cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", wl, "--steps", str(steps), "--warmup", "20",
-                   "--no-cpu-baseline", "--e2e-steps", "3"]
+                   "--quick", "--e2e-steps", "3", "--regions", "5"]
             p = subprocess.run(cmd, env=env, capture_output=True, text=True, cwd=ROOT)
             line = None
             for l in p.stdout.splitlines():

@@ -154,6 +154,30 @@ def fill_table(t, seed: int, row0: int = 0, cvm_cols: bool = True, row_stride: i
         raise RuntimeError(f"synth_fill_table failed: cudaError {rc}")
 
 
+_host_lib = None
+
+
+def fill_table_host(rows: int, dim: int, dtype: str, seed: int, cvm_cols: bool = True, threads: int = 0) -> np.ndarray:
+    """Logical rows 0..rows-1 generated on the host cores (benchtools/synth_host.c, OpenMP),
+    bit-identical to fill_table / table_rows_numpy.  bf16 comes back as uint16 bit patterns."""
+    global _host_lib
+    if _host_lib is None:
+        import subprocess
+        src, out = os.path.join(_HERE, "synth_host.c"), os.path.join(_HERE, "libsynth_host.so")
+        if not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src):
+            subprocess.check_call(["gcc", "-O3", "-fopenmp", "-fPIC", "-shared", "-ffp-contract=off", "-o", out, src, "-lm"])
+        _host_lib = C.CDLL(out)
+        _host_lib.synth_fill_table_host.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_ulonglong, C.c_longlong,
+                                                    C.c_longlong, C.c_int, C.c_int]
+    npdt = {"f32": np.float32, "f16": np.float16, "bf16": np.uint16}[dtype]
+    t = np.empty((rows, dim), dtype=npdt)
+    rc = _host_lib.synth_fill_table_host(t.ctypes.data, rows, dim, {"f32": 0, "f16": 1, "bf16": 2}[dtype], seed, 0, 1,
+                                         int(cvm_cols), threads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise RuntimeError("synth_fill_table_host failed")
+    return t
+
+
 # ------------------------------------------------------------------------------------------
 # lengths and ids
 # ------------------------------------------------------------------------------------------

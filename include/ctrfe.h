@@ -216,13 +216,25 @@ int ctrfe_plan_launch(ctrfe_plan* plan, void* stream);
  * draining (programmatic dependent launch), which hides the tail of a launch -- 15-20 % of a
  * cfg2 step.  Everything later in the stream still waits for both kernels.  Without the flag
  * the launch is an ordinary stream-ordered one.  No reference counterpart. */
-enum { CTRFE_LAUNCH_OVERLAP_PREVIOUS = 1 };
+enum {
+  CTRFE_LAUNCH_OVERLAP_PREVIOUS = 1,
+  CTRFE_LAUNCH_UPLOAD_LOD = 2  /* ctrfe_plan_launch_many only: before each launch, upload the plan's host LoD image
+                                  again (one async copy on the context's copy stream, so it runs beside the previous
+                                  batch's kernel) -- the serving-loop step in which the offsets change every batch
+                                  (ctrfe_plan_update_lod); plans created from device LoDs just launch */
+};
 int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags);
 /* n plans of one context launched back to back on `stream` in one call, with the same flags for
  * each (CTRFE_LAUNCH_OVERLAP_PREVIOUS: every launch may start while the one before it drains) --
  * the serving loop's inner step without a host-language call per batch.  No reference
  * counterpart (the reference launches per op, per slot). */
 int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32_t flags);
+/* New offsets for a plan created from host LoDs: lods[s] = the [n_seg + 1] offsets of slot s (same
+ * n_seg as at creation).  Validated like ctrfe_plan_create does (CheckLoD, lod_tensor.h:74-104) and
+ * written into the plan's pinned image; they reach the device with the next CTRFE_LAUNCH_UPLOAD_LOD
+ * launch.  Host-only, no CUDA call.  Stands where the reference re-copies the LoD per op
+ * (framework/mixed_vector.cc:57-76). */
+int ctrfe_plan_update_lod(ctrfe_plan* plan, const uint64_t* const* lods);
 int ctrfe_plan_destroy(ctrfe_plan* plan);
 /* Number of kernels one ctrfe_plan_launch enqueues (for launch accounting). */
 int ctrfe_plan_num_kernels(const ctrfe_plan* plan);

@@ -66,6 +66,7 @@ struct ctrfe_ctx {
   // that met it even with several plans in flight.
   std::vector<IdSource> tag_ids[256];
   unsigned next_tag = 1;
+  cudaStream_t copy_stream = nullptr;  // LoD re-uploads of CTRFE_LAUNCH_UPLOAD_LOD
   int sm_count = 148;
 };
 
@@ -87,6 +88,13 @@ struct ctrfe_plan {
   std::vector<char> all_max;  // per launch: every slot pools with MAX (selecting launches only)
   std::vector<IdSource> id_src;
   unsigned tag = 0;
+  // host-LoD plans: the pinned image the offsets were uploaded from (re-filled by ctrfe_plan_update_lod,
+  // re-uploaded by CTRFE_LAUNCH_UPLOAD_LOD) and what is needed to validate new offsets
+  char* host_img = nullptr;
+  size_t img_bytes = 0;
+  struct SlotShape { int64_t n_seg; int64_t bound; bool has_ids; };
+  std::vector<SlotShape> shapes;
+  cudaEvent_t lod_ready = nullptr, done = nullptr;
   std::vector<std::string> kernel_names;  // per launch, for ctrfe_plan_kernel_name
 };
 
@@ -231,7 +239,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       return fail(CTRFE_ERR_ARG, "slot %d: n_ids %lld outside [0, 2^31) (a slot holds fewer than 2^31 ids)", s, (long long)sl.n_ids);
     if (sl.out_ld * es >= (1LL << 32)) return fail(CTRFE_ERR_ARG, "slot %d: out_ld %lld too large", s, (long long)sl.out_ld);
     if (!sharded && reinterpret_cast<uintptr_t>(sl.table) % 16 != 0) v = false;
-    lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+    lb += align_up(static_cast<size_t>(sl.n_seg + 1) * 4, 16);  // the library's own image holds 32-bit offsets
   }
   // the specialised kernel: rows of exactly 16 << k bytes, zero-initialised accumulating pools, no
   // padding_idx, aligned outputs (CTRFE_NO_FAST=1 forces the general kernel, for A/B runs)
@@ -346,7 +354,8 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     o.n_seg = static_cast<unsigned>(sl.n_seg);
     // what every LoD offset is checked against: the id count, or -- dense rows -- the rows of X
     o.n_ids = static_cast<unsigned>(sl.ids ? sl.n_ids : (sl.table_rows > 0x7fffffffLL ? 0x7fffffffLL : sl.table_rows));
-    o.pooltype = static_cast<short>(sl.pooltype);
+    o.pooltype = static_cast<signed char>(sl.pooltype);
+    o.lod32 = d->lod_location == CTRFE_LOD_HOST ? 1 : 0;
     o.id_kind = static_cast<short>(km ? 3 : (sl.ids ? (sl.ids_dtype == CTRFE_I32 ? 1 : 0) : 2));
     o.slot_index = s;
     if (sl.n_seg > max_seg[c]) max_seg[c] = sl.n_seg;
@@ -358,6 +367,10 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     if (gx > 0x7fffffffLL) return fail(CTRFE_ERR_ARG, "fused: batch too large for one launch");
     plan->grids.push_back(dim3(static_cast<unsigned>(gx > 0 ? gx : 1), static_cast<unsigned>(plan->chunks[c].n_slots), 1));
   }
+  plan->shapes.resize(d->n_slots);
+  for (int s = 0; s < d->n_slots; ++s)
+    plan->shapes[s] = ctrfe_plan::SlotShape{d->slots[s].n_seg, d->slots[s].ids ? d->slots[s].n_ids : d->slots[s].table_rows,
+                                            d->slots[s].ids != nullptr};
   plan->id_src.resize(d->n_slots);
   for (int s = 0; s < d->n_slots; ++s)
     plan->id_src[s] = IdSource{d->slots[s].ids, d->slots[s].ids_dtype == CTRFE_I32};
@@ -381,41 +394,48 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
   return CTRFE_OK;
 }
 
-// Copies the host LoDs into one pinned image, validating them in the same pass:
-// non-decreasing offsets (framework CheckLoD, lod_tensor.h:74-104) and, for dense rows,
-// lod.back() <= rows (sequence_pool_op.h:52-60); re-points the descriptors at the device image.
+// One slot's host offsets -> 32-bit image, validated in the same pass: non-decreasing (framework
+// CheckLoD, lod_tensor.h:74-104), below 2^31, last offset inside the ids (or, dense rows, inside X:
+// sequence_pool_op.h:52-60).
+int stage_one_lod(int s, const uint64_t* lod, int64_t n_seg, int64_t bound, bool has_ids, uint32_t* dst) {
+  if (n_seg == 0) {
+    dst[0] = lod ? static_cast<uint32_t>(lod[0]) : 0u;
+    return CTRFE_OK;
+  }
+  uint64_t prev = lod[0];
+  dst[0] = static_cast<uint32_t>(prev);
+  bool mono = true;
+  for (int64_t i = 1; i <= n_seg; ++i) {
+    const uint64_t v = lod[i];
+    mono &= v >= prev;
+    dst[i] = static_cast<uint32_t>(v);
+    prev = v;
+  }
+  if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
+  if (prev >= (1ull << 31))
+    return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large (a slot holds fewer than 2^31 ids)", s,
+                (unsigned long long)prev);
+  if (has_ids && static_cast<int64_t>(prev) > bound)
+    return fail(CTRFE_ERR_ARG, "slot %d: the last LoD offset (%llu) exceeds the number of ids (%lld)", s,
+                (unsigned long long)prev, (long long)bound);
+  if (!has_ids && static_cast<int64_t>(prev) > bound)
+    return fail(CTRFE_ERR_ARG, "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)", s,
+                (long long)bound, (unsigned long long)prev);
+  return CTRFE_OK;
+}
+
+// Copies the host LoDs into one pinned image of 32-bit offsets, validating them in the same pass,
+// and re-points the descriptors at the device image.
 int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, ctrfe_plan* plan) {
   size_t off = 0;
   for (int s = 0; s < d->n_slots; ++s) {
     const ctrfe_slot& sl = d->slots[s];
     ctrfe::SlotK& o = plan->chunks[plan->where[s].first].slots[plan->where[s].second];
-    auto* dst = reinterpret_cast<uint64_t*>(host_img + off);
     o.lod = reinterpret_cast<const unsigned long long*>(dev_img + off);
-    if (sl.n_seg == 0) {
-      dst[0] = sl.lod ? sl.lod[0] : 0;
-    } else {
-      uint64_t prev = sl.lod[0];
-      dst[0] = prev;
-      bool mono = true;
-      for (int64_t i = 1; i <= sl.n_seg; ++i) {
-        const uint64_t v = sl.lod[i];
-        mono &= v >= prev;
-        dst[i] = v;
-        prev = v;
-      }
-      if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
-      if (prev >= (1ull << 31))
-        return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large (a slot holds fewer than 2^31 ids)", s,
-                    (unsigned long long)prev);
-      if (sl.ids && static_cast<int64_t>(prev) > sl.n_ids)
-        return fail(CTRFE_ERR_ARG, "slot %d: the last LoD offset (%llu) exceeds the number of ids (%lld)", s,
-                    (unsigned long long)prev, (long long)sl.n_ids);
-      if (!sl.ids && static_cast<int64_t>(prev) > sl.table_rows)
-        return fail(CTRFE_ERR_ARG,
-                    "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)",
-                    s, (long long)sl.table_rows, (unsigned long long)prev);
-    }
-    off += align_up(static_cast<size_t>(sl.n_seg + 1) * 8, 16);
+    const int rc = stage_one_lod(s, sl.lod, sl.n_seg, sl.ids ? sl.n_ids : sl.table_rows, sl.ids != nullptr,
+                                 reinterpret_cast<uint32_t*>(host_img + off));
+    if (rc) return rc;
+    off += align_up(static_cast<size_t>(sl.n_seg + 1) * 4, 16);
   }
   return CTRFE_OK;
 }
@@ -592,6 +612,7 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
     if (s.host) cudaFreeHost(s.host);
   }
   if (c->scratch) cudaFree(c->scratch);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
   delete c;
@@ -657,13 +678,19 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
   if (bytes) {
     char* dev = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
+    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&plan->host_img), bytes, cudaHostAllocDefault);
     if (e != cudaSuccess) {
+      if (dev) cudaFree(dev);
       delete plan;
-      return fail(CTRFE_ERR_CUDA, "plan_create: cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+      return fail(CTRFE_ERR_CUDA, "plan_create: allocating %zu bytes for the LoD image: %s", bytes, cudaGetErrorString(e));
     }
     plan->owns_dev = true;
-    rc = plan_upload(ctx, desc, static_cast<cudaStream_t>(stream), dev, bytes, plan);
-    if (rc) { cudaFree(dev); delete plan; return rc; }
+    plan->dev = dev;
+    plan->img_bytes = bytes;
+    rc = plan_stage_lods(desc, plan->host_img, dev, plan);
+    if (rc == CTRFE_OK && cudaMemcpyAsync(dev, plan->host_img, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)) != cudaSuccess)
+      rc = fail(CTRFE_ERR_CUDA, "plan_create: LoD upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc) { cudaFree(dev); cudaFreeHost(plan->host_img); delete plan; return rc; }
   }
   *out = plan;
   return CTRFE_OK;
@@ -682,18 +709,51 @@ int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags) {
   return launch_plan(*plan, static_cast<cudaStream_t>(stream), (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0);
 }
 
+int ctrfe_plan_update_lod(ctrfe_plan* plan, const uint64_t* const* lods) {
+  if (!plan || !lods) return fail(CTRFE_ERR_ARG, "plan_update_lod: null argument");
+  if (!plan->host_img) return fail(CTRFE_ERR_ARG, "plan_update_lod: the plan was not created from host LoD offsets");
+  size_t off = 0;
+  for (size_t s = 0; s < plan->shapes.size(); ++s) {
+    const auto& sh = plan->shapes[s];
+    if (sh.n_seg > 0 && !lods[s]) return fail(CTRFE_ERR_ARG, "plan_update_lod: slot %zu: null LoD", s);
+    const int rc = stage_one_lod(static_cast<int>(s), lods[s], sh.n_seg, sh.bound, sh.has_ids,
+                                 reinterpret_cast<uint32_t*>(plan->host_img + off));
+    if (rc) return rc;
+    off += align_up(static_cast<size_t>(sh.n_seg + 1) * 4, 16);
+  }
+  return CTRFE_OK;
+}
+
 int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32_t flags) {
   if (!plans || n < 0) return fail(CTRFE_ERR_ARG, "plan_launch_many: bad argument");
-  if (flags & ~static_cast<uint32_t>(CTRFE_LAUNCH_OVERLAP_PREVIOUS)) return fail(CTRFE_ERR_ARG, "plan_launch_many: unknown flag");
+  if (flags & ~static_cast<uint32_t>(CTRFE_LAUNCH_OVERLAP_PREVIOUS | CTRFE_LAUNCH_UPLOAD_LOD))
+    return fail(CTRFE_ERR_ARG, "plan_launch_many: unknown flag");
   if (n == 0) return CTRFE_OK;
   for (int i = 0; i < n; ++i)
     if (!plans[i] || plans[i]->ctx != plans[0]->ctx) return fail(CTRFE_ERR_ARG, "plan_launch_many: plan %d is null or of another context", i);
-  DeviceGuard g(plans[0]->ctx->device);
+  ctrfe_ctx* ctx = plans[0]->ctx;
+  DeviceGuard g(ctx->device);
   const bool overlap = (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0;
+  const bool upload = (flags & CTRFE_LAUNCH_UPLOAD_LOD) != 0;
   auto st = static_cast<cudaStream_t>(stream);
+  if (upload && !ctx->copy_stream) CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
   for (int i = 0; i < n; ++i) {
-    const int rc = launch_plan(*plans[i], st, overlap);
+    ctrfe_plan* p = plans[i];
+    if (upload && p->host_img) {
+      // the offsets travel on the context's copy stream, so the upload of batch i + 1 runs beside the
+      // kernel of batch i; the image is not overwritten before the plan's previous launch is through
+      if (!p->lod_ready) CU(cudaEventCreateWithFlags(&p->lod_ready, cudaEventDisableTiming));
+      if (p->done) CU(cudaStreamWaitEvent(ctx->copy_stream, p->done, 0));
+      CU(cudaMemcpyAsync(p->dev, p->host_img, p->img_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+      CU(cudaEventRecord(p->lod_ready, ctx->copy_stream));
+      CU(cudaStreamWaitEvent(st, p->lod_ready, 0));
+    }
+    const int rc = launch_plan(*p, st, overlap);
     if (rc) return rc;
+    if (upload && p->host_img) {
+      if (!p->done) CU(cudaEventCreateWithFlags(&p->done, cudaEventDisableTiming));
+      CU(cudaEventRecord(p->done, st));
+    }
   }
   return CTRFE_OK;
 }
@@ -705,6 +765,9 @@ int ctrfe_plan_destroy(ctrfe_plan* plan) {
     cudaDeviceSynchronize();
     cudaFree(plan->dev);
   }
+  if (plan->host_img) cudaFreeHost(plan->host_img);
+  if (plan->lod_ready) cudaEventDestroy(plan->lod_ready);
+  if (plan->done) cudaEventDestroy(plan->done);
   delete plan;
   return CTRFE_OK;
 }
@@ -807,7 +870,7 @@ int ctrfe_sequence_pool(ctrfe_ctx* ctx, const void* x, int32_t dtype, int64_t wi
     DeviceGuard g(ctx->device);
     auto st = static_cast<cudaStream_t>(stream);
     // the single slot's LoD image sits at the start of the context scratch
-    const auto* lod_dev = reinterpret_cast<const unsigned long long*>(ctx->scratch);
+    const auto* lod_dev = reinterpret_cast<const unsigned*>(ctx->scratch);  // the upload holds 32-bit offsets
     const long long total = n_seg * width;
     const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
     const char* xc = static_cast<const char*>(x);

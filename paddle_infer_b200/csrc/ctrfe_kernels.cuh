@@ -62,7 +62,8 @@ struct SlotK {
   unsigned int table_rows;         // < 2^32 - 2
   unsigned int n_seg;
   unsigned int n_ids;              // entries in ids (dense rows: table_rows); every LoD offset must be <= it (< 2^31)
-  short pooltype;
+  signed char pooltype;
+  unsigned char lod32;             // the LoD image holds 32-bit offsets (the library's own upload of a host LoD)
   short id_kind;                   // 0 int64, 1 int32, 2 dense (row index = position), 3 uint64 feasign keys (key map)
   int slot_index;                  // position in the caller's slot array (bad-id report)
 };
@@ -119,8 +120,15 @@ __device__ __forceinline__ unsigned long long err_key(const KParams& kp, const S
 // so one 64-bit compare also rejects offsets with a non-zero high word).  An offending sequence
 // is pooled as empty and recorded in err[1]; the kernel never reads past the ids it was given.
 __device__ __forceinline__ void seg_bounds(const KParams& kp, const SlotK* slp, unsigned seg, uint32_t& start, int& len) {
-  const unsigned long long a = __ldg(slp->lod + seg);
-  const unsigned long long b = __ldg(slp->lod + seg + 1);
+  unsigned long long a, b;
+  if (slp->lod32) {  // offsets the library uploaded itself: validated on the host, 4 bytes each
+    const unsigned* w = reinterpret_cast<const unsigned*>(slp->lod);
+    a = __ldg(w + seg);
+    b = __ldg(w + seg + 1);
+  } else {
+    a = __ldg(slp->lod + seg);
+    b = __ldg(slp->lod + seg + 1);
+  }
   const bool ok = a <= b && b <= static_cast<unsigned long long>(slp->n_ids);
   start = static_cast<uint32_t>(a);
   len = ok ? static_cast<int>(static_cast<uint32_t>(b) - static_cast<uint32_t>(a)) : 0;
@@ -616,7 +624,7 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
 // kept for interface completeness: one thread per output element.
 // ---------------------------------------------------------------------------------------
 template <int DT>
-__global__ void max_index_kernel(const char* __restrict__ x, const unsigned long long* __restrict__ lod,
+__global__ void max_index_kernel(const char* __restrict__ x, const unsigned* __restrict__ lod,
                                  long long n_seg, int width, int* __restrict__ index) {
   constexpr int ES = (DT == CTRFE_F32) ? 4 : 2;
   const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
