@@ -25,10 +25,13 @@ VARIANTS = {
     "base": ([], {}),
     "ldg128": ([], {"CTRFE_LDG256": "0"}),          # 128-bit lanes for every row width (the round-1 kernels)
     "ldg256_all": ([], {"CTRFE_LDG256": "1"}),      # 256-bit lanes also for 32- / 64-byte rows
-    "w8_8": (["-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
-    "w6_6": (["-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
-    "w5_4": (["-DCTRFE_MINB_WIDE32=5", "-DCTRFE_MINB_WIDE16=4"], {}),
-    "w4_3": (["-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=3"], {}),
+    "u2_w8_8": (["-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
+    "u2_w6_6": (["-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
+    "u2_w4_4": (["-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=4"], {}),
+    "u4_w6_6": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
+    "u4_w5_4": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=5", "-DCTRFE_MINB_WIDE16=4"], {}),
+    "u4_w4_3": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=3"], {}),
+    "u4_w8_8": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
 }
 
 

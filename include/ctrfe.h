@@ -268,6 +268,29 @@ const char* ctrfe_plan_kernel_name(const ctrfe_plan* plan, int i);
  *     offender (the row was treated as zeros, as ctrfe_check_ids documents). */
 int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint64_t* bad_id_key_host);
 
+/* ---- host buffers in, host buffers out ------------------------------------------------
+ * The fused front end for a predictor fed from CPU memory: per slot the ids and LoD offsets in
+ * host memory, the pooled rows back in host memory.  Replaces, around the fused launch, the
+ * reference's feed / fetch path: ZeroCopyTensor::CopyFromCpu + SetLoD per slot and CopyToCpu on
+ * the result (inference/api/details/zero_copy_tensor.cc).  Such a step is PCIe-bound, so the
+ * slots are cut into n_groups groups and pipelined over both copy engines: group g goes up while
+ * group g-1 is pooled and group g-2's rows come down.  The pipe owns its device staging
+ * (ids [n_slots, max_ids_per_slot], outputs, LoD images); a run allocates nothing.
+ *   create: desc gives the slots' tables, n_seg, pooltypes, id width (one for all slots) and the
+ *           attributes; its ids / lod / out pointers are ignored.
+ *   run:    ids_host[s] (n_ids[s] entries) and lods_host[s] ([n_seg + 1] offsets, validated as
+ *           ctrfe_plan_create does) are read, out_host[s] receives slot s's [n_seg, D_out] rows
+ *           with row stride out_ld elements.  Pinned host memory keeps the copies asynchronous;
+ *           the ids and the output must stay untouched until the run is through.  wait != 0:
+ *           returns once the rows are on the host; wait == 0: `stream` is made to wait for them.
+ *           Pooling kernels run on `stream`.  One run at a time per pipe. */
+typedef struct ctrfe_host_pipe ctrfe_host_pipe;
+int ctrfe_host_pipe_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, int64_t max_ids_per_slot, int n_groups,
+                           ctrfe_host_pipe** out);
+int ctrfe_host_pipe_run(ctrfe_host_pipe* pipe, const void* const* ids_host, const int64_t* n_ids,
+                        const uint64_t* const* lods_host, void* const* out_host, int64_t out_ld, void* stream, int wait);
+int ctrfe_host_pipe_destroy(ctrfe_host_pipe* pipe);
+
 /* ---- row-sharded tables across the GPUs of one box ------------------------------------
  * One process per GPU.  Each process allocates its shard with ctrfe_shard_alloc (plain
  * cudaMalloc memory, so that it can be exported), exports a 64-byte handle, exchanges the

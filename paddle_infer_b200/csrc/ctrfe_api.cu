@@ -1387,3 +1387,5 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* d, void* stream, uint64_t
 }
 
 }  // extern "C"
+
+#include "ctrfe_host_pipe.inc"

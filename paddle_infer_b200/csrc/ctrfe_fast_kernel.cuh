@@ -16,6 +16,10 @@
 
 namespace ctrfe {
 
+#ifndef CTRFE_WIDE_U
+#define CTRFE_WIDE_U 2   // rows in flight per lane with 256-bit lanes (2 = the same bytes as four 128-bit loads)
+#endif
+
 // Programmatic dependent launch: lets a kernel that was launched with the overlap flag
 // (ctrfe_plan_launch_ex, CTRFE_LAUNCH_OVERLAP_PREVIOUS) start filling SMs as soon as every CTA
 // of this grid has been scheduled, i.e. during this grid's tail.  A no-op otherwise.
@@ -174,7 +178,7 @@ __device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDE
   constexpr int RW = L::RW;
   constexpr unsigned kFull = 0xffffffffu;
   constexpr int G = 1 << GS;
-  constexpr int U = kUnroll * 16 / CB;  // the same bytes in flight per lane
+  constexpr int U = CB == 32 ? CTRFE_WIDE_U : kUnroll;  // row loads in flight per lane
   constexpr int NI = G >= U ? 1 : U / G;  // ids held per lane
   constexpr int R = G * NI;               // rows consumed per step of the sequence loop
   const int maxlen = __reduce_max_sync(kFull, len);
