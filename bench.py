@@ -509,9 +509,15 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
     stream = torch.cuda.current_stream(dev)
     Ke = max(3, min(args.steps, args.e2e_steps))
     max_ids = max(int(i.size) for hb in host_batches for i in hb.ids)
-    fe = ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, mode=args.e2e_mode)
+    fe = None if args.e2e_mode == "pipe" else ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx,
+                                                               mode=args.e2e_mode)
     pinned = [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
-    if args.e2e_mode == "zero_copy":
+    if args.e2e_mode == "pipe":
+        fe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups)
+        e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
+        step_fns = [(lambda b=b: fe.run(pinned[b], e2e_lods[b])) for b in range(n_batches)]
+        h2d_of = None
+    elif args.e2e_mode == "zero_copy":
         e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
         calls = [fe.bind(pinned[b], e2e_lods[b]) for b in range(n_batches)]
         step_fns = [c.run for c in calls]
@@ -531,7 +537,7 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
     h2d = d2h = 0
     for i in range(Ke):
         step_fns[i % n_batches]()
-        h2d += h2d_of[i % n_batches]
+        h2d += h2d_of[i % n_batches] if h2d_of is not None else fe.h2d_bytes
         d2h += fe.d2h_bytes
     e1.record(stream)
     torch.cuda.synchronize()
@@ -541,13 +547,17 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     # the last step's result against the oracle: the host-buffer path is checked too
-    res = fe._result()
+    res = [fe.host_out[s] for s in range(S)] if args.e2e_mode == "pipe" else fe._result()
     got = np.stack([(r.view(torch.int16).numpy().view(np.uint16) if r.dtype == torch.bfloat16 else r.numpy()) for r in res], axis=1)
     par = parity_check(cfg, host_batches[(Ke - 1) % n_batches], got, 1 if cfg.shared_table else S, sample=16)
     rec = {"value": S * Bsz * Ke * world / (float(te.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d // Ke,
            "d2h_bytes_per_step": d2h // Ke, "steps": Ke, "ms_per_step": float(te.item()) / Ke, "parity": par,
            "pcie_gbs_per_gpu": (h2d + d2h) / Ke / (float(te.item()) / Ke * 1e-3) / 1e9,
-           "path": ("HostFrontEnd zero_copy (buffers bound once): the kernel reads pinned host ids/LoD and writes the pinned "
+           "path": (f"HostPipe (ctrfe_host_pipe_run, {args.e2e_groups} slot groups): per group the LoD image and ids go up on one "
+                    "copy engine (cudaMemcpyAsync from pinned memory), the group is pooled, its rows come down on the other copy "
+                    "engine; the call returns when the last rows are in pinned host memory; LoD validated on the host per call"
+                    if args.e2e_mode == "pipe" else
+                    "HostFrontEnd zero_copy (buffers bound once): the kernel reads pinned host ids/LoD and writes the pinned "
                     "per-slot host outputs over PCIe inside the one launch, then the stream is synchronised"
                     if args.e2e_mode == "zero_copy" else "HostFrontEnd copy: H2D ids + LoD upload, launch, D2H output")}
     if args.e2e_mode == "zero_copy" and not args.quick:
@@ -761,7 +771,8 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
     ap.add_argument("--regions", type=int, default=15, help="timed regions of --steps launches; the median region is reported")
     ap.add_argument("--e2e-steps", type=int, default=40)
-    ap.add_argument("--e2e-mode", default="zero_copy", choices=["zero_copy", "copy"])
+    ap.add_argument("--e2e-mode", default="pipe", choices=["pipe", "zero_copy", "copy"])
+    ap.add_argument("--e2e-groups", type=int, default=4, help="slot groups of the host-buffer pipe")
     ap.add_argument("--no-overlap", action="store_true",
                     help="timed loop without CTRFE_LAUNCH_OVERLAP_PREVIOUS (each launch waits for the one before)")
     ap.add_argument("--cpu-budget", type=float, default=12.0)

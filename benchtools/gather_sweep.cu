@@ -355,6 +355,12 @@ int main(int argc, char** argv) {
   cudaMemset(buf, 1, g_bytes);
   g_buf = buf;
   cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, 0);
+  if (argc > 2 && argv[2][0] == 'w') {  // table-size check: the LDG ceilings only (does a > 100 GB table change them?)
+    printf("ldg / ldg256 pass, table %.1f GB\n", g_bytes / 1e9);
+    run_ldg<4, 4>(8); run_ldg<8, 4>(8); run_ldg<16, 4>(8);
+    run_ldg256<2, 2>(); run_ldg256<4, 2>(); run_ldg256<4, 4>(); run_ldg256<8, 2>(); run_ldg256<8, 4>();
+    return 0;
+  }
   if (argc > 2 && argv[2][0] == 'h') {  // second pass: hybrid LDG + bulk, and 256-bit loads
     printf("hybrid / ldg256 pass, table %.1f GB\n", g_bytes / 1e9);
     run_ldg256<2, 2>(); run_ldg256<2, 4>(); run_ldg256<4, 2>(); run_ldg256<4, 4>(); run_ldg256<8, 2>(); run_ldg256<8, 4>();

@@ -758,3 +758,96 @@ class BoundHostCall:
     def result(self, done):
         done.synchronize()
         return self.fe._result()
+
+
+class HostPipe:
+    """The fused front end with HOST inputs and outputs through the library's pipelined host-buffer
+    call (ctrfe_host_pipe_*): per slot the ids and LoD offsets in (pinned) host memory in, the
+    pooled rows in pinned host memory out.  The shape of the reference's feed / fetch path --
+    ZeroCopyTensor::CopyFromCpu + SetLoD per slot, CopyToCpu on the result
+    (inference/api/details/zero_copy_tensor.cc) -- around the fused launch.  The slots are cut into
+    `n_groups` groups and pipelined over both copy engines (group g goes up while group g-1 is
+    pooled and group g-2's rows come down), so both directions of PCIe are busy at once; the LoD
+    offsets are validated on the host like any host LoD.  run() returns one [B, D_out] pinned host
+    view per slot (the op's Out@VECTOR)."""
+
+    def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
+                 padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, n_groups: int = 4,
+                 ids_dtype=torch.int64, ctx: Optional[Context] = None):
+        from .shard import LocalShards, ShardedTable
+        sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
+        if sharded is not None:
+            t0 = torch.empty((0, W.dim), dtype=W.dtype, device=W.device)
+            tables = [_TableRef(None, W.n_rows)] * n_slots
+        else:
+            tables = _as_list(W, n_slots)
+            t0 = tables[0]
+            _need_cuda(t0, "W")
+        self.S, self.B, self.dim = n_slots, batch, t0.shape[1]
+        self.ctx = ctx or default_context(t0.device)
+        self._dev = t0.device
+        pools = _as_list(pooltype, n_slots)
+        cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
+        self.d_out = self.dim - (cvm_offset if use_cvm is False else 0)
+        slots = (B.Slot * n_slots)()
+        for s in range(n_slots):
+            slots[s] = B.Slot(tables[s].data_ptr(), tables[s].shape[0], None, None, batch, None, self.d_out,
+                              B.POOLTYPES[pools[s]], _IDT[ids_dtype], 0)
+        desc = B.FusedDesc(n_slots, _DT[t0.dtype], slots, self.dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset,
+                           B.SCALE_DIVIDE, B.INIT_ZERO, B.LOD_HOST, 0)
+        if sharded is not None:
+            desc.n_shards = sharded.n_shards
+            desc.shard_tables = C.cast(sharded.shard_ptrs, C.POINTER(C.c_void_p))
+            if getattr(sharded, "hot", None) is not None:
+                desc.hot_cache = C.pointer(sharded.hot.struct)
+        self._keep = (tables, sharded)
+        h = C.c_void_p()
+        B.check(B.lib().ctrfe_host_pipe_create(self.ctx.handle, C.byref(desc), int(max_ids_per_slot), int(n_groups), C.byref(h)))
+        self.handle = h
+        self.host_out = torch.empty((n_slots, batch, self.d_out), dtype=t0.dtype, pin_memory=True)
+        self._out_ptrs = (C.c_void_p * n_slots)(*[self.host_out[s].data_ptr() for s in range(n_slots)])
+        self._ids_ptrs = (C.c_void_p * n_slots)()
+        self._lod_ptrs = (C.c_void_p * n_slots)()
+        self._n_ids = (C.c_int64 * n_slots)()
+        self._id_es = 8 if ids_dtype == torch.int64 else 4
+        self.d2h_bytes = self.host_out.numel() * self.host_out.element_size()
+        self.h2d_bytes = 0
+
+    def run(self, ids_host: Sequence, lods_host: Sequence, wait: bool = True):
+        """ids_host[s]: int64 (or int32) CPU tensor / numpy array, pinned for asynchronous copies;
+        lods_host[s]: the [B + 1] offsets as a numpy uint64 array or an int64 CPU tensor."""
+        keep = []
+        h2d = 0
+        for s in range(self.S):
+            i, l = ids_host[s], lods_host[s]
+            if isinstance(i, torch.Tensor):
+                self._ids_ptrs[s], self._n_ids[s] = i.data_ptr(), i.numel()
+            else:
+                self._ids_ptrs[s], self._n_ids[s] = i.ctypes.data, i.size
+            if isinstance(l, torch.Tensor):
+                self._lod_ptrs[s] = l.data_ptr()
+                n = l.numel()
+            else:
+                a = _lod_np(l)
+                keep.append(a)
+                self._lod_ptrs[s] = a.ctypes.data
+                n = a.size
+            if n != self.B + 1:
+                raise InvalidArgument("Batchsize of all inputs should be equal.")
+            h2d += self._n_ids[s] * self._id_es + n * 4
+        self.h2d_bytes = h2d
+        stream = torch.cuda.current_stream(self._dev)
+        B.check(B.lib().ctrfe_host_pipe_run(self.handle, self._ids_ptrs, self._n_ids, self._lod_ptrs, self._out_ptrs, self.d_out,
+                                            stream.cuda_stream, 1 if wait else 0))
+        return [self.host_out[s] for s in range(self.S)]
+
+    def close(self):
+        if getattr(self, "handle", None):
+            B.lib().ctrfe_host_pipe_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

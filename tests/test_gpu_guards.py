@@ -150,3 +150,46 @@ def test_launch_many_equals_single_launches(env):
     assert plans[0].kernel_names() and "fused_pool" in plans[0].kernel_names()[0]
     for p in plans:
         p.close()
+
+
+@pytest.mark.parametrize("n_groups", [1, 3, 5])
+def test_host_pipe_equals_the_device_call(env, n_groups):
+    """ctrfe_host_pipe_*: host ids / LoD in, host rows out, slots pipelined in groups -- the same
+    bits as the device-resident call, on several runs in a row with different batches (the
+    pipe's buffers are reused), for fp32 SUM + CVM and for bf16 mixed pools."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(40 + n_groups)
+    for dtype, D, pools, use_cvm in (("f32", 16, "SUM", True), ("bf16", 64, ["SUM", "AVERAGE", "SQRT", "SUM", "SQRT"], None)):
+        S, Bsz, N = 5, 300, 4000
+        table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+        table[:, 0] = rng.integers(0, 16, N)
+        table[:, 1] = np.minimum(table[:, 0], rng.integers(0, 16, N))
+        tt = torch.from_numpy(table).to(dev)
+        if dtype == "bf16":
+            tt = tt.to(torch.bfloat16)
+        pipe = ops.HostPipe(tt, S, Bsz, 4000, pools, use_cvm=use_cvm, n_groups=n_groups)
+        for _ in range(3):
+            lods, ids = [], []
+            for _s in range(S):
+                l = rng.integers(0, 9, Bsz)
+                lod = np.concatenate([[0], np.cumsum(l)]).astype(np.uint64)
+                lods.append(lod)
+                ids.append(torch.from_numpy(rng.integers(0, N, int(lod[-1])).astype(np.int64)).pin_memory())
+            got = pipe.run(ids, lods)
+            want = ops.ctr_fused_emb_seqpool_cvm(tt, [i.to(dev) for i in ids], lods, pools, use_cvm=use_cvm)
+            for s in range(S):
+                assert torch.equal(got[s], want[s].cpu()), (dtype, s)
+        # a LoD that names more ids than were passed is refused on the host
+        bad = [l.copy() for l in lods]
+        bad[2][-1] += 5
+        with pytest.raises(B.CtrfeError, match="exceeds the number of ids"):
+            pipe.run(ids, bad)
+        # an out-of-range id is reported by check_ids with the slot it came from
+        ids[3] = ids[3].clone()
+        if ids[3].numel():
+            ids[3][0] = N + 3
+            pipe.run(ids, lods)
+            with pytest.raises(ValueError) as e:
+                pipe.ctx.check_ids()
+            assert e.value.id_value == N + 3
+        pipe.close()
