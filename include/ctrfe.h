@@ -327,6 +327,17 @@ int ctrfe_hot_cache_build(ctrfe_ctx* ctx, const int64_t* hot_ids, int64_t n, con
 int ctrfe_keymap_build(ctrfe_ctx* ctx, const uint64_t* keys, int64_t n, uint64_t* map_keys, uint32_t* map_rows,
                        int32_t log2_slots, uint32_t* n_unplaced, void* stream);
 
+/* fused_embedding_seq_pool: gather + SUM per sequence in the EmbSeqPool order (first row copied, the
+ * rest added in id order).  ids: device int64 [n_rows, index_width] row-major with ONE LoD level over
+ * its rows (lod_host: [n_seg + 1] offsets); out: device [n_seg, dim * index_width], column j of ids
+ * pooled into columns [j*dim, (j+1)*dim).  Replaces FusedEmbeddingSeqPoolKernel / EmbeddingVSumFunctor
+ * (fused/fused_embedding_seq_pool_op.h:84-127) and jit::refer::EmbSeqPool incl. index_width > 1
+ * (jit/refer/refer.h:477-528).  Ids outside the table are reported by ctrfe_check_ids (slot = the
+ * ids column); the reference kernel has no padding_idx on this path, here it pools as a zero row. */
+int ctrfe_fused_embedding_seq_pool(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t dim, int32_t dtype,
+                                   const int64_t* ids, int64_t n_rows, int64_t index_width, const uint64_t* lod_host,
+                                   int64_t n_seg, int64_t padding_idx, void* out, void* stream);
+
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 
 /* lookup_table_v2 / phi embedding: out[k,:] = (ids[k]==padding_idx) ? 0 : table[ids[k],:].

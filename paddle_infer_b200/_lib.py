@@ -71,7 +71,7 @@ _lib = None
 EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
-    "ctrfe_plan_num_kernels", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create",
+    "ctrfe_plan_num_kernels", "ctrfe_fused_embedding_seq_pool", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create",
     "ctrfe_host_pipe_run", "ctrfe_host_pipe_destroy", "ctrfe_plan_kernel_name", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
@@ -106,6 +106,7 @@ def lib():
         L.ctrfe_host_pipe_destroy.argtypes = [vp]
         L.ctrfe_plan_kernel_name.argtypes = [vp, C.c_int]
         L.ctrfe_plan_kernel_name.restype = C.c_char_p
+        L.ctrfe_fused_embedding_seq_pool.argtypes = [vp, vp, i64, i64, i32, vp, i64, i64, vp, i64, i64, vp, vp]
         L.ctrfe_embedding.argtypes = [vp, vp, i64, i64, vp, i32, i64, i64, vp, vp]
         L.ctrfe_sequence_pool.argtypes = [vp, vp, i32, i64, vp, i64, i32, C.c_float, vp, vp, vp]
         L.ctrfe_cvm.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp]

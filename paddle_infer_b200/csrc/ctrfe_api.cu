@@ -61,6 +61,8 @@ struct ctrfe_ctx {
   // LoD image of the one-shot ctrfe_fused_forward / ctrfe_sequence_pool paths
   char* scratch = nullptr;
   size_t scratch_cap = 0;
+  char* id_scratch = nullptr;  // transposed ids of ctrfe_fused_embedding_seq_pool (index_width > 1)
+  size_t id_scratch_cap = 0;
   // Every plan and every one-shot call gets a tag (1..255, reused cyclically) that its launches OR
   // into the error keys they record, so ctrfe_check_ids can fetch the offending id from the batch
   // that met it even with several plans in flight.
@@ -612,6 +614,7 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
     if (s.host) cudaFreeHost(s.host);
   }
   if (c->scratch) cudaFree(c->scratch);
+  if (c->id_scratch) cudaFree(c->id_scratch);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
@@ -794,6 +797,61 @@ int ctrfe_fused_forward(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stre
   if (rc) return rc;
   ctx->tag_ids[plan.tag].swap(plan.id_src);
   return launch_plan(plan, st);
+}
+
+int ctrfe_fused_embedding_seq_pool(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t dim, int32_t dtype,
+                                   const int64_t* ids, int64_t n_rows, int64_t index_width, const uint64_t* lod_host,
+                                   int64_t n_seg, int64_t padding_idx, void* out, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "fused_embedding_seq_pool: null ctx");
+  if (!lod_host) return fail(CTRFE_ERR_ARG, "fused_embedding_seq_pool: The LoD level of Input(Ids) should be 1.");
+  if (index_width < 1 || index_width > 4096 || n_rows < 0 || n_seg < 0 || dim <= 0)
+    return fail(CTRFE_ERR_ARG, "fused_embedding_seq_pool: bad shape (index_width %lld)", (long long)index_width);
+  if (n_seg == 0) return CTRFE_OK;
+  if (!table || !out || (n_rows > 0 && !ids)) return fail(CTRFE_ERR_ARG, "fused_embedding_seq_pool: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  const long long* cols = reinterpret_cast<const long long*>(ids);
+  if (index_width > 1 && n_rows > 0) {
+    const size_t need = static_cast<size_t>(n_rows) * index_width * 8;
+    if (ctx->id_scratch_cap < need) {
+      if (ctx->id_scratch) { CU(cudaStreamSynchronize(st)); CU(cudaFree(ctx->id_scratch)); ctx->id_scratch = nullptr; }
+      CU(cudaMalloc(reinterpret_cast<void**>(&ctx->id_scratch), need + need / 4));
+      ctx->id_scratch_cap = need + need / 4;
+    }
+    const long long total = n_rows * index_width;
+    ctrfe::ids_transpose_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+        reinterpret_cast<const long long*>(ids), n_rows, static_cast<int>(index_width), reinterpret_cast<long long*>(ctx->id_scratch));
+    CU(cudaGetLastError());
+    cols = reinterpret_cast<const long long*>(ctx->id_scratch);
+  }
+  std::vector<ctrfe_slot> slots(static_cast<size_t>(index_width));
+  const int es = elem_size(dtype);
+  for (int64_t w = 0; w < index_width; ++w) {
+    ctrfe_slot& sl = slots[w];
+    sl.table = table;
+    sl.table_rows = table_rows;
+    sl.ids = cols + w * n_rows;
+    sl.n_ids = n_rows;
+    sl.lod = lod_host;
+    sl.n_seg = n_seg;
+    sl.out = static_cast<char*>(out) + w * dim * es;  // column w of Ids pools into columns [w*D, (w+1)*D) of Out
+    sl.out_ld = dim * index_width;
+    sl.pooltype = CTRFE_POOL_SUM;
+    sl.ids_dtype = CTRFE_I64;
+  }
+  ctrfe_fused_desc d{};
+  d.n_slots = static_cast<int32_t>(index_width);
+  d.dtype = dtype;
+  d.slots = slots.data();
+  d.dim = dim;
+  d.padding_idx = padding_idx;
+  d.pad_value = 0.0f;
+  d.cvm_mode = CTRFE_CVM_NONE;
+  d.cvm_offset = 2;
+  d.scale_mode = CTRFE_SCALE_DIVIDE;
+  d.init_mode = CTRFE_INIT_FIRST_ROW;  // refer.h:513-517: the first row is copied, the rest added in id order
+  d.lod_location = CTRFE_LOD_HOST;
+  return ctrfe_fused_forward(ctx, &d, stream);
 }
 
 int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes, const void* ids,

@@ -749,6 +749,17 @@ __global__ void cvm_f64_kernel(const double* __restrict__ x, long long rows, int
   y[t] = v;
 }
 
+// ids [K, W] row-major -> W contiguous arrays of K ids (column w at out + w * K): lets an Ids tensor
+// whose last dimension is wider than 1 (fused_embedding_seq_pool, refer.h:477-528 index_width) feed
+// the pooling kernels, which want one contiguous id run per slot.
+__global__ void ids_transpose_kernel(const long long* __restrict__ ids, long long k, int w, long long* __restrict__ out) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= k * w) return;
+  const long long r = t / w;
+  const int c = static_cast<int>(t - r * w);
+  out[static_cast<long long>(c) * k + r] = ids[t];
+}
+
 // Fills a feasign key map: keys[i] -> row i.  Open addressing, linear probing, 0 = empty slot
 // (key 0 is the padding feasign and is never stored).  A key that finds no slot within
 // kKeyProbes is counted in *n_unplaced (the caller rebuilds with more slots).

@@ -591,16 +591,37 @@ def fused_embedding_seq_pool(W: torch.Tensor, Ids: torch.Tensor, lod, combiner: 
                              padding_idx: int = -1, is_sparse: bool = False, *, check: bool = True,
                              ctx: Optional[Context] = None) -> torch.Tensor:
     """Gather + SUM per sequence (fused/fused_embedding_seq_pool_op.h:84-127, the EmbSeqPool
-    route: first row copied, the rest added in id order).  Ids: [K, 1] int64 with one LoD
-    level; Out: [num_seq, D]."""
+    route: first row copied, the rest added in id order).  Ids: [K, idx_width] int64 with one LoD
+    level over its rows; Out: [num_seq, D * idx_width], column j of Ids pooled into columns
+    [j*D, (j+1)*D) (jit/refer/refer.h:477-528)."""
     if combiner != "sum":
         raise Unimplemented("fused_embedding_seq_pool only supports combiner 'sum'")
-    if Ids.dim() == 2 and Ids.shape[1] != 1:
-        raise Unimplemented("fused_embedding_seq_pool: ids last dimension > 1 is not supported here")
     if len(lod) != 1:
         raise InvalidArgument("The LoD level of Input(Ids) should be 1.")
-    return ctr_fused_emb_seqpool_cvm(W, [Ids.reshape(-1)], [lod[0]], "SUM", padding_idx=padding_idx, use_cvm=None,
-                                     init_mode=B.INIT_FIRST_ROW, check=check, ctx=ctx)[0]
+    _need_cuda(W, "W"), _need_cuda(Ids, "Ids")
+    if W.dim() != 2 or Ids.dim() > 2:
+        raise InvalidArgument("The dimension of W and Ids should be 2.")
+    if Ids.dtype != torch.int64:
+        raise Unimplemented("fused_embedding_seq_pool: Ids must be int64")
+    if W.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise Unimplemented(f"dtype {W.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    ids2 = Ids.contiguous().view(Ids.shape[0], -1)
+    width = ids2.shape[1]
+    last = _lod_np(lod[0])
+    n_seg = last.size - 1
+    if int(last[-1]) > ids2.shape[0]:
+        raise InvalidArgument("The last LoD offset exceeds the first dimension of Input(Ids).")
+    ctx = ctx or default_context(W.device)
+    W = W.contiguous()
+    out = torch.empty((n_seg, W.shape[1] * width), dtype=W.dtype, device=W.device)
+    B.check(B.lib().ctrfe_fused_embedding_seq_pool(ctx.handle, W.data_ptr(), W.shape[0], W.shape[1], _DT[W.dtype],
+                                                   ids2.data_ptr(), ids2.shape[0], width, last.ctypes.data, n_seg,
+                                                   int(padding_idx), out.data_ptr(), ctx.stream()))
+    if check:
+        ctx.check_ids()
+    else:
+        ctx._keep_alive = ids2  # the launch reads it asynchronously
+    return out
 
 
 # ------------------------------------------------------------------------------------------

@@ -13,13 +13,20 @@
 //     b200_lookup_table_v2        W, Ids -> Out                    (1:1 clone)
 //     b200_sequence_pool          X -> Out, MaxIndex               (1:1 clone)
 //     b200_cvm                    X, CVM -> Y                      (1:1 clone)
+//     b200_fused_seqpool_cvm      X@VECTOR, CVM -> Out@VECTOR      (PaddleBox's multi-slot op, 1:1 clone)
+//     b200_fused_embedding_seq_pool  W, Ids -> Out                 (1:1 clone)
+//     b200_pull_box_sparse        W, MapKeys, MapRows, Ids@VECTOR -> Out@VECTOR  (resident table + key map)
+//     b200_fusion_seqpool_cvm_concat X@VECTOR, CVM -> Out          (the CPU predictor's fused op)
 // with the reference ops' input/output/attribute names, and paddle_infer_b200/rewrite.py
 // retargets a loaded program's op types (the saved model on disk is untouched).
 //
 // LoD: paddle::Tensor has no LoD accessor; the DenseTensor behind it carries it
 // (custom_operator.cc:159,173 copy meta incl. lod; phi/core/tensor_meta.h:72).
 #include <cstdint>
+#include <map>
+#include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "paddle/extension.h"
@@ -72,16 +79,24 @@ int PoolCode(const std::string& p) {
   return -1;
 }
 
-// One context per device for the process (the C core is re-entrant across contexts; a
-// predictor and its clones run one thread each, so guard the lazy creation only).
+// One context per (device, stream).  A ctrfe_ctx owns one LoD scratch image, one staging ring and
+// one error record, all ordered by the stream it is used with, so two predictor clones -- one
+// thread and one stream each on the same GPU (analysis_predictor.cc Clone) -- must not share one.
+// The map itself is guarded; a context is only ever used from the thread that runs its stream.
 ctrfe_ctx* CtxFor(const paddle::Tensor& t) {
-  static ctrfe_ctx* ctxs[64] = {nullptr};
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, ctrfe_ctx*> ctxs;
   const int dev = t.place().GetDeviceId();
-  PD_CHECK(dev >= 0 && dev < 64, "ctrfe: bad device id");
-  if (ctxs[dev] == nullptr) {
-    PD_CHECK(ctrfe_ctx_create(dev, &ctxs[dev]) == CTRFE_OK, ctrfe_last_error());
+  PD_CHECK(dev >= 0, "ctrfe: bad device id");
+  const void* stream = reinterpret_cast<const void*>(t.stream());
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = ctxs.find({dev, stream});
+  if (it == ctxs.end()) {
+    ctrfe_ctx* c = nullptr;
+    PD_CHECK(ctrfe_ctx_create(dev, &c) == CTRFE_OK, ctrfe_last_error());
+    it = ctxs.emplace(std::make_pair(dev, stream), c).first;
   }
-  return ctxs[dev];
+  return it->second;
 }
 
 void Check(int rc) { PD_CHECK(rc == CTRFE_OK, ctrfe_last_error()); }
@@ -97,7 +112,7 @@ void NeedGpu(const paddle::Tensor& t, const char* what) {
 // ---------------------------------------------------------------------------------------
 std::vector<paddle::Tensor> CtrFusedForward(const paddle::Tensor& w, const std::vector<paddle::Tensor>& ids,
                                             const std::string& pooltype, float pad_value, int64_t padding_idx,
-                                            bool use_cvm, int cvm_offset) {
+                                            bool use_cvm, int cvm_offset, bool check_ids) {
   NeedGpu(w, "W");
   const auto wshape = w.shape();
   PD_CHECK(wshape.size() == 2, "ShapeError: The dimensions of the 'lookup table' must be 2.");
@@ -124,6 +139,7 @@ std::vector<paddle::Tensor> CtrFusedForward(const paddle::Tensor& w, const std::
     sl.out_ld = d_out;
     sl.pooltype = pool;
     sl.ids_dtype = IdCode(ids[s].dtype());
+    sl.n_ids = ids[s].numel();  // a LoD that names more ids than the tensor holds is refused, not read
   }
   ctrfe_fused_desc d{};
   d.n_slots = static_cast<int32_t>(slots.size());
@@ -137,14 +153,19 @@ std::vector<paddle::Tensor> CtrFusedForward(const paddle::Tensor& w, const std::
   d.scale_mode = CTRFE_SCALE_DIVIDE;
   d.init_mode = CTRFE_INIT_ZERO;
   d.lod_location = CTRFE_LOD_HOST;
-  Check(ctrfe_fused_forward(CtxFor(w), &d, w.stream()));
+  ctrfe_ctx* ctx = CtxFor(w);
+  Check(ctrfe_fused_forward(ctx, &d, w.stream()));
+  // check_ids: synchronise and raise on an id outside the table, as the reference's CPU
+  // lookup_table_v2 does (embedding_kernel.cc:59-76).  Without it an offending row pools as zeros
+  // and the record stays with THIS launch's tag until some later check reports it.
+  if (check_ids) Check(ctrfe_check_ids(ctx, w.stream(), nullptr, nullptr, nullptr));
   return outs;
 }
 
 std::vector<std::vector<int64_t>> CtrFusedInferShape(const std::vector<int64_t>& w_shape,
                                                      const std::vector<std::vector<int64_t>>& ids_shapes,
                                                      const std::string& pooltype, float pad_value,
-                                                     int64_t padding_idx, bool use_cvm, int cvm_offset) {
+                                                     int64_t padding_idx, bool use_cvm, int cvm_offset, bool check_ids) {
   // batch is only known from the LoD at run time, as in fused_seqpool_cvm_op.cc:82-91
   std::vector<std::vector<int64_t>> out;
   for (size_t i = 0; i < ids_shapes.size(); ++i) out.push_back({-1, use_cvm ? w_shape[1] : w_shape[1] - cvm_offset});
@@ -160,7 +181,7 @@ PD_BUILD_OP(ctr_fused_emb_seqpool_cvm)
     .Inputs({"W", paddle::Vec("Ids")})
     .Outputs({paddle::Vec("Out")})
     .Attrs({"pooltype: std::string", "pad_value: float", "padding_idx: int64_t", "use_cvm: bool",
-            "cvm_offset: int"})
+            "cvm_offset: int", "check_ids: bool"})
     .SetKernelFn(PD_KERNEL(CtrFusedForward))
     .SetInferShapeFn(PD_INFER_SHAPE(CtrFusedInferShape))
     .SetInferDtypeFn(PD_INFER_DTYPE(CtrFusedInferDtype));
@@ -237,6 +258,218 @@ PD_BUILD_OP(b200_fusion_seqpool_cvm_concat)
     .SetKernelFn(PD_KERNEL(B200FusionSeqpoolCvmConcat))
     .SetInferShapeFn(PD_INFER_SHAPE(B200FusionSeqpoolCvmConcatInferShape))
     .SetInferDtypeFn(PD_INFER_DTYPE(B200FusionSeqpoolCvmConcatInferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_fused_seqpool_cvm  (FusedSeqpoolCVMOpMaker, fused/fused_seqpool_cvm_op.cc:120-150): PaddleBox's
+// multi-slot op over pre-pulled values.  X (duplicable, LoD rows), CVM -> Out (duplicable);
+// pooltype in {SUM}; the accumulator STARTS at pad_value (fused_seqpool_cvm_op.cu:49);
+// use_cvm=false drops cvm_offset leading columns.  One launch for all slots.
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200FusedSeqpoolCvm(const std::vector<paddle::Tensor>& xs, const paddle::Tensor& cvm,
+                                                const std::string& pooltype, float pad_value, bool use_cvm,
+                                                int cvm_offset) {
+  PD_CHECK(pooltype == "SUM", "fused_seqpool_cvm only supports pooltype SUM");
+  PD_CHECK(!xs.empty(), "Input(X) of fused_seqpool_cvm is empty");
+  NeedGpu(xs[0], "X");
+  const int64_t w = xs[0].numel() / xs[0].shape()[0];
+  const int64_t d_out = use_cvm ? w : w - cvm_offset;
+  std::vector<ctrfe_slot> slots(xs.size());
+  std::vector<paddle::Tensor> outs;
+  outs.reserve(xs.size());
+  for (size_t s = 0; s < xs.size(); ++s) {
+    const auto& lod = LodOf(xs[s]);
+    PD_CHECK(!lod.empty(), "Input(X) of fused_seqpool_cvm must carry LoD");
+    PD_CHECK(xs[s].numel() / xs[s].shape()[0] == w, "Width of all inputs should be equal.");
+    const auto& last = lod.back();
+    const int64_t n_seg = static_cast<int64_t>(last.size()) - 1;
+    outs.emplace_back(paddle::empty({n_seg, d_out}, xs[s].dtype(), xs[s].place()));
+    ctrfe_slot& sl = slots[s];
+    sl.table = Raw(xs[s]);
+    sl.table_rows = xs[s].shape()[0];
+    sl.ids = nullptr;  // dense rows: row index = position
+    sl.n_ids = 0;
+    sl.lod = reinterpret_cast<const uint64_t*>(last.data());
+    sl.n_seg = n_seg;
+    sl.out = RawMut(outs.back());
+    sl.out_ld = d_out;
+    sl.pooltype = CTRFE_POOL_SUM;
+    sl.ids_dtype = CTRFE_I64;
+  }
+  ctrfe_fused_desc d{};
+  d.n_slots = static_cast<int32_t>(slots.size());
+  d.dtype = DtypeCode(xs[0].dtype());
+  d.slots = slots.data();
+  d.dim = w;
+  d.padding_idx = -1;
+  d.pad_value = pad_value;
+  d.cvm_mode = use_cvm ? CTRFE_CVM_USE : CTRFE_CVM_STRIP;
+  d.cvm_offset = cvm_offset;
+  d.scale_mode = CTRFE_SCALE_DIVIDE;
+  d.init_mode = CTRFE_INIT_PAD;
+  d.lod_location = CTRFE_LOD_HOST;
+  Check(ctrfe_fused_forward(CtxFor(xs[0]), &d, xs[0].stream()));
+  return outs;
+}
+
+std::vector<std::vector<int64_t>> B200FusedSeqpoolCvmInferShape(const std::vector<std::vector<int64_t>>& x_shapes,
+                                                                const std::vector<int64_t>& cvm_shape,
+                                                                const std::string& pooltype, float pad_value,
+                                                                bool use_cvm, int cvm_offset) {
+  std::vector<std::vector<int64_t>> out;  // batch comes from the LoD at run time (fused_seqpool_cvm_op.cc:82-91)
+  for (const auto& xs : x_shapes) out.push_back({-1, use_cvm ? xs[1] : xs[1] - cvm_offset});
+  return out;
+}
+
+std::vector<paddle::DataType> B200FusedSeqpoolCvmInferDtype(const std::vector<paddle::DataType>& x_dtypes,
+                                                            const paddle::DataType& cvm_dtype) {
+  return x_dtypes;
+}
+
+PD_BUILD_OP(b200_fused_seqpool_cvm)
+    .Inputs({paddle::Vec("X"), "CVM"})
+    .Outputs({paddle::Vec("Out")})
+    .Attrs({"pooltype: std::string", "pad_value: float", "use_cvm: bool", "cvm_offset: int"})
+    .SetKernelFn(PD_KERNEL(B200FusedSeqpoolCvm))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200FusedSeqpoolCvmInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200FusedSeqpoolCvmInferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_fused_embedding_seq_pool  (FusedEmbeddingSeqPoolOpMaker, fused/fused_embedding_seq_pool_op.cc:
+// 82-130): W, Ids [K, idx_width] int64 with one LoD level -> Out [num_seq, D * idx_width]; combiner
+// "sum"; the EmbSeqPool order (first row copied, the rest added in id order,
+// jit/refer/refer.h:477-528).  Column j of Ids is pooled into columns [j*D, (j+1)*D) of Out.
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200FusedEmbeddingSeqPool(const paddle::Tensor& w, const paddle::Tensor& ids,
+                                                      const std::string& combiner, int64_t padding_idx,
+                                                      bool grad_inplace, bool is_sparse) {
+  PD_CHECK(combiner == "sum", "fused_embedding_seq_pool only supports combiner sum");
+  NeedGpu(w, "W");
+  NeedGpu(ids, "Ids");
+  PD_CHECK(ids.dtype() == paddle::DataType::INT64, "fused_embedding_seq_pool: Ids must be int64");
+  const auto wshape = w.shape();
+  const auto ishape = ids.shape();
+  PD_CHECK(wshape.size() == 2 && ishape.size() == 2, "The dimension of W and Ids should be 2.");
+  const auto& lod = LodOf(ids);
+  PD_CHECK(lod.size() == 1, "The LoD level of Input(Ids) should be 1.");
+  const int64_t n_seg = static_cast<int64_t>(lod[0].size()) - 1;
+  const int64_t width = ishape[1], dim = wshape[1];
+  auto out = paddle::empty({n_seg, dim * width}, w.dtype(), w.place());
+  Check(ctrfe_fused_embedding_seq_pool(CtxFor(w), Raw(w), wshape[0], dim, DtypeCode(w.dtype()), static_cast<const int64_t*>(Raw(ids)), ishape[0], width,
+                                       reinterpret_cast<const uint64_t*>(lod[0].data()), n_seg, padding_idx,
+                                       RawMut(out), w.stream()));
+  Check(ctrfe_check_ids(CtxFor(w), w.stream(), nullptr, nullptr, nullptr));
+  return {out};
+}
+
+std::vector<std::vector<int64_t>> B200FusedEmbeddingSeqPoolInferShape(const std::vector<int64_t>& w_shape,
+                                                                      const std::vector<int64_t>& ids_shape,
+                                                                      const std::string& combiner, int64_t padding_idx,
+                                                                      bool grad_inplace, bool is_sparse) {
+  return {{-1, w_shape[1] * ids_shape[1]}};  // fused_embedding_seq_pool_op.cc:62-71
+}
+
+std::vector<paddle::DataType> B200FusedEmbeddingSeqPoolInferDtype(const paddle::DataType& w_dtype,
+                                                                  const paddle::DataType& ids_dtype) {
+  return {w_dtype};
+}
+
+PD_BUILD_OP(b200_fused_embedding_seq_pool)
+    .Inputs({"W", "Ids"})
+    .Outputs({"Out"})
+    .Attrs({"combiner: std::string", "padding_idx: int64_t", "grad_inplace: bool", "is_sparse: bool"})
+    .SetKernelFn(PD_KERNEL(B200FusedEmbeddingSeqPool))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200FusedEmbeddingSeqPoolInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200FusedEmbeddingSeqPoolInferDtype));
+
+// ---------------------------------------------------------------------------------------
+// b200_pull_box_sparse  (PullBoxSparseOpMaker, pull_box_sparse_op.cc:62-100): Ids (duplicable,
+// uint64 feasign keys held as int64) -> Out (duplicable, [K_s, size]).  The reference asks BoxPS for
+// the values; here the table is resident: W [n_keys, size] is the dense image of the pull values and
+// MapKeys / MapRows the key map built by ctrfe_keymap_build (two extra inputs the reference op does
+// not have -- its table lives behind the BoxPS handle).  Key 0 and unknown keys give zero rows.
+// ---------------------------------------------------------------------------------------
+std::vector<paddle::Tensor> B200PullBoxSparse(const paddle::Tensor& w, const paddle::Tensor& map_keys,
+                                              const paddle::Tensor& map_rows, const std::vector<paddle::Tensor>& ids,
+                                              int size, bool is_sparse, bool is_distributed) {
+  NeedGpu(w, "W");
+  const auto wshape = w.shape();
+  PD_CHECK(wshape.size() == 2 && wshape[1] == size, "pull_box_sparse: W must be [n_keys, size]");
+  const int64_t n_slots_map = map_keys.numel();
+  PD_CHECK(n_slots_map == map_rows.numel() && n_slots_map >= 16 && (n_slots_map & (n_slots_map - 1)) == 0,
+           "pull_box_sparse: MapKeys / MapRows must have the same power-of-two length");
+  int log2 = 0;
+  while ((int64_t{1} << log2) < n_slots_map) ++log2;
+  ctrfe_keymap km{};
+  km.keys = static_cast<const uint64_t*>(Raw(map_keys));
+  km.rows = static_cast<const uint32_t*>(Raw(map_rows));
+  km.log2_slots = log2;
+  km.n_keys = wshape[0];
+  std::vector<ctrfe_slot> slots(ids.size());
+  std::vector<std::vector<uint64_t>> unit(ids.size());  // one key per "sequence": FIRST pool = plain pull
+  std::vector<paddle::Tensor> outs;
+  outs.reserve(ids.size());
+  for (size_t s = 0; s < ids.size(); ++s) {
+    NeedGpu(ids[s], "Ids");
+    PD_CHECK(ids[s].dtype() == paddle::DataType::INT64, "pull_box_sparse: Ids must be int64 (uint64 feasigns)");
+    const int64_t k = ids[s].numel();
+    unit[s].resize(static_cast<size_t>(k) + 1);
+    for (int64_t i = 0; i <= k; ++i) unit[s][i] = static_cast<uint64_t>(i);
+    outs.emplace_back(paddle::empty({k, static_cast<int64_t>(size)}, w.dtype(), w.place()));
+    ctrfe_slot& sl = slots[s];
+    sl.table = Raw(w);
+    sl.table_rows = wshape[0];
+    sl.ids = Raw(ids[s]);
+    sl.n_ids = k;
+    sl.lod = unit[s].data();
+    sl.n_seg = k;
+    sl.out = RawMut(outs.back());
+    sl.out_ld = size;
+    sl.pooltype = CTRFE_POOL_FIRST;
+    sl.ids_dtype = CTRFE_I64;
+  }
+  ctrfe_fused_desc d{};
+  d.n_slots = static_cast<int32_t>(slots.size());
+  d.dtype = DtypeCode(w.dtype());
+  d.slots = slots.data();
+  d.dim = size;
+  d.padding_idx = -1;
+  d.cvm_mode = CTRFE_CVM_NONE;
+  d.cvm_offset = 2;
+  d.scale_mode = CTRFE_SCALE_DIVIDE;
+  d.init_mode = CTRFE_INIT_ZERO;
+  d.lod_location = CTRFE_LOD_HOST;
+  d.keymap = &km;
+  Check(ctrfe_fused_forward(CtxFor(w), &d, w.stream()));
+  return outs;
+}
+
+std::vector<std::vector<int64_t>> B200PullBoxSparseInferShape(const std::vector<int64_t>& w_shape,
+                                                              const std::vector<int64_t>& mk_shape,
+                                                              const std::vector<int64_t>& mr_shape,
+                                                              const std::vector<std::vector<int64_t>>& ids_shapes, int size,
+                                                              bool is_sparse, bool is_distributed) {
+  std::vector<std::vector<int64_t>> out;  // Ids dims with the trailing 1 replaced by size (pull_box_sparse_op.cc:40-52)
+  for (const auto& is : ids_shapes) {
+    auto o = is;
+    if (!o.empty() && o.back() == 1) o.back() = size; else o.push_back(size);
+    out.push_back(o);
+  }
+  return out;
+}
+
+std::vector<paddle::DataType> B200PullBoxSparseInferDtype(const paddle::DataType& w_dtype, const paddle::DataType& mk,
+                                                          const paddle::DataType& mr,
+                                                          const std::vector<paddle::DataType>& ids_dtypes) {
+  return std::vector<paddle::DataType>(ids_dtypes.size(), w_dtype);
+}
+
+PD_BUILD_OP(b200_pull_box_sparse)
+    .Inputs({"W", "MapKeys", "MapRows", paddle::Vec("Ids")})
+    .Outputs({paddle::Vec("Out")})
+    .Attrs({"size: int", "is_sparse: bool", "is_distributed: bool"})
+    .SetKernelFn(PD_KERNEL(B200PullBoxSparse))
+    .SetInferShapeFn(PD_INFER_SHAPE(B200PullBoxSparseInferShape))
+    .SetInferDtypeFn(PD_INFER_DTYPE(B200PullBoxSparseInferDtype));
 
 // ---------------------------------------------------------------------------------------
 // b200_lookup_table_v2  (LookupTableV2OpMaker, lookup_table_v2_op.cc:69-104)

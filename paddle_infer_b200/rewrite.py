@@ -24,7 +24,7 @@ every field this module does not name are carried through as opaque bytes / unkn
 """
 from __future__ import annotations
 
-from typing import Dict, List, Tuple
+from typing import Optional, Dict, List, Tuple
 
 from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
 
@@ -106,7 +106,16 @@ def _build_messages():
 
 ProgramDesc, BlockDesc, OpDesc = _build_messages()
 
-RETARGET = {"lookup_table_v2": "b200_lookup_table_v2", "sequence_pool": "b200_sequence_pool", "cvm": "b200_cvm"}
+RETARGET = {"lookup_table_v2": "b200_lookup_table_v2", "sequence_pool": "b200_sequence_pool", "cvm": "b200_cvm",
+            "fused_seqpool_cvm": "b200_fused_seqpool_cvm", "fused_embedding_seq_pool": "b200_fused_embedding_seq_pool"}
+# Ops that read the LoD of their input.  The custom-op runner never copies an output's LoD back
+# (framework/custom_operator.cc:293), so a retargeted lookup_table_v2 / cvm cannot honour the
+# reference's ShareLoD (lookup_table_v2_op.cc:65, cvm_op.cc:46): such an op is left to the built-in
+# kernel when one of these reads its output (the fused rewrites need no LoD to travel).
+LOD_READERS = {"sequence_pool", "b200_sequence_pool", "fused_seqpool_cvm", "b200_fused_seqpool_cvm",
+               "fusion_seqpool_cvm_concat", "b200_fusion_seqpool_cvm_concat", "fused_embedding_seq_pool",
+               "b200_fused_embedding_seq_pool", "cvm_grad", "sequence_pool_grad"}
+SHARES_LOD = {"lookup_table_v2": "Out", "cvm": "Y"}
 FUSED_OP = "ctr_fused_emb_seqpool_cvm"
 
 
@@ -166,14 +175,38 @@ def make_op(op_type: str, inputs: Dict[str, List[str]], outputs: Dict[str, List[
 
 
 # ---- the rewrites ------------------------------------------------------------------------------------
-def retarget_ops(program) -> int:
-    """1:1 renaming of the three ops to their b200_* clones.  Returns the number of ops changed."""
+def _reads_lod(op_type: str) -> bool:
+    return op_type in LOD_READERS or op_type.startswith("sequence_")
+
+
+def retarget_ops(program, pull_box_table: Optional[Dict[str, str]] = None) -> int:
+    """1:1 renaming of the ops to their b200_* clones.  A lookup_table_v2 / cvm whose output feeds
+    an op that reads LoD stays with the built-in kernel (see LOD_READERS).  pull_box_table =
+    {"W": ..., "MapKeys": ..., "MapRows": ...} (variable names of the resident value table and its
+    key map) also retargets pull_box_sparse, which needs those inputs.  Returns the number of ops
+    changed."""
     n = 0
     for blk in program.blocks:
+        use = _consumers(blk)
         for op in blk.ops:
-            if op.type in RETARGET:
-                op.type = RETARGET[op.type]
+            if op.type == "pull_box_sparse" and pull_box_table:
+                ids, outs = op_input(op, "Ids"), op_output(op, "Out")
+                new = make_op("b200_pull_box_sparse",
+                              {"W": [pull_box_table["W"]], "MapKeys": [pull_box_table["MapKeys"]],
+                               "MapRows": [pull_box_table["MapRows"]], "Ids": ids}, {"Out": outs},
+                              [("size", INT, op_attr(op, "size", 1)), ("is_sparse", BOOLEAN, op_attr(op, "is_sparse", False)),
+                               ("is_distributed", BOOLEAN, op_attr(op, "is_distributed", False))])
+                op.CopyFrom(new)
                 n += 1
+                continue
+            if op.type not in RETARGET:
+                continue
+            if op.type in SHARES_LOD:
+                outs = op_output(op, SHARES_LOD[op.type])
+                if any(_reads_lod(blk.ops[u].type) for o in outs for u in use.get(o, [])):
+                    continue  # its output's LoD is needed downstream and a custom op cannot set it
+            op.type = RETARGET[op.type]
+            n += 1
     return n
 
 
@@ -186,18 +219,29 @@ def _consumers(blk) -> Dict[str, List[int]]:
     return use
 
 
-def fuse_front_end(program) -> int:
+def _single_producers(blk) -> Dict[str, int]:
+    """variable -> the op that writes it, for variables written exactly once in the block (a name
+    written twice cannot be matched to one producer, so the rewrites leave it alone)."""
+    count: Dict[str, int] = {}
+    last: Dict[str, int] = {}
+    for i, op in enumerate(blk.ops):
+        for v in op.outputs:
+            for a in v.arguments:
+                count[a] = count.get(a, 0) + 1
+                last[a] = i
+    return {a: i for a, i in last.items() if count[a] == 1}
+
+
+def fuse_front_end(program, check_ids: bool = True) -> int:
     """Replaces lookup_table_v2 -> sequence_pool -> cvm chains by ctr_fused_emb_seqpool_cvm ops,
-    one per group of slots that share (W, pooltype, pad_value, padding_idx, use_cvm).  Returns
-    the number of chains fused."""
+    one per group of slots that share (W, pooltype, pad_value, padding_idx, use_cvm).  check_ids:
+    the fused op synchronises and raises on an id outside the table, as the reference's CPU
+    lookup_table_v2 does (False: a serving loop that checks elsewhere).  Returns the number of
+    chains fused."""
     fused = 0
     for blk in program.blocks:
         use = _consumers(blk)
-        producer = {}
-        for i, op in enumerate(blk.ops):
-            for v in op.outputs:
-                for a in v.arguments:
-                    producer[a] = i
+        producer = _single_producers(blk)
         groups: Dict[Tuple, List[Tuple[int, int, int, str, str]]] = {}
         for ci, cvm in enumerate(blk.ops):
             if cvm.type != "cvm":
@@ -240,7 +284,8 @@ def fuse_front_end(program) -> int:
                 continue
             op = make_op(FUSED_OP, {"W": [w], "Ids": [c[3] for c in chains]}, {"Out": [c[4] for c in chains]},
                          [("pooltype", STRING, pooltype), ("pad_value", FLOAT, pad_value),
-                          ("padding_idx", LONG, padding_idx), ("use_cvm", BOOLEAN, use_cvm), ("cvm_offset", INT, 2)])
+                          ("padding_idx", LONG, padding_idx), ("use_cvm", BOOLEAN, use_cvm), ("cvm_offset", INT, 2),
+                          ("check_ids", BOOLEAN, check_ids)])
             # the fused op goes where the LAST of its cvm ops stood: every input exists by then
             inserts.append((chains[-1][2], op))
             for li, pi, ci, _, _ in chains:
@@ -275,11 +320,7 @@ def fuse_seqpool_cvm_concat(program) -> int:
     fused = 0
     for blk in program.blocks:
         use = _consumers(blk)
-        producer = {}
-        for i, op in enumerate(blk.ops):
-            for v in op.outputs:
-                for a in v.arguments:
-                    producer[a] = i
+        producer = _single_producers(blk)
         dead = set()
         inserts = {}
         for ki, cat in enumerate(blk.ops):
@@ -302,6 +343,9 @@ def fuse_seqpool_cvm_concat(program) -> int:
                 pt = op_attr(pool, "pooltype", "AVERAGE")
                 idx = op_output(pool, "MaxIndex")
                 c_in = op_input(cvm, "CVM")
+                if float(op_attr(pool, "pad_value", 0.0)) != 0.0:
+                    ok = False  # the fused op has no pad_value: an empty sequence would give cvm(0) instead of cvm(pad_value)
+                    break
                 if pt not in ("SUM", "AVERAGE", "SQRT") or (pooltype not in (None, pt)) or (idx and use.get(idx[0])) \
                         or len(c_in) != 1 or (cvm_in not in (None, c_in[0])) or len(op_input(pool, "X")) != 1:
                     ok = False
@@ -333,11 +377,12 @@ def fuse_seqpool_cvm_concat(program) -> int:
     return fused
 
 
-def rewrite_program_bytes(pdmodel: bytes, fuse: bool = True) -> Tuple[bytes, Dict[str, int]]:
+def rewrite_program_bytes(pdmodel: bytes, fuse: bool = True, check_ids: bool = True,
+                          pull_box_table: Optional[Dict[str, str]] = None) -> Tuple[bytes, Dict[str, int]]:
     """Parses a serialized ProgramDesc (`*.pdmodel`), applies the rewrites, serializes it again."""
     prog = ProgramDesc()
     prog.ParseFromString(pdmodel)
-    stats = {"fused_chains": fuse_front_end(prog) if fuse else 0,
+    stats = {"fused_chains": fuse_front_end(prog, check_ids) if fuse else 0,
              "fused_concats": fuse_seqpool_cvm_concat(prog) if fuse else 0}
-    stats["retargeted_ops"] = retarget_ops(prog)
+    stats["retargeted_ops"] = retarget_ops(prog, pull_box_table)
     return prog.SerializeToString(), stats

@@ -222,6 +222,42 @@ def test_fused_modes_reciprocal_firstrow_padinit(env):
         np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), ref.view(np.uint32))
 
 
+@pytest.mark.parametrize("tbl_w,idx_w", [(16, 2), (8, 3), (64, 5), (11, 4)])
+def test_fused_embedding_seq_pool_index_width(env, tbl_w, idx_w):
+    """Ids whose last dimension is wider than 1 (jit/refer/refer.h:477-528, the grid of
+    jit/test.cc:669-720): column j of Ids pools into columns [j*D, (j+1)*D) of Out.  Checked
+    per sequence against the reference's OWN refer::EmbSeqPool compiled into oracle/_ref, to the
+    bit, and against a plain numpy statement when that library is absent."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(tbl_w * 10 + idx_w)
+    N = 300
+    table = rng.uniform(-1, 1, (N, tbl_w)).astype(np.float32)
+    lens = rng.integers(1, 9, 37)
+    lod = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    ids = rng.integers(0, N, (int(lod[-1]), idx_w)).astype(np.int64)
+    out = ops.fused_embedding_seq_pool(_t(table, dev), _t(ids, dev), [lod]).cpu().numpy()
+    assert out.shape == (37, tbl_w * idx_w)
+    R = O.ref_lib()
+    for i in range(37):
+        sub = np.ascontiguousarray(ids[int(lod[i]):int(lod[i + 1])])
+        if R is not None:
+            ref = np.empty(tbl_w * idx_w, np.float32)
+            assert R.ref_embseqpool_f32(table.ctypes.data, N, tbl_w, sub.ctypes.data, sub.shape[0], idx_w, ref.ctypes.data) == 0
+        else:
+            ref = np.empty(tbl_w * idx_w, np.float32)
+            for w in range(idx_w):
+                acc = table[sub[0, w]].copy()
+                for h in range(1, sub.shape[0]):
+                    acc = acc + table[sub[h, w]]
+                ref[w * tbl_w:(w + 1) * tbl_w] = acc
+        np.testing.assert_array_equal(out[i].view(np.uint32), ref.view(np.uint32))
+    bad = ids.copy()
+    bad[5, idx_w - 1] = N + 9
+    with pytest.raises(ValueError) as e:
+        ops.fused_embedding_seq_pool(_t(table, dev), _t(bad, dev), [lod])
+    assert e.value.slot == idx_w - 1 and e.value.position == 5 and e.value.id_value == N + 9
+
+
 def test_fused_seqpool_cvm_paddlebox(env):
     ops, O, B, dev = env
     rng = np.random.default_rng(31)

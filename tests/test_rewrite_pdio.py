@@ -64,15 +64,16 @@ def test_fuse_groups_by_table_and_respects_other_consumers():
     assert R.fuse_front_end(prog) == 2                                     # slot 0's pooled rows have two readers
     types = [o.type for o in prog.blocks[0].ops]
     assert types.count(R.FUSED_OP) == 1 and types[:3] == ["lookup_table_v2", "sequence_pool", "cvm"]
-    # what is left is retargeted 1:1
-    assert R.retarget_ops(prog) == 3
-    assert [o.type for o in prog.blocks[0].ops][:3] == ["b200_lookup_table_v2", "b200_sequence_pool", "b200_cvm"]
+    # what is left is retargeted 1:1 -- except the gather, whose Out feeds an op that reads its LoD: a
+    # custom op cannot pass LoD on (custom_operator.cc:293), so it stays with the built-in kernel
+    assert R.retarget_ops(prog) == 2
+    assert [o.type for o in prog.blocks[0].ops][:3] == ["lookup_table_v2", "b200_sequence_pool", "b200_cvm"]
 
 
 def test_retarget_only():
     prog = _front_end_program(2)
     out, stats = R.rewrite_program_bytes(prog.SerializeToString(), fuse=False)
-    assert stats == {"fused_chains": 0, "fused_concats": 0, "retargeted_ops": 6}
+    assert stats == {"fused_chains": 0, "fused_concats": 0, "retargeted_ops": 4}   # the two gathers keep their LoD-sharing kernel
     new = R.ProgramDesc()
     new.ParseFromString(out)
     op = new.blocks[0].ops[1]
@@ -230,3 +231,40 @@ def test_rewritten_program_computes_the_same_front_end():
     assert R.fuse_front_end(prog) == S
     after = run(prog)
     assert before.shape == (Bsz, S * D) and torch.equal(before, after)
+
+
+def test_retarget_rules_for_lod_and_new_clones():
+    """A lookup_table_v2 whose rows go to an op that does not read LoD is retargeted; the PaddleBox ops
+    get their clones; pull_box_sparse only with the resident table's variables; a pool with a
+    non-zero pad_value is not folded into the concat fusion; a variable written twice is not matched."""
+    prog = R.ProgramDesc()
+    blk = prog.blocks.add()
+    blk.idx, blk.parent_idx = 0, -1
+    blk.ops.add().CopyFrom(R.make_op("lookup_table_v2", {"W": ["emb"], "Ids": ["ids"]}, {"Out": ["rows"]},
+                                     [("padding_idx", R.LONG, -1)]))
+    blk.ops.add().CopyFrom(R.make_op("scale", {"X": ["rows"]}, {"Out": ["z"]}))
+    blk.ops.add().CopyFrom(R.make_op("fused_seqpool_cvm", {"X": ["a", "b"], "CVM": ["n"]}, {"Out": ["p", "q"]},
+                                     [("pooltype", R.STRING, "SUM"), ("pad_value", R.FLOAT, 0.0), ("use_cvm", R.BOOLEAN, True),
+                                      ("cvm_offset", R.INT, 2)]))
+    blk.ops.add().CopyFrom(R.make_op("fused_embedding_seq_pool", {"W": ["emb"], "Ids": ["ids2"]}, {"Out": ["o"]},
+                                     [("combiner", R.STRING, "sum")]))
+    blk.ops.add().CopyFrom(R.make_op("pull_box_sparse", {"Ids": ["k0", "k1"]}, {"Out": ["v0", "v1"]}, [("size", R.INT, 11)]))
+    assert R.retarget_ops(prog) == 3
+    assert [o.type for o in blk.ops] == ["b200_lookup_table_v2", "scale", "b200_fused_seqpool_cvm",
+                                         "b200_fused_embedding_seq_pool", "pull_box_sparse"]
+    assert R.retarget_ops(prog, pull_box_table={"W": "vals", "MapKeys": "mk", "MapRows": "mr"}) == 1
+    p = blk.ops[4]
+    assert p.type == "b200_pull_box_sparse" and R.op_input(p, "W") == ["vals"] and R.op_input(p, "MapKeys") == ["mk"]
+    assert R.op_input(p, "Ids") == ["k0", "k1"] and R.op_output(p, "Out") == ["v0", "v1"] and R.op_attr(p, "size") == 11
+    # pad_value != 0 blocks the concat fusion
+    prog = _pass_tester_program()
+    R.set_attr(prog.blocks[0].ops[1], "pad_value", R.FLOAT, 0.5)
+    assert R.fuse_seqpool_cvm_concat(prog) == 0
+    # a variable with two writers is not matched
+    prog = _pass_tester_program()
+    prog.blocks[0].ops.add().CopyFrom(R.make_op("scale", {"X": ["a"]}, {"Out": ["e"]}))
+    assert R.fuse_seqpool_cvm_concat(prog) == 0
+    # the fused front end carries check_ids
+    prog = _front_end_program(2)
+    assert R.fuse_front_end(prog, check_ids=False) == 2
+    assert R.op_attr(prog.blocks[0].ops[0], "check_ids") is False
