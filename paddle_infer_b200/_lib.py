@@ -52,6 +52,7 @@ class CtrfeError(RuntimeError):
         self.code = code
 
 
+COPY_H2D, COPY_D2H, COPY_D2D = 1, 2, 3
 LAUNCH_OVERLAP_PREVIOUS = 1
 LAUNCH_UPLOAD_LOD = 2
 
@@ -69,7 +70,8 @@ _lib = None
 
 # every symbol include/ctrfe.h declares (tests check the .so exports each one)
 EXPORTS = [
-    "ctrfe_version", "ctrfe_last_error", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
+    "ctrfe_version", "ctrfe_last_error", "ctrfe_malloc", "ctrfe_free", "ctrfe_host_alloc", "ctrfe_host_free",
+    "ctrfe_memcpy", "ctrfe_stream_synchronize", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_fused_embedding_seq_pool", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create",
     "ctrfe_host_pipe_run", "ctrfe_host_pipe_destroy", "ctrfe_plan_kernel_name", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
@@ -90,6 +92,12 @@ def lib():
         vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
         L.ctrfe_version.restype = C.c_int
         L.ctrfe_last_error.restype = C.c_char_p
+        L.ctrfe_malloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp)]
+        L.ctrfe_free.argtypes = [C.c_int, vp]
+        L.ctrfe_host_alloc.argtypes = [C.c_uint64, C.POINTER(vp)]
+        L.ctrfe_host_free.argtypes = [vp]
+        L.ctrfe_memcpy.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_int, vp, C.c_int]
+        L.ctrfe_stream_synchronize.argtypes = [C.c_int, vp]
         L.ctrfe_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
         L.ctrfe_ctx_destroy.argtypes = [vp]
         L.ctrfe_check_ids.argtypes = [vp, vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]

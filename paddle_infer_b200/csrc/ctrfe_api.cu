@@ -399,20 +399,26 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
 // One slot's host offsets -> 32-bit image, validated in the same pass: non-decreasing (framework
 // CheckLoD, lod_tensor.h:74-104), below 2^31, last offset inside the ids (or, dense rows, inside X:
 // sequence_pool_op.h:52-60).
+// (the narrowing loop has no loop-carried dependency besides an OR, so the AVX2 clone runs it eight
+// offsets at a time: a cfg2 batch has 320 K offsets and this pass sits on the host-buffer path)
+__attribute__((target_clones("avx2", "default")))
+uint64_t narrow_and_check(const uint64_t* lod, int64_t n, uint32_t* dst) {
+  uint64_t bad = 0;
+  dst[0] = static_cast<uint32_t>(lod[0]);
+  for (int64_t i = 1; i < n; ++i) {
+    bad |= static_cast<uint64_t>(lod[i] < lod[i - 1]);
+    dst[i] = static_cast<uint32_t>(lod[i]);
+  }
+  return bad;
+}
+
 int stage_one_lod(int s, const uint64_t* lod, int64_t n_seg, int64_t bound, bool has_ids, uint32_t* dst) {
   if (n_seg == 0) {
     dst[0] = lod ? static_cast<uint32_t>(lod[0]) : 0u;
     return CTRFE_OK;
   }
-  uint64_t prev = lod[0];
-  dst[0] = static_cast<uint32_t>(prev);
-  bool mono = true;
-  for (int64_t i = 1; i <= n_seg; ++i) {
-    const uint64_t v = lod[i];
-    mono &= v >= prev;
-    dst[i] = static_cast<uint32_t>(v);
-    prev = v;
-  }
+  const bool mono = narrow_and_check(lod, n_seg + 1, dst) == 0;
+  const uint64_t prev = lod[n_seg];
   if (!mono) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
   if (prev >= (1ull << 31))
     return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large (a slot holds fewer than 2^31 ids)", s,
@@ -619,6 +625,56 @@ int ctrfe_ctx_destroy(ctrfe_ctx* c) {
   if (c->err_dev) cudaFree(c->err_dev);
   if (c->err_host) cudaFreeHost(c->err_host);
   delete c;
+  return CTRFE_OK;
+}
+
+// ---- plain device / pinned memory, for host languages that bring no allocator of their own ----
+int ctrfe_malloc(int device, uint64_t bytes, void** ptr) {
+  if (!ptr) return fail(CTRFE_ERR_ARG, "malloc: null ptr");
+  *ptr = nullptr;
+  if (bytes == 0) return CTRFE_OK;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CTRFE_ERR_CUDA, "malloc: cannot select device %d", device);
+  CU(cudaMalloc(ptr, bytes));
+  return CTRFE_OK;
+}
+
+int ctrfe_free(int device, void* ptr) {
+  if (!ptr) return CTRFE_OK;
+  DeviceGuard g(device);
+  CU(cudaFree(ptr));
+  return CTRFE_OK;
+}
+
+int ctrfe_host_alloc(uint64_t bytes, void** ptr) {
+  if (!ptr) return fail(CTRFE_ERR_ARG, "host_alloc: null ptr");
+  *ptr = nullptr;
+  if (bytes == 0) return CTRFE_OK;
+  CU(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
+  return CTRFE_OK;
+}
+
+int ctrfe_host_free(void* ptr) {
+  if (!ptr) return CTRFE_OK;
+  CU(cudaFreeHost(ptr));
+  return CTRFE_OK;
+}
+
+int ctrfe_memcpy(int device, void* dst, const void* src, uint64_t bytes, int kind, void* stream, int wait) {
+  if (bytes == 0) return CTRFE_OK;
+  if (!dst || !src) return fail(CTRFE_ERR_ARG, "memcpy: null pointer");
+  if (kind < CTRFE_COPY_H2D || kind > CTRFE_COPY_D2D) return fail(CTRFE_ERR_ARG, "memcpy: bad kind %d", kind);
+  DeviceGuard g(device);
+  auto st = static_cast<cudaStream_t>(stream);
+  const cudaMemcpyKind k = kind == CTRFE_COPY_H2D ? cudaMemcpyHostToDevice : (kind == CTRFE_COPY_D2H ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice);
+  CU(cudaMemcpyAsync(dst, src, bytes, k, st));
+  if (wait) CU(cudaStreamSynchronize(st));
+  return CTRFE_OK;
+}
+
+int ctrfe_stream_synchronize(int device, void* stream) {
+  DeviceGuard g(device);
+  CU(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   return CTRFE_OK;
 }
 

@@ -2,7 +2,10 @@
 
 Same op names, argument names/meaning and error behaviour as the reference operators;
 each function marshals into the C ABI (include/ctrfe.h) and launches sm_100a kernels.
-torch is used only for what it is good at here: device memory and streams.
+The module itself needs numpy and the library only.  Arrays may be `device.DeviceArray`s (memory
+from the library's own allocator), anything with `__cuda_array_interface__`, or torch CUDA
+tensors -- torch is imported only when a torch tensor is passed in, and then outputs are torch
+tensors and launches go to torch's current stream.
 
     lookup_table_v2            paddle/fluid/operators/lookup_table_v2_op.cc:26-104
     sequence_pool              paddle/fluid/operators/sequence_ops/sequence_pool_op.{cc,h}
@@ -10,6 +13,7 @@ torch is used only for what it is good at here: device memory and streams.
     fused_seqpool_cvm          paddle/fluid/operators/fused/fused_seqpool_cvm_op.{cc,cu}
     fusion_seqpool_cvm_concat  paddle/fluid/operators/fused/fusion_seqpool_cvm_concat_op.cc
     fused_embedding_seq_pool   paddle/fluid/operators/fused/fused_embedding_seq_pool_op.{cc,h}
+    pull_box_sparse            paddle/fluid/operators/pull_box_sparse_op.{cc,h}
     ctr_fused_emb_seqpool_cvm  NEW: the whole front end in one launch (SURVEY.md section 8b,
                                route 1 -- Paddle's custom-op loader refuses to re-register a
                                built-in name, framework/custom_operator.cc:722-725)
@@ -20,16 +24,17 @@ LoD arguments are offset-based lists of levels, as LoDTensor::lod() returns them
 from __future__ import annotations
 
 import ctypes as C
+import sys
 from collections import namedtuple
 from typing import List, Optional, Sequence, Union
 
 import numpy as np
-import torch
 
 from . import _lib as B
+from .device import Arr, DeviceArray, PinnedArray, as_arr, empty, is_torch, stream_of
 
-_DT = {torch.float32: B.F32, torch.float16: B.F16, torch.bfloat16: B.BF16, torch.float64: B.F64}
-_IDT = {torch.int64: B.I64, torch.int32: B.I32}
+_FLOATS = ("float32", "float16", "bfloat16")
+_IDS = {"int64": B.I64, "int32": B.I32}
 
 
 class InvalidArgument(ValueError):
@@ -43,26 +48,60 @@ class Unimplemented(NotImplementedError):
 # ------------------------------------------------------------------------------------------
 # context plumbing
 # ------------------------------------------------------------------------------------------
-class Context:
-    """One ctrfe_ctx per CUDA device (pinned staging ring, device scratch, bad-id flag)."""
+def _device_index(device) -> int:
+    if device is None:
+        if "torch" in sys.modules:
+            import torch
+            if torch.cuda.is_available():
+                return torch.cuda.current_device()
+        return 0
+    if isinstance(device, int):
+        return device
+    idx = getattr(device, "index", None)  # a torch.device
+    if idx is None and "torch" in sys.modules:
+        import torch
+        idx = torch.device(device).index
+        if idx is None:
+            idx = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    return int(idx or 0)
 
-    def __init__(self, device: Union[int, torch.device, None] = None):
-        if not torch.cuda.is_available():
-            raise RuntimeError("paddle_infer_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
-        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        if dev.index is None:
-            dev = torch.device("cuda", torch.cuda.current_device())
-        self.device = dev
+
+class Context:
+    """One ctrfe_ctx per CUDA device (pinned staging ring, device scratch, error records).  Used with
+    ONE stream at a time: torch's current stream when torch is in the process, else `stream_handle`
+    (the legacy default stream unless set)."""
+
+    def __init__(self, device=None):
+        idx = _device_index(device)
+        self.device_index = idx
+        self.stream_handle: Optional[int] = None
         h = C.c_void_p()
-        B.check(B.lib().ctrfe_ctx_create(dev.index, C.byref(h)))
+        rc = B.lib().ctrfe_ctx_create(idx, C.byref(h))
+        if rc != B.OK:
+            raise RuntimeError("paddle_infer_b200 needs a CUDA device (sm_100a); there is no CPU fallback: "
+                               + B.lib().ctrfe_last_error().decode("utf-8", "replace"))
         self.handle = h
 
+    @property
+    def device(self):
+        import torch
+        return torch.device("cuda", self.device_index)
+
     def stream(self) -> int:
-        return torch.cuda.current_stream(self.device).cuda_stream
+        if self.stream_handle is not None:
+            return self.stream_handle
+        if "torch" in sys.modules:
+            import torch
+            return torch.cuda.current_stream(self.device_index).cuda_stream
+        return 0
+
+    def synchronize(self) -> None:
+        B.check(B.lib().ctrfe_stream_synchronize(self.device_index, self.stream()))
 
     def check_ids(self) -> None:
         """Raise BadIdError if any launch since the last check met an id outside the table
-        (what EmbeddingCPUFunctor enforces, phi/kernels/cpu/embedding_kernel.cc:59-76)."""
+        (what EmbeddingCPUFunctor enforces, phi/kernels/cpu/embedding_kernel.cc:59-76), or
+        InvalidArgument if a kernel met a malformed device-resident LoD."""
         s, p, i = C.c_int64(-1), C.c_int64(-1), C.c_int64(-1)
         rc = B.lib().ctrfe_check_ids(self.handle, self.stream(), C.byref(s), C.byref(p), C.byref(i))
         if rc == B.ERR_BAD_ID:
@@ -87,17 +126,10 @@ _ctxs = {}
 
 
 def default_context(device=None) -> Context:
-    idx = torch.cuda.current_device() if device is None else torch.device(device).index
-    if idx is None:
-        idx = torch.cuda.current_device()
+    idx = _device_index(device)
     if idx not in _ctxs:
-        _ctxs[idx] = Context(torch.device("cuda", idx))
+        _ctxs[idx] = Context(idx)
     return _ctxs[idx]
-
-
-def _need_cuda(t: torch.Tensor, name: str) -> None:
-    if not t.is_cuda:
-        raise RuntimeError(f"{name} must live on the GPU: this op has no CPU kernel (no CPU fallback)")
 
 
 def _last_level(lod, name="X") -> List[int]:
@@ -117,30 +149,42 @@ def _lod_np(level: Sequence[int]) -> np.ndarray:
     return a
 
 
+def _float_arr(x, name, allow64=False) -> Arr:
+    a = as_arr(x, name)
+    if a.dtype not in _FLOATS and not (allow64 and a.dtype == "float64"):
+        raise Unimplemented(f"{name}: dtype {a.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    return a
+
+
+def _ids_arr(x, name="Ids") -> Arr:
+    a = as_arr(x, name)
+    if a.dtype not in _IDS:
+        raise Unimplemented("emebdding input only support int32 and int64")
+    return a
+
+
 # ------------------------------------------------------------------------------------------
 # lookup_table_v2
 # ------------------------------------------------------------------------------------------
-def lookup_table_v2(W: torch.Tensor, Ids: torch.Tensor, padding_idx: int = -1, *, check: bool = True,
-                    ctx: Optional[Context] = None) -> torch.Tensor:
+def lookup_table_v2(W, Ids, padding_idx: int = -1, *, check: bool = True, ctx: Optional[Context] = None):
     """Out = W[Ids] with a zero row where Ids == padding_idx; Out.shape = Ids.shape + [D]
     (lookup_table_v2_op.cc:45-66).  Out shares Ids' LoD (the caller keeps carrying it).
     check=True synchronises and raises BadIdError for ids outside [0, N), as the reference
     CPU kernel does; pass check=False in a serving loop and call ctx.check_ids() at will."""
-    _need_cuda(W, "W"), _need_cuda(Ids, "Ids")
-    if W.dim() != 2:
+    w, ids = as_arr(W, "W"), as_arr(Ids, "Ids")
+    if len(w.shape) != 2:
         raise InvalidArgument(f"ShapeError: The dimensions of the 'lookup table' must be 2. But received "
-                              f"lookup table's dimensions = {W.dim()}.")
-    if Ids.dtype not in _IDT:
+                              f"lookup table's dimensions = {len(w.shape)}.")
+    if ids.dtype not in _IDS:
         raise Unimplemented("emebdding input only support int32 and int64")
-    ctx = ctx or default_context(W.device)
-    W = W.contiguous()
-    ids = Ids.contiguous()
-    out = torch.empty(tuple(Ids.shape) + (W.shape[1],), dtype=W.dtype, device=W.device)
-    B.check(B.lib().ctrfe_embedding(ctx.handle, W.data_ptr(), W.shape[0], W.shape[1] * W.element_size(),
-                                    ids.data_ptr(), _IDT[ids.dtype], ids.numel(), int(padding_idx),
-                                    out.data_ptr(), ctx.stream()))
+    ctx = ctx or default_context(w.device)
+    out, o = empty(ids.shape + (w.shape[1],), w.dtype, w)
+    B.check(B.lib().ctrfe_embedding(ctx.handle, w.ptr, w.shape[0], w.shape[1] * w.itemsize, ids.ptr, _IDS[ids.dtype],
+                                    ids.numel, int(padding_idx), o.ptr, ctx.stream()))
     if check:
         ctx.check_ids()
+    else:
+        ctx._keep = (w.obj, ids.obj)
     return out
 
 
@@ -150,38 +194,38 @@ def lookup_table_v2(W: torch.Tensor, Ids: torch.Tensor, padding_idx: int = -1, *
 SeqPoolOut = namedtuple("SeqPoolOut", ["Out", "MaxIndex", "lod"])
 
 
-def sequence_pool(X: torch.Tensor, lod, pooltype: str = "AVERAGE", pad_value: float = 0.0,
-                  is_test: bool = False, *, ctx: Optional[Context] = None) -> SeqPoolOut:
+def sequence_pool(X, lod, pooltype: str = "AVERAGE", pad_value: float = 0.0, is_test: bool = False, *,
+                  ctx: Optional[Context] = None) -> SeqPoolOut:
     """Pools each sequence of the LAST LoD level of X ([K, ...]) into one row.
     Out: [num_seq, ...]; Out's LoD is lod[0] when X has two levels, else none
     (sequence_pool_op.h:42-72).  MaxIndex (int32, Out's shape) is produced for MAX unless
     is_test (the reference skips it for is_test on CPU, sequence_pool_op.h:79-87).
     Empty sequences yield pad_value."""
-    _need_cuda(X, "X")
+    x = as_arr(X, "X")
     if pooltype not in B.POOLTYPES:
         raise InvalidArgument(f"unsupported pooling pooltype: {pooltype}. Only support \"AVERAGE\", \"SUM\", "
                               "\"SQRT\", \"LAST\", \"FIRST\" and \"MAX\"")
-    if X.dtype not in (torch.float32, torch.float16, torch.bfloat16):
-        raise Unimplemented(f"sequence_pool: dtype {X.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
+    if x.dtype not in _FLOATS:
+        raise Unimplemented(f"sequence_pool: dtype {x.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
     last = _last_level(lod)
     n_seq = len(last) - 1
-    if X.shape[0] < n_seq:
+    if x.shape[0] < n_seq:
         raise InvalidArgument("The first dimension of Input(X) must be large than batch size."
-                              f"But received first dimension of Input(X) is {X.shape[0]}, while batch"
+                              f"But received first dimension of Input(X) is {x.shape[0]}, while batch"
                               f"size is {n_seq}.")
-    if last[-1] > X.shape[0]:
+    if last[-1] > x.shape[0]:
         raise InvalidArgument(f"The last LoD offset ({last[-1]}) exceeds the first dimension of Input(X) "
-                              f"({X.shape[0]}).")
-    ctx = ctx or default_context(X.device)
-    X = X.contiguous()
-    width = int(np.prod(X.shape[1:])) if X.dim() > 1 else 1
-    out = torch.empty((n_seq,) + tuple(X.shape[1:]), dtype=X.dtype, device=X.device)
+                              f"({x.shape[0]}).")
+    ctx = ctx or default_context(x.device)
+    width = int(np.prod(x.shape[1:])) if len(x.shape) > 1 else 1
+    out, o = empty((n_seq,) + x.shape[1:], x.dtype, x)
     want_index = pooltype == "MAX" and not is_test
-    index = torch.empty(out.shape, dtype=torch.int32, device=X.device) if want_index else None
+    index, ix = empty(o.shape, "int32", x) if want_index else (None, None)
     lod_a = _lod_np(last)
-    B.check(B.lib().ctrfe_sequence_pool(ctx.handle, X.data_ptr(), _DT[X.dtype], width, lod_a.ctypes.data, n_seq,
-                                        B.POOLTYPES[pooltype], float(pad_value), out.data_ptr(),
-                                        index.data_ptr() if want_index else None, ctx.stream()))
+    B.check(B.lib().ctrfe_sequence_pool(ctx.handle, x.ptr, x.code, width, lod_a.ctypes.data, n_seq,
+                                        B.POOLTYPES[pooltype], float(pad_value), o.ptr,
+                                        ix.ptr if want_index else None, ctx.stream()))
+    ctx._keep = (x.obj,)
     out_lod = [list(lod[0])] if len(lod) == 2 else []
     return SeqPoolOut(out, index, out_lod)
 
@@ -189,108 +233,104 @@ def sequence_pool(X: torch.Tensor, lod, pooltype: str = "AVERAGE", pad_value: fl
 # ------------------------------------------------------------------------------------------
 # cvm
 # ------------------------------------------------------------------------------------------
-def cvm(X: torch.Tensor, CVM: Optional[torch.Tensor] = None, use_cvm: bool = True, *,
-        ctx: Optional[Context] = None) -> torch.Tensor:
+def cvm(X, CVM=None, use_cvm: bool = True, *, ctx: Optional[Context] = None):
     """Y[:,0] = log(X[:,0]+1), Y[:,1] = log(X[:,1]+1) - Y[:,0], rest copied (use_cvm=True);
     or X[:, 2:] (use_cvm=False).  X must be rank 2 (cvm_op.cc:34-38).  The CVM input is
     accepted for signature parity and, as in the reference forward, never read
-    (cvm_op.h:60-99).  Y shares X's LoD."""
-    _need_cuda(X, "X")
-    if X.dim() != 2:
-        raise InvalidArgument(f"Input(X)'s rank should be 2, but got {X.dim()}")
-    if X.dtype not in _DT:
-        raise Unimplemented(f"cvm: dtype {X.dtype} has no sm_100a kernel (float32/float64/float16/bfloat16)")
-    ctx = ctx or default_context(X.device)
-    X = X.contiguous()
-    rows, w = X.shape
+    (cvm_op.h:60-99).  Y shares X's LoD.  float32 / float64 / float16 / bfloat16."""
+    x = as_arr(X, "X")
+    if len(x.shape) != 2:
+        raise InvalidArgument(f"Input(X)'s rank should be 2, but got {len(x.shape)}")
+    if x.dtype not in _FLOATS + ("float64",):
+        raise Unimplemented(f"cvm: dtype {x.dtype} has no sm_100a kernel (float32/float64/float16/bfloat16)")
+    ctx = ctx or default_context(x.device)
+    rows, w = x.shape
     if w < 2:
         raise InvalidArgument("Input(X) of cvm needs at least the show and click columns")
-    y = torch.empty((rows, w if use_cvm else w - 2), dtype=X.dtype, device=X.device)
-    B.check(B.lib().ctrfe_cvm(ctx.handle, X.data_ptr(), _DT[X.dtype], rows, w, int(bool(use_cvm)), y.data_ptr(),
-                              ctx.stream()))
+    y, yo = empty((rows, w if use_cvm else w - 2), x.dtype, x)
+    B.check(B.lib().ctrfe_cvm(ctx.handle, x.ptr, x.code, rows, w, int(bool(use_cvm)), yo.ptr, ctx.stream()))
+    ctx._keep = (x.obj,)
     return y
 
 
 # ------------------------------------------------------------------------------------------
 # backward of the three ops (fp32; SURVEY 8(f) row 4 -- inference never calls these)
 # ------------------------------------------------------------------------------------------
-def _need_f32(t, name):
-    _need_cuda(t, name)
-    if t.dtype != torch.float32:
+def _f32(x, name) -> Arr:
+    a = as_arr(x, name)
+    if a.dtype != "float32":
         raise Unimplemented(f"{name}: the gradient kernels are float32 only")
-    return t.contiguous()
+    return a
 
 
-def sequence_pool_grad(OutGrad: torch.Tensor, lod, pooltype: str, x_rows: Optional[int] = None,
-                       MaxIndex: Optional[torch.Tensor] = None, *, ctx: Optional[Context] = None) -> torch.Tensor:
+def sequence_pool_grad(OutGrad, lod, pooltype: str, x_rows: Optional[int] = None, MaxIndex=None, *,
+                       ctx: Optional[Context] = None):
     """X@GRAD of sequence_pool (sequence_pool_op.h:99-121): [x_rows, ...] from Out@GRAD
     [num_seq, ...] and X's LoD; MAX needs the forward op's MaxIndex."""
     if pooltype not in B.POOLTYPES:
         raise InvalidArgument(f"unsupported pooling pooltype: {pooltype}")
-    g = _need_f32(OutGrad, "Out@GRAD")
+    g = _f32(OutGrad, "Out@GRAD")
     last = _last_level(lod)
     n_seq = len(last) - 1
     if g.shape[0] != n_seq:
         raise InvalidArgument(f"Out@GRAD has {g.shape[0]} rows, the LoD names {n_seq} sequences")
     rows = last[-1] if x_rows is None else int(x_rows)
-    width = int(np.prod(g.shape[1:])) if g.dim() > 1 else 1
+    width = int(np.prod(g.shape[1:])) if len(g.shape) > 1 else 1
     idx = None
     if pooltype == "MAX":
         if MaxIndex is None:
             raise InvalidArgument("sequence_pool_grad(MAX) needs MaxIndex")
-        _need_cuda(MaxIndex, "MaxIndex")
-        idx = MaxIndex.to(torch.int32).contiguous()
+        idx = as_arr(MaxIndex, "MaxIndex")
+        if idx.dtype != "int32":
+            raise InvalidArgument("MaxIndex must be int32")
     ctx = ctx or default_context(g.device)
-    dx = torch.empty((rows,) + tuple(g.shape[1:]), dtype=torch.float32, device=g.device)
+    dx, dxo = empty((rows,) + g.shape[1:], "float32", g)
     lod_a = _lod_np(last)
-    B.check(B.lib().ctrfe_sequence_pool_grad(ctx.handle, g.data_ptr(), width, lod_a.ctypes.data, n_seq, rows,
-                                             B.POOLTYPES[pooltype], idx.data_ptr() if idx is not None else None,
-                                             dx.data_ptr(), ctx.stream()))
+    B.check(B.lib().ctrfe_sequence_pool_grad(ctx.handle, g.ptr, width, lod_a.ctypes.data, n_seq, rows,
+                                             B.POOLTYPES[pooltype], idx.ptr if idx is not None else None,
+                                             dxo.ptr, ctx.stream()))
+    ctx._keep = (g.obj, idx.obj if idx is not None else None)
     return dx
 
 
-def cvm_grad(YGrad: torch.Tensor, CVM: torch.Tensor, use_cvm: bool = True, lod=None, *,
-             ctx: Optional[Context] = None) -> torch.Tensor:
+def cvm_grad(YGrad, CVM, use_cvm: bool = True, lod=None, *, ctx: Optional[Context] = None):
     """X@GRAD of cvm (cvm_op.h:100-140): columns 0-1 take the CVM input (show, click) of the row's
     sequence, the rest Y@GRAD.  lod: X's LoD when it has one (CVM then has one row per sequence),
     else None (one CVM row per row of X)."""
-    g = _need_f32(YGrad, "Y@GRAD")
-    c = _need_f32(CVM, "CVM")
-    if g.dim() != 2 or c.dim() != 2 or c.shape[1] != 2:
+    g, c = _f32(YGrad, "Y@GRAD"), _f32(CVM, "CVM")
+    if len(g.shape) != 2 or len(c.shape) != 2 or c.shape[1] != 2:
         raise InvalidArgument("Y@GRAD must be rank 2 and CVM [n, 2]")
     rows = g.shape[0]
     w = g.shape[1] + (0 if use_cvm else 2)
     ctx = ctx or default_context(g.device)
-    dx = torch.empty((rows, w), dtype=torch.float32, device=g.device)
+    dx, dxo = empty((rows, w), "float32", g)
     lod_a = None
     if lod is not None and len(lod) > 0:
         lod_a = _lod_np(lod[0] if isinstance(lod[0], (list, tuple, np.ndarray)) else lod)
         if lod_a.size - 1 != c.shape[0]:
             raise InvalidArgument("CVM needs one row per sequence of X")
-    B.check(B.lib().ctrfe_cvm_grad(ctx.handle, g.data_ptr(), c.data_ptr(), lod_a.ctypes.data if lod_a is not None else None,
-                                   c.shape[0], rows, w, int(bool(use_cvm)), dx.data_ptr(), ctx.stream()))
+    B.check(B.lib().ctrfe_cvm_grad(ctx.handle, g.ptr, c.ptr, lod_a.ctypes.data if lod_a is not None else None,
+                                   c.shape[0], rows, w, int(bool(use_cvm)), dxo.ptr, ctx.stream()))
+    ctx._keep = (g.obj, c.obj)
     return dx
 
 
-def lookup_table_v2_grad(OutGrad: torch.Tensor, Ids: torch.Tensor, table_rows: int, padding_idx: int = -1, *,
-                         check: bool = True, ctx: Optional[Context] = None) -> torch.Tensor:
+def lookup_table_v2_grad(OutGrad, Ids, table_rows: int, padding_idx: int = -1, *, check: bool = True,
+                         ctx: Optional[Context] = None):
     """Dense W@GRAD of lookup_table_v2 (phi embedding_grad): [table_rows, D]; rows of ids equal to
     padding_idx get no gradient.  Atomic adds: equal to the CPU kernel up to rounding."""
-    g = _need_f32(OutGrad, "Out@GRAD")
-    _need_cuda(Ids, "Ids")
-    if Ids.dtype not in _IDT:
-        raise Unimplemented("emebdding input only support int32 and int64")
-    ids = Ids.contiguous().view(-1)
+    g, ids = _f32(OutGrad, "Out@GRAD"), _ids_arr(Ids)
     d = g.shape[-1]
-    g2 = g.view(-1, d)
-    if g2.shape[0] != ids.numel():
+    if g.numel // d != ids.numel:
         raise InvalidArgument("Out@GRAD must have one row per id")
     ctx = ctx or default_context(g.device)
-    dw = torch.empty((table_rows, d), dtype=torch.float32, device=g.device)
-    B.check(B.lib().ctrfe_embedding_grad(ctx.handle, g2.data_ptr(), ids.data_ptr(), _IDT[ids.dtype], ids.numel(),
-                                         table_rows, d, int(padding_idx), dw.data_ptr(), ctx.stream()))
+    dw, dwo = empty((table_rows, d), "float32", g)
+    B.check(B.lib().ctrfe_embedding_grad(ctx.handle, g.ptr, ids.ptr, _IDS[ids.dtype], ids.numel,
+                                         table_rows, d, int(padding_idx), dwo.ptr, ctx.stream()))
     if check:
         ctx.check_ids()
+    else:
+        ctx._keep = (g.obj, ids.obj)
     return dw
 
 
@@ -303,7 +343,7 @@ def _as_list(x, n):
 
 class FusedPlan:
     """A prepared batch: descriptors + LoD resident on the device; launch() enqueues ONE
-    kernel for all slots.  Keeps the tensors it names alive."""
+    kernel for all slots.  Keeps the arrays it names alive."""
 
     def __init__(self, ctx: Context, handle, outs, keep):
         self.ctx, self.handle, self.outs, self._keep = ctx, handle, outs, keep
@@ -322,6 +362,13 @@ class FusedPlan:
     def kernel_names(self) -> List[str]:
         return [B.lib().ctrfe_plan_kernel_name(self.handle, i).decode() for i in range(self.num_kernels())]
 
+    def update_lod(self, lods: Sequence) -> None:
+        """New host LoD offsets for the plan's slots (same sequence counts); they reach the device
+        with the next launch_many(..., upload_lod=True)."""
+        arrs = [_lod_np(l) for l in lods]
+        ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+        B.check(B.lib().ctrfe_plan_update_lod(self.handle, ptrs))
+
     def close(self):
         if self.handle:
             B.lib().ctrfe_plan_destroy(self.handle)
@@ -334,28 +381,30 @@ class FusedPlan:
             pass
 
 
-def launch_many(plans: Sequence[FusedPlan], overlap_previous: bool = False) -> None:
+def launch_many(plans: Sequence[FusedPlan], overlap_previous: bool = False, upload_lod: bool = False) -> None:
     """Launch several prepared batches back to back with ONE call into the library
     (ctrfe_plan_launch_many): the inner step of a serving loop without a Python call per batch."""
     if not plans:
         return
     arr = (C.c_void_p * len(plans))(*[p.handle.value for p in plans])
-    B.check(B.lib().ctrfe_plan_launch_many(arr, len(plans), plans[0].ctx.stream(),
-                                           B.LAUNCH_OVERLAP_PREVIOUS if overlap_previous else 0))
+    flags = (B.LAUNCH_OVERLAP_PREVIOUS if overlap_previous else 0) | (B.LAUNCH_UPLOAD_LOD if upload_lod else 0)
+    B.check(B.lib().ctrfe_plan_launch_many(arr, len(plans), plans[0].ctx.stream(), flags))
 
 
 class _TableRef:
     """What a slot descriptor needs from a table: a base pointer and a row count."""
 
     def __init__(self, ptr, rows):
-        self._ptr, self.shape = ptr, (rows,)
-
-    def data_ptr(self):
-        return self._ptr
+        self.ptr, self.shape = ptr, (rows,)
 
 
-def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_value, padding_idx, cvm_mode,
+def _is_host_lod(l) -> bool:
+    return isinstance(l, (list, tuple, np.ndarray))
+
+
+def _build_desc(tables, ids, lods, pooltypes, out_ptrs, out_ld, *, dim, dtype_code, pad_value, padding_idx, cvm_mode,
                 cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None, keymap=None):
+    """tables: Arr / _TableRef per slot; ids: Arr or None per slot; lods: host sequences or device Arrs."""
     S = len(lods)
     slots = (B.Slot * S)()
     keep = []
@@ -364,17 +413,19 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
     for s in range(S):
         t = tables[s]
         if lod_on_device:
-            lod_ptr, n_seg = lods[s].data_ptr(), lods[s].numel() - 1
-            keep.append(lods[s])
+            la = as_arr(lods[s], "lod")
+            lod_ptr, n_seg = la.ptr, la.numel - 1
+            keep.append(la.obj)
         else:
             a = _lod_np(lods[s])
             keep.append(a)
             lod_ptr, n_seg = a.ctypes.data, a.size - 1
         i = ids[s]
-        slots[s] = B.Slot(t.data_ptr(), t.shape[0], i.data_ptr() if i is not None else None, lod_ptr, n_seg,
-                          outs[s].data_ptr(), out_ld, B.POOLTYPES[pooltypes[s]],
-                          _IDT[i.dtype] if i is not None else B.I64, i.numel() if i is not None else 0)
-    desc = B.FusedDesc(S, dtype, slots, dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset, scale_mode,
+        slots[s] = B.Slot(t.ptr, t.shape[0], i.ptr if i is not None else None, lod_ptr, n_seg,
+                          out_ptrs[s], out_ld, B.POOLTYPES[pooltypes[s]],
+                          _IDS[i.dtype] if i is not None else B.I64, i.numel if i is not None else 0)
+        keep.append((getattr(t, "obj", None), i.obj if i is not None else None))
+    desc = B.FusedDesc(S, dtype_code, slots, dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset, scale_mode,
                        init_mode, B.LOD_DEVICE if lod_on_device else B.LOD_HOST, 0)
     if sharded is not None:
         desc.n_shards = sharded.n_shards
@@ -391,12 +442,22 @@ def _build_desc(tables, ids, lods, pooltypes, outs, out_ld, *, dim, dtype, pad_v
     return desc, keep
 
 
-def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, pooltype="SUM", *,
+def _is_sharded(W) -> bool:
+    return hasattr(W, "shard_ptrs") and hasattr(W, "n_shards")
+
+
+def _sharded_like(W) -> Arr:
+    """An Arr standing for a sharded table's element type and device (outputs are allocated like it)."""
+    import torch
+    t0 = torch.empty((0, W.dim), dtype=W.dtype, device=W.device)
+    return Arr(0, (W.n_rows, W.dim), str(W.dtype).replace("torch.", ""), t0.device.index, "torch", t0)
+
+
+def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence, lods: Sequence, pooltype="SUM", *,
                               pad_value: float = 0.0, padding_idx: int = -1, use_cvm: Optional[bool] = True,
                               cvm_offset: int = 2, concat: bool = False, scale_mode: int = B.SCALE_DIVIDE,
                               init_mode: int = B.INIT_ZERO, check: bool = True, plan_only: bool = False,
-                              out: Optional[torch.Tensor] = None, ctx: Optional[Context] = None,
-                              keymap: Optional["KeyMap"] = None):
+                              out=None, ctx: Optional[Context] = None, keymap: Optional["KeyMap"] = None):
     """lookup_table_v2 -> sequence_pool -> cvm for every slot of a CTR batch in one launch.
 
     W         one table [N, D] shared by all slots, or a list with one table per slot, or a
@@ -404,73 +465,75 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence[torch.Tensor], lods: Sequence, po
               remote rows the kernel fetches itself over NVLink (results are bit-identical)
     Ids       per slot: 1-D int64/int32 ids, LoD-packed
     lods      per slot: offsets of the last LoD level -- a host sequence / numpy array, or a
-              CUDA uint64-as-int64 tensor when the offsets are already on the device
+              device uint64-as-int64 array when the offsets are already on the device (then the
+              kernels check every pair they read, see ctx.check_ids)
     pooltype  one name or one per slot
     use_cvm   True: cvm(use_cvm=True); False: cvm(use_cvm=False) (drops cvm_offset columns);
               None: no cvm op after the pool
-    concat    write all slots into one [B, S*D_out] tensor (concat(axis=1) fused, as
+    concat    write all slots into one [B, S*D_out] array (concat(axis=1) fused, as
               fusion_seqpool_cvm_concat does)
     keymap    a KeyMap: Ids are then uint64 feasign keys (viewed as int64, as pull_box_sparse
               takes them) and W holds one row per key of the map; key 0 and unknown keys pool
               as zero rows
-    Returns a list of [B_s, D_out] tensors, or the [B, S*D_out] tensor when concat=True;
+    Returns a list of [B_s, D_out] arrays, or the [B, S*D_out] array when concat=True;
     with plan_only=True returns a FusedPlan instead (nothing launched yet).
     """
-    from .shard import LocalShards, ShardedTable
     S = len(Ids)
-    sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
+    sharded = W if _is_sharded(W) else None
     pools = _as_list(pooltype, S)
     for p in pools:
         if p not in B.POOLTYPES:
             raise InvalidArgument(f"unsupported pooling pooltype: {p}")
     if sharded is not None:
-        # W is one logical table row-sharded over the GPUs of the box (shard.py)
-        tables = []
-        t0 = torch.empty((0, sharded.dim), dtype=sharded.dtype, device=sharded.device)
+        tables: List = []
+        t0 = _sharded_like(sharded)
     else:
-        tables = _as_list(W, S)
-        if len(tables) != S:
+        tl = _as_list(W, S)
+        if len(tl) != S:
             raise InvalidArgument("W must be one table or one per slot")
+        tables = [as_arr(t, "W") for t in tl]
         t0 = tables[0]
-    _need_cuda(t0, "W")
-    if t0.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+    if t0.dtype not in _FLOATS:
         raise Unimplemented(f"dtype {t0.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
     dim = t0.shape[1]
     for t in tables:
-        if t.dim() != 2 or t.shape[1] != dim or t.dtype != t0.dtype or not t.is_contiguous():
+        if len(t.shape) != 2 or t.shape[1] != dim or t.dtype != t0.dtype:
             raise InvalidArgument("all tables must be contiguous [N, D] with equal D and dtype")
-    for i in Ids:
-        _need_cuda(i, "Ids")
-        if i.dtype not in _IDT:
-            raise Unimplemented("emebdding input only support int32 and int64")
+    ids_a = [_ids_arr(i) for i in Ids]
     ctx = ctx or default_context(t0.device)
     cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
     d_out = dim - cvm_offset if cvm_mode == B.CVM_STRIP else dim
-    lod_on_device = isinstance(lods[0], torch.Tensor)
-    n_segs = [(l.numel() if lod_on_device else len(l)) - 1 for l in lods]
-    ids_c = [i.contiguous().view(-1) for i in Ids]
+    lod_on_device = not _is_host_lod(lods[0])
+    n_segs = [(as_arr(l, "lod").numel if lod_on_device else len(l)) - 1 for l in lods]
+    es = t0.itemsize
     if concat:
         if len(set(n_segs)) != 1:
             raise InvalidArgument("Batchsize of all inputs should be equal.")
         if out is None:
-            out = torch.empty((n_segs[0], S * d_out), dtype=t0.dtype, device=t0.device)
-        outs = [out[:, s * d_out:(s + 1) * d_out] for s in range(S)]
+            out, oa = empty((n_segs[0], S * d_out), t0.dtype, t0)
+        else:
+            oa = as_arr(out, "out")
+        out_ptrs = [oa.ptr + s * d_out * es for s in range(S)]
         ld = S * d_out
+        result = out
     else:
-        outs = [torch.empty((n, d_out), dtype=t0.dtype, device=t0.device) for n in n_segs]
+        pairs = [empty((n, d_out), t0.dtype, t0) for n in n_segs]
+        out_ptrs = [a.ptr for _, a in pairs]
         ld = d_out
-    desc, keep = _build_desc(tables, ids_c, lods, pools, outs, ld, dim=dim, dtype=_DT[t0.dtype],
+        result = [o for o, _ in pairs]
+    desc, keep = _build_desc(tables, ids_a, lods, pools, out_ptrs, ld, dim=dim, dtype_code=t0.code,
                              pad_value=pad_value, padding_idx=padding_idx, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
                              scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device, sharded=sharded,
                              keymap=keymap)
-    result = out if concat else outs
     if plan_only:
         h = C.c_void_p()
         B.check(B.lib().ctrfe_plan_create(ctx.handle, C.byref(desc), ctx.stream(), C.byref(h)))
-        return FusedPlan(ctx, h, result, (tables, ids_c, outs, out, keep))
+        return FusedPlan(ctx, h, result, (keep, result))
     B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
     if check:
         ctx.check_ids()
+    else:
+        ctx._keep = keep
     return result
 
 
@@ -478,51 +541,55 @@ class KeyMap:
     """uint64 feasign key -> table row, resident on the GPU (ctrfe_keymap): the lookup half of
     the reference's per-GPU HashTable (framework/fleet/heter_ps/hashtable_kernel.cu), which
     pull_box_sparse / pull_gpups_sparse consult.  keys[i] maps to row i of the value table the
-    caller keeps beside it; keys must be distinct and non-zero (0 is the padding feasign)."""
+    caller keeps beside it; keys are non-zero (0 is the padding feasign); of duplicate keys the
+    first occurrence wins."""
 
-    def __init__(self, keys: torch.Tensor, ctx: Optional[Context] = None):
-        _need_cuda(keys, "keys")
-        if keys.dtype != torch.int64:
-            raise InvalidArgument("feasign keys are uint64 values held in an int64 tensor")
-        keys = keys.contiguous().view(-1)
-        n = keys.numel()
-        ctx = ctx or default_context(keys.device)
+    def __init__(self, keys, ctx: Optional[Context] = None):
+        k = as_arr(keys, "keys")
+        if k.dtype != "int64":
+            raise InvalidArgument("feasign keys are uint64 values held in an int64 array")
+        n = k.numel
+        ctx = ctx or default_context(k.device)
         log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.0))))  # load factor <= 0.5
         while True:
             if log2 > 31:
                 raise InvalidArgument("too many keys for one key map")
-            self.keys = torch.zeros(1 << log2, dtype=torch.int64, device=keys.device)
-            self.rows = torch.zeros(1 << log2, dtype=torch.int32, device=keys.device)
-            unplaced = torch.zeros(1, dtype=torch.int32, device=keys.device)
-            B.check(B.lib().ctrfe_keymap_build(ctx.handle, keys.data_ptr(), n, self.keys.data_ptr(), self.rows.data_ptr(),
-                                               log2, unplaced.data_ptr(), ctx.stream()))
-            if int(unplaced.item()) == 0:
+            self.keys = DeviceArray((1 << log2,), "int64", k.device)
+            self.rows = DeviceArray((1 << log2,), "int32", k.device)
+            unplaced = DeviceArray((1,), "int32", k.device)
+            zero = np.zeros(1 << log2, np.int64)
+            self.keys.fill_bytes_from(zero, ctx.stream())
+            unplaced.fill_bytes_from(np.zeros(1, np.int32), ctx.stream())
+            B.check(B.lib().ctrfe_keymap_build(ctx.handle, k.ptr, n, self.keys.ptr, self.rows.ptr,
+                                               log2, unplaced.ptr, ctx.stream()))
+            if int(unplaced.numpy(ctx.stream())[0]) == 0:
                 break
             log2 += 1  # a probe chain longer than the kernel follows: spread the keys out
         self.log2_slots, self.n_keys = log2, n
-        self.struct = B.KeyMap(self.keys.data_ptr(), self.rows.data_ptr(), log2, 0, n)
+        self.struct = B.KeyMap(self.keys.ptr, self.rows.ptr, log2, 0, n)
 
 
-def pull_box_sparse(keymap: KeyMap, W: torch.Tensor, Ids: Sequence[torch.Tensor], *,
-                    ctx: Optional[Context] = None) -> List[torch.Tensor]:
+def pull_box_sparse(keymap: KeyMap, W, Ids: Sequence, *, ctx: Optional[Context] = None) -> List:
     """pull_box_sparse / pull_gpups_sparse over a resident table (operators/pull_box_sparse_op.h:
     32-62, .cc:62-100): per slot, Ids [K_s(, 1)] uint64 feasign keys -> Out [K_s, D] with
     D = W.shape[1] (the op's `size`); key 0 and unknown keys give zero rows.  One launch for all
     slots.  The fused call (ctr_fused_emb_seqpool_cvm(..., keymap=...)) never writes these
     values; this clone exists for programs that consume them elsewhere."""
-    flat = [i.contiguous().view(-1) for i in Ids]
-    lods = [torch.arange(i.numel() + 1, dtype=torch.int64, device=i.device) for i in flat]
-    outs = ctr_fused_emb_seqpool_cvm(W, flat, lods, "FIRST", use_cvm=None, keymap=keymap, ctx=ctx, check=False)
-    return [o.view(*i.shape[:1], W.shape[1]) for o, i in zip(outs, flat)]
+    flat = [as_arr(i, "Ids") for i in Ids]
+    lods = [np.arange(i.numel + 1, dtype=np.uint64) for i in flat]
+    flat1 = [Arr(i.ptr, (i.numel,), i.dtype, i.device, i.kind, i.obj) for i in flat]
+    return ctr_fused_emb_seqpool_cvm(W, flat1, lods, "FIRST", use_cvm=None, keymap=keymap, ctx=ctx, check=True)
 
 
 def _dense_slots(Xs, lods):
+    flat = []
     for x in Xs:
-        _need_cuda(x, "X")
-    w = Xs[0].shape[1] if Xs[0].dim() == 2 else int(np.prod(Xs[0].shape[1:]))
-    flat = [x.contiguous().view(x.shape[0], -1) for x in Xs]
+        a = _float_arr(x, "X")
+        w = a.shape[1] if len(a.shape) == 2 else int(np.prod(a.shape[1:]))
+        flat.append(Arr(a.ptr, (a.shape[0], w), a.dtype, a.device, a.kind, a.obj))
+    w = flat[0].shape[1] if flat else 0
     for f in flat:
-        if f.shape[1] != w:
+        if f.shape[1] != w or f.dtype != flat[0].dtype:
             raise InvalidArgument("Width of all inputs should be equal.")
     lasts = [_last_level(l) for l in lods]
     for f, l in zip(flat, lasts):
@@ -531,36 +598,33 @@ def _dense_slots(Xs, lods):
     return flat, lasts, w
 
 
-def fused_seqpool_cvm(X: Sequence[torch.Tensor], lods: Sequence, CVM: Optional[torch.Tensor] = None,
-                      pooltype: str = "SUM", pad_value: float = 0.0, use_cvm: bool = True, cvm_offset: int = 2,
-                      *, ctx: Optional[Context] = None) -> List[torch.Tensor]:
+def fused_seqpool_cvm(X: Sequence, lods: Sequence, CVM=None, pooltype: str = "SUM", pad_value: float = 0.0,
+                      use_cvm: bool = True, cvm_offset: int = 2, *, ctx: Optional[Context] = None) -> List:
     """PaddleBox's multi-slot op over PRE-PULLED values (fused/fused_seqpool_cvm_op.cc:120-150):
-    X is a list of [K_s, D] LoD tensors, one per slot; SUM only; the accumulator STARTS at
+    X is a list of [K_s, D] LoD arrays, one per slot; SUM only; the accumulator STARTS at
     pad_value (fused_seqpool_cvm_op.cu:49), so an empty sequence yields pad_value too;
     use_cvm=False drops cvm_offset leading columns.  One launch instead of the reference's
     two kernels + intermediate buffer."""
     if pooltype != "SUM":
         raise InvalidArgument("fused_seqpool_cvm only supports pooltype SUM")  # op maker InEnum({"SUM"})
-    flat, lasts, w = _dense_slots(X, lods)
-    if not flat:
+    if not X:
         return []
-    if flat[0].dtype not in (torch.float32, torch.float16, torch.bfloat16):
-        raise Unimplemented("fused_seqpool_cvm: float32/float16/bfloat16 only")
+    flat, lasts, w = _dense_slots(X, lods)
     ctx = ctx or default_context(flat[0].device)
     S = len(flat)
     cvm_mode = B.CVM_USE if use_cvm else B.CVM_STRIP
     d_out = w if use_cvm else w - cvm_offset
-    outs = [torch.empty((len(l) - 1, d_out), dtype=flat[0].dtype, device=flat[0].device) for l in lasts]
-    desc, keep = _build_desc(flat, [None] * S, lasts, ["SUM"] * S, outs, d_out, dim=w, dtype=_DT[flat[0].dtype],
-                             pad_value=pad_value, padding_idx=-1, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
-                             scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_PAD, lod_on_device=False)
+    pairs = [empty((len(l) - 1, d_out), flat[0].dtype, flat[0]) for l in lasts]
+    desc, keep = _build_desc(flat, [None] * S, lasts, ["SUM"] * S, [a.ptr for _, a in pairs], d_out, dim=w,
+                             dtype_code=flat[0].code, pad_value=pad_value, padding_idx=-1, cvm_mode=cvm_mode,
+                             cvm_offset=cvm_offset, scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_PAD, lod_on_device=False)
     B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
-    return outs
+    ctx._keep = keep
+    return [o for o, _ in pairs]
 
 
-def fusion_seqpool_cvm_concat(X: Sequence[torch.Tensor], lods: Sequence, CVM: Optional[torch.Tensor] = None,
-                              pooltype: str = "SUM", use_cvm: bool = True, axis: int = 1, *,
-                              ctx: Optional[Context] = None) -> torch.Tensor:
+def fusion_seqpool_cvm_concat(X: Sequence, lods: Sequence, CVM=None, pooltype: str = "SUM", use_cvm: bool = True,
+                              axis: int = 1, *, ctx: Optional[Context] = None):
     """The CPU predictor's fused op (fused/fusion_seqpool_cvm_concat_op.cc:97-159): per slot
     sequence_pool (SUM / AVERAGE / SQRT, jit kernel: scale by reciprocal) -> cvm(use_cvm=True)
     -> written at column s*w of Out [B, S*w].  axis must be 1, use_cvm must be True, as the
@@ -578,18 +642,18 @@ def fusion_seqpool_cvm_concat(X: Sequence[torch.Tensor], lods: Sequence, CVM: Op
         if len(l) - 1 != bs:
             raise InvalidArgument("Batchsize of all inputs should be equal.")
     ctx = ctx or default_context(flat[0].device)
-    out = torch.empty((bs, S * w), dtype=flat[0].dtype, device=flat[0].device)
-    outs = [out[:, s * w:(s + 1) * w] for s in range(S)]
-    desc, keep = _build_desc(flat, [None] * S, lasts, [pooltype] * S, outs, S * w, dim=w, dtype=_DT[flat[0].dtype],
-                             pad_value=0.0, padding_idx=-1, cvm_mode=B.CVM_USE, cvm_offset=2,
+    out, oa = empty((bs, S * w), flat[0].dtype, flat[0])
+    es = flat[0].itemsize
+    desc, keep = _build_desc(flat, [None] * S, lasts, [pooltype] * S, [oa.ptr + s * w * es for s in range(S)], S * w, dim=w,
+                             dtype_code=flat[0].code, pad_value=0.0, padding_idx=-1, cvm_mode=B.CVM_USE, cvm_offset=2,
                              scale_mode=B.SCALE_RECIPROCAL, init_mode=B.INIT_ZERO, lod_on_device=False)
     B.check(B.lib().ctrfe_fused_forward(ctx.handle, C.byref(desc), ctx.stream()))
+    ctx._keep = keep
     return out
 
 
-def fused_embedding_seq_pool(W: torch.Tensor, Ids: torch.Tensor, lod, combiner: str = "sum",
-                             padding_idx: int = -1, is_sparse: bool = False, *, check: bool = True,
-                             ctx: Optional[Context] = None) -> torch.Tensor:
+def fused_embedding_seq_pool(W, Ids, lod, combiner: str = "sum", padding_idx: int = -1, is_sparse: bool = False, *,
+                             check: bool = True, ctx: Optional[Context] = None):
     """Gather + SUM per sequence (fused/fused_embedding_seq_pool_op.h:84-127, the EmbSeqPool
     route: first row copied, the rest added in id order).  Ids: [K, idx_width] int64 with one LoD
     level over its rows; Out: [num_seq, D * idx_width], column j of Ids pooled into columns
@@ -598,30 +662,36 @@ def fused_embedding_seq_pool(W: torch.Tensor, Ids: torch.Tensor, lod, combiner: 
         raise Unimplemented("fused_embedding_seq_pool only supports combiner 'sum'")
     if len(lod) != 1:
         raise InvalidArgument("The LoD level of Input(Ids) should be 1.")
-    _need_cuda(W, "W"), _need_cuda(Ids, "Ids")
-    if W.dim() != 2 or Ids.dim() > 2:
+    w, ids = _float_arr(W, "W"), as_arr(Ids, "Ids")
+    if len(w.shape) != 2 or len(ids.shape) > 2:
         raise InvalidArgument("The dimension of W and Ids should be 2.")
-    if Ids.dtype != torch.int64:
+    if ids.dtype != "int64":
         raise Unimplemented("fused_embedding_seq_pool: Ids must be int64")
-    if W.dtype not in (torch.float32, torch.float16, torch.bfloat16):
-        raise Unimplemented(f"dtype {W.dtype} has no sm_100a kernel (float32/float16/bfloat16)")
-    ids2 = Ids.contiguous().view(Ids.shape[0], -1)
-    width = ids2.shape[1]
+    n_rows = ids.shape[0]
+    width = ids.numel // max(n_rows, 1) if n_rows else 1
     last = _lod_np(lod[0])
     n_seg = last.size - 1
-    if int(last[-1]) > ids2.shape[0]:
+    if int(last[-1]) > n_rows:
         raise InvalidArgument("The last LoD offset exceeds the first dimension of Input(Ids).")
-    ctx = ctx or default_context(W.device)
-    W = W.contiguous()
-    out = torch.empty((n_seg, W.shape[1] * width), dtype=W.dtype, device=W.device)
-    B.check(B.lib().ctrfe_fused_embedding_seq_pool(ctx.handle, W.data_ptr(), W.shape[0], W.shape[1], _DT[W.dtype],
-                                                   ids2.data_ptr(), ids2.shape[0], width, last.ctypes.data, n_seg,
-                                                   int(padding_idx), out.data_ptr(), ctx.stream()))
+    ctx = ctx or default_context(w.device)
+    out, oa = empty((n_seg, w.shape[1] * width), w.dtype, w)
+    B.check(B.lib().ctrfe_fused_embedding_seq_pool(ctx.handle, w.ptr, w.shape[0], w.shape[1], w.code, ids.ptr, n_rows, width,
+                                                   last.ctypes.data, n_seg, int(padding_idx), oa.ptr, ctx.stream()))
     if check:
         ctx.check_ids()
     else:
-        ctx._keep_alive = ids2  # the launch reads it asynchronously
+        ctx._keep = (w.obj, ids.obj)
     return out
+
+
+def _TORCH_DT():
+    import torch
+    return {torch.float32: B.F32, torch.float16: B.F16, torch.bfloat16: B.BF16, torch.float64: B.F64}
+
+
+def _TORCH_IDT():
+    import torch
+    return {torch.int64: B.I64, torch.int32: B.I32}
 
 
 # ------------------------------------------------------------------------------------------
@@ -648,16 +718,16 @@ class HostFrontEnd:
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
                  padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, mode: str = "zero_copy",
                  concat: bool = False, ctx: Optional[Context] = None):
-        from .shard import LocalShards, ShardedTable
-        self.sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
+        import torch
+        self.sharded = W if _is_sharded(W) else None
         if self.sharded is not None:  # one logical table row-sharded over the GPUs of the box
             t0 = torch.empty((0, W.dim), dtype=W.dtype, device=W.device)
             tables = [_TableRef(None, W.n_rows)] * n_slots
             self._dev = W.device
         else:
-            tables = _as_list(W, n_slots)
-            t0 = tables[0]
-            _need_cuda(t0, "W")
+            tl = _as_list(W, n_slots)
+            t0 = tl[0]
+            tables = [as_arr(t, "W") for t in tl]
             self._dev = t0.device
         if mode not in ("zero_copy", "copy"):
             raise InvalidArgument("mode must be 'zero_copy' or 'copy'")
@@ -674,6 +744,7 @@ class HostFrontEnd:
         if mode == "copy":
             self.dev_ids = [torch.empty(max_ids_per_slot, dtype=torch.int64, device=t0.device) for _ in range(n_slots)]
             self.dev_out = torch.empty(shape, dtype=t0.dtype, device=t0.device)
+            self.dev_out_cat = None if concat else torch.empty((batch, n_slots * self.d_out), dtype=t0.dtype, device=t0.device)
         self.h2d_bytes = 0
         self.d2h_bytes = self.host_out.numel() * self.host_out.element_size()
 
@@ -686,6 +757,7 @@ class HostFrontEnd:
         return [block[s] for s in range(self.S)], self.d_out
 
     def _desc(self, ids_host, lods_host):
+        import torch
         for t in list(ids_host) + list(lods_host):
             if not (isinstance(t, torch.Tensor) and t.is_pinned()):
                 raise InvalidArgument("zero_copy mode needs pinned host tensors for ids and LoD offsets")
@@ -696,10 +768,10 @@ class HostFrontEnd:
         slots = (B.Slot * S)()
         for s in range(S):
             t = self.tables[s]
-            slots[s] = B.Slot(t.data_ptr(), t.shape[0], ids_host[s].data_ptr(), lods_host[s].data_ptr(),
+            slots[s] = B.Slot(t.ptr, t.shape[0], ids_host[s].data_ptr(), lods_host[s].data_ptr(),
                               lods_host[s].numel() - 1, outs[s].data_ptr(), ld, B.POOLTYPES[self.pools[s]],
-                              _IDT[ids_host[s].dtype], ids_host[s].numel())
-        desc = B.FusedDesc(S, _DT[self._dtype], slots, self.dim, int(self.kw["padding_idx"]),
+                              _TORCH_IDT()[ids_host[s].dtype], ids_host[s].numel())
+        desc = B.FusedDesc(S, _TORCH_DT()[self._dtype], slots, self.dim, int(self.kw["padding_idx"]),
                            float(self.kw["pad_value"]), cvm_mode, self.kw["cvm_offset"], B.SCALE_DIVIDE,
                            B.INIT_ZERO, B.LOD_DEVICE, 0)
         if self.sharded is not None:
@@ -715,6 +787,7 @@ class HostFrontEnd:
         one kernel launch + one stream synchronise, whatever the buffers currently hold."""
         if self.mode != "zero_copy":
             raise InvalidArgument("bind() needs mode='zero_copy'")
+        import torch
         desc, slots, h2d = self._desc(ids_host, lods_host)
         h = C.c_void_p()
         stream = torch.cuda.current_stream(self._dev)
@@ -724,6 +797,7 @@ class HostFrontEnd:
     def run(self, ids_host: Sequence[torch.Tensor], lods_host: Sequence, check: bool = False):
         """ids_host: pinned int64/int32 CPU tensors, one per slot.  lods_host: per slot the
         offsets -- numpy uint64 arrays (mode="copy") or pinned int64 CPU tensors (zero_copy)."""
+        import torch
         S = self.S
         stream = torch.cuda.current_stream(self._dev)
         if self.mode == "copy":
@@ -732,14 +806,12 @@ class HostFrontEnd:
                 d = self.dev_ids[s][:ids_host[s].numel()]
                 d.copy_(ids_host[s], non_blocking=True)
                 ids_dev.append(d)
-            outs, ld = self._out_views(self.dev_out)
-            desc, keep = _build_desc(self.tables, ids_dev, lods_host, self.pools, outs, ld, dim=self.dim,
-                                     dtype=_DT[self._dtype], pad_value=self.kw["pad_value"],
-                                     padding_idx=self.kw["padding_idx"],
-                                     cvm_mode=B.CVM_NONE if self.kw["use_cvm"] is None else (B.CVM_USE if self.kw["use_cvm"] else B.CVM_STRIP),
-                                     cvm_offset=self.kw["cvm_offset"], scale_mode=B.SCALE_DIVIDE, init_mode=B.INIT_ZERO,
-                                     lod_on_device=False, sharded=self.sharded)
-            B.check(B.lib().ctrfe_fused_forward(self.ctx.handle, C.byref(desc), stream.cuda_stream))
+            ctr_fused_emb_seqpool_cvm(self.sharded if self.sharded is not None else [t.obj for t in self.tables], ids_dev, lods_host,
+                                      self.pools, pad_value=self.kw["pad_value"], padding_idx=self.kw["padding_idx"],
+                                      use_cvm=self.kw["use_cvm"], cvm_offset=self.kw["cvm_offset"], concat=True, check=False,
+                                      out=self.dev_out if self.concat else self.dev_out_cat, ctx=self.ctx)
+            if not self.concat:  # per-slot blocks: un-concatenate on the device
+                self.dev_out.copy_(self.dev_out_cat.view(self.B, S, self.d_out).permute(1, 0, 2))
             self.host_out.copy_(self.dev_out, non_blocking=True)
             self.h2d_bytes = sum(i.numel() * i.element_size() for i in ids_host) + sum(l.size * 8 for l in lods_host)
         else:
@@ -756,6 +828,7 @@ class BoundHostCall:
     """HostFrontEnd with its input buffers bound: run() = one launch + one synchronise."""
 
     def __init__(self, fe: HostFrontEnd, plan: FusedPlan, h2d_bytes: int):
+        import torch
         self.fe, self.plan, self.h2d_bytes, self.d2h_bytes = fe, plan, h2d_bytes, fe.d2h_bytes
         self._stream = torch.cuda.current_stream(fe._dev)
 
@@ -771,6 +844,7 @@ class BoundHostCall:
         request i+1 before waiting for request i, so the PCIe reads of one overlap the PCIe
         writes of the other; overlap_previous=True additionally lets the kernel start while the
         previous request's kernel drains (the requests are independent)."""
+        import torch
         self.plan.launch(overlap_previous)
         done = torch.cuda.Event()
         done.record(self._stream)
@@ -789,32 +863,31 @@ class HostPipe:
     (inference/api/details/zero_copy_tensor.cc) -- around the fused launch.  The slots are cut into
     `n_groups` groups and pipelined over both copy engines (group g goes up while group g-1 is
     pooled and group g-2's rows come down), so both directions of PCIe are busy at once; the LoD
-    offsets are validated on the host like any host LoD.  run() returns one [B, D_out] pinned host
-    view per slot (the op's Out@VECTOR)."""
+    offsets are validated on the host like any host LoD.  Needs no torch: ids are numpy arrays
+    (ideally views of `device.PinnedArray`s) or CPU tensors; run() returns one [B, D_out] numpy view
+    of the pinned output block per slot (torch views when W is a torch tensor)."""
 
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
                  padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, n_groups: int = 4,
-                 ids_dtype=torch.int64, ctx: Optional[Context] = None):
-        from .shard import LocalShards, ShardedTable
-        sharded = W if isinstance(W, (ShardedTable, LocalShards)) else None
+                 ids_dtype="int64", ctx: Optional[Context] = None):
+        sharded = W if _is_sharded(W) else None
         if sharded is not None:
-            t0 = torch.empty((0, W.dim), dtype=W.dtype, device=W.device)
+            t0 = _sharded_like(sharded)
             tables = [_TableRef(None, W.n_rows)] * n_slots
         else:
-            tables = _as_list(W, n_slots)
+            tables = [as_arr(t, "W") for t in _as_list(W, n_slots)]
             t0 = tables[0]
-            _need_cuda(t0, "W")
+        ids_dtype = str(ids_dtype).replace("torch.", "")
         self.S, self.B, self.dim = n_slots, batch, t0.shape[1]
         self.ctx = ctx or default_context(t0.device)
-        self._dev = t0.device
         pools = _as_list(pooltype, n_slots)
         cvm_mode = B.CVM_NONE if use_cvm is None else (B.CVM_USE if use_cvm else B.CVM_STRIP)
         self.d_out = self.dim - (cvm_offset if use_cvm is False else 0)
         slots = (B.Slot * n_slots)()
         for s in range(n_slots):
-            slots[s] = B.Slot(tables[s].data_ptr(), tables[s].shape[0], None, None, batch, None, self.d_out,
-                              B.POOLTYPES[pools[s]], _IDT[ids_dtype], 0)
-        desc = B.FusedDesc(n_slots, _DT[t0.dtype], slots, self.dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset,
+            slots[s] = B.Slot(tables[s].ptr, tables[s].shape[0], None, None, batch, None, self.d_out,
+                              B.POOLTYPES[pools[s]], _IDS[ids_dtype], 0)
+        desc = B.FusedDesc(n_slots, t0.code, slots, self.dim, int(padding_idx), float(pad_value), cvm_mode, cvm_offset,
                            B.SCALE_DIVIDE, B.INIT_ZERO, B.LOD_HOST, 0)
         if sharded is not None:
             desc.n_shards = sharded.n_shards
@@ -825,42 +898,58 @@ class HostPipe:
         h = C.c_void_p()
         B.check(B.lib().ctrfe_host_pipe_create(self.ctx.handle, C.byref(desc), int(max_ids_per_slot), int(n_groups), C.byref(h)))
         self.handle = h
-        self.host_out = torch.empty((n_slots, batch, self.d_out), dtype=t0.dtype, pin_memory=True)
-        self._out_ptrs = (C.c_void_p * n_slots)(*[self.host_out[s].data_ptr() for s in range(n_slots)])
+        np_dt = {"float32": np.float32, "float16": np.float16, "bfloat16": np.uint16}[t0.dtype]
+        self._pinned = PinnedArray((n_slots, batch, self.d_out), np_dt)
+        self.host_out = self._pinned.array
+        if t0.kind == "torch":
+            import torch
+            ht = torch.from_numpy(self.host_out)
+            self.host_out = ht.view(torch.bfloat16) if t0.dtype == "bfloat16" else ht
+        row_bytes = batch * self.d_out * t0.itemsize
+        self._out_ptrs = (C.c_void_p * n_slots)(*[self._pinned.ptr + s * row_bytes for s in range(n_slots)])
         self._ids_ptrs = (C.c_void_p * n_slots)()
         self._lod_ptrs = (C.c_void_p * n_slots)()
         self._n_ids = (C.c_int64 * n_slots)()
-        self._id_es = 8 if ids_dtype == torch.int64 else 4
-        self.d2h_bytes = self.host_out.numel() * self.host_out.element_size()
+        self._id_es = 8 if ids_dtype == "int64" else 4
+        self.d2h_bytes = n_slots * row_bytes
         self.h2d_bytes = 0
 
-    def run(self, ids_host: Sequence, lods_host: Sequence, wait: bool = True):
-        """ids_host[s]: int64 (or int32) CPU tensor / numpy array, pinned for asynchronous copies;
-        lods_host[s]: the [B + 1] offsets as a numpy uint64 array or an int64 CPU tensor."""
-        keep = []
-        h2d = 0
-        for s in range(self.S):
+    def prepare(self, ids_host: Sequence, lods_host: Sequence):
+        """The pointer tables of one request, built once for buffers that are reused (a serving loop's
+        feed buffers): run_prepared() then is one call into the library.  Slots whose id arrays
+        follow each other in host memory (views of one feed buffer) go up in one copy per group."""
+        S = self.S
+        ids_ptrs, lod_ptrs, n_ids = (C.c_void_p * S)(), (C.c_void_p * S)(), (C.c_int64 * S)()
+        keep, h2d = [ids_host, lods_host], 0
+        for s in range(S):
             i, l = ids_host[s], lods_host[s]
-            if isinstance(i, torch.Tensor):
-                self._ids_ptrs[s], self._n_ids[s] = i.data_ptr(), i.numel()
+            if isinstance(i, np.ndarray):
+                ids_ptrs[s], n_ids[s] = i.ctypes.data, i.size
             else:
-                self._ids_ptrs[s], self._n_ids[s] = i.ctypes.data, i.size
-            if isinstance(l, torch.Tensor):
-                self._lod_ptrs[s] = l.data_ptr()
-                n = l.numel()
-            else:
+                ids_ptrs[s], n_ids[s] = i.data_ptr(), i.numel()
+            if isinstance(l, np.ndarray) or _is_host_lod(l):
                 a = _lod_np(l)
                 keep.append(a)
-                self._lod_ptrs[s] = a.ctypes.data
+                lod_ptrs[s] = a.ctypes.data
                 n = a.size
+            else:
+                lod_ptrs[s] = l.data_ptr()
+                n = l.numel()
             if n != self.B + 1:
                 raise InvalidArgument("Batchsize of all inputs should be equal.")
-            h2d += self._n_ids[s] * self._id_es + n * 4
-        self.h2d_bytes = h2d
-        stream = torch.cuda.current_stream(self._dev)
-        B.check(B.lib().ctrfe_host_pipe_run(self.handle, self._ids_ptrs, self._n_ids, self._lod_ptrs, self._out_ptrs, self.d_out,
-                                            stream.cuda_stream, 1 if wait else 0))
+            h2d += n_ids[s] * self._id_es + n * 4
+        return (ids_ptrs, n_ids, lod_ptrs, keep, h2d)
+
+    def run_prepared(self, prep, wait: bool = True):
+        ids_ptrs, n_ids, lod_ptrs, _keep, self.h2d_bytes = prep
+        B.check(B.lib().ctrfe_host_pipe_run(self.handle, ids_ptrs, n_ids, lod_ptrs, self._out_ptrs, self.d_out,
+                                            self.ctx.stream(), 1 if wait else 0))
         return [self.host_out[s] for s in range(self.S)]
+
+    def run(self, ids_host: Sequence, lods_host: Sequence, wait: bool = True):
+        """ids_host[s]: int64 (or int32) numpy array or CPU tensor, pinned for asynchronous copies;
+        lods_host[s]: the [B + 1] offsets as a numpy uint64 array or an int64 CPU tensor."""
+        return self.run_prepared(self.prepare(ids_host, lods_host), wait)
 
     def close(self):
         if getattr(self, "handle", None):

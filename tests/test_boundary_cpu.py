@@ -148,3 +148,14 @@ def test_synth_generators_are_deterministic_and_shaped():
     # long-sequence law
     l5 = synth.draw_lengths(np.random.default_rng(0), 4096, 200)
     assert 150 < l5.mean() < 230 and l5.max() <= 1024
+
+
+def test_package_core_does_not_import_torch():
+    """`import paddle_infer_b200.ops` needs numpy and the library only (torch is imported lazily, and
+    only when a torch tensor is passed in)."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, %r); import paddle_infer_b200.ops, paddle_infer_b200.device, paddle_infer_b200.lod; "
+            "assert 'torch' not in sys.modules; print('ok')" % ROOT)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]

@@ -193,3 +193,55 @@ def test_host_pipe_equals_the_device_call(env, n_groups):
                 pipe.ctx.check_ids()
             assert e.value.id_value == N + 3
         pipe.close()
+
+
+def test_host_layer_runs_without_torch(env):
+    """The package core needs numpy and the library only: a child process that never imports torch
+    runs the fused front end, the three ops on their own and the host pipe on device.DeviceArray /
+    device.PinnedArray memory and matches the oracle."""
+    import os
+    import subprocess
+    import sys
+    import textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = textwrap.dedent('''
+        import sys
+        import numpy as np
+        sys.path.insert(0, %r)
+        from oracle import oracle as O
+        from paddle_infer_b200 import ops
+        from paddle_infer_b200.device import DeviceArray, PinnedArray
+        rng = np.random.default_rng(5)
+        N, D, S, Bsz = 3000, 16, 4, 200
+        table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+        table[:, 0] = rng.integers(0, 16, N); table[:, 1] = np.minimum(table[:, 0], rng.integers(0, 16, N))
+        lods, ids = [], []
+        for s in range(S):
+            l = rng.integers(0, 8, Bsz)
+            lods.append(np.concatenate([[0], np.cumsum(l)]).astype(np.uint64))
+            ids.append(rng.integers(0, N, int(lods[-1][-1])).astype(np.int64))
+        W = DeviceArray.from_numpy(table)
+        ids_d = [DeviceArray.from_numpy(i) for i in ids]
+        want = O.fused_forward([table], ids, lods, ["SUM"] * S, cvm_mode=O.CVM_USE, concat=True)
+        got = ops.ctr_fused_emb_seqpool_cvm(W, ids_d, lods, "SUM", use_cvm=True, concat=True).numpy()
+        g, w = got.reshape(Bsz, S, D), want.reshape(Bsz, S, D)
+        assert np.array_equal(g[:, :, 2:], w[:, :, 2:]) and np.allclose(g[:, :, :2], w[:, :, :2], rtol=1e-6, atol=1e-6)
+        rows = ops.lookup_table_v2(W, ids_d[0]).numpy()
+        assert np.array_equal(rows, table[ids[0]])
+        pooled = ops.sequence_pool(DeviceArray.from_numpy(rows), [list(lods[0])], "MAX", is_test=True).Out.numpy()
+        assert np.array_equal(pooled, O.sequence_pool(rows, lods[0], "MAX"))
+        y = ops.cvm(DeviceArray.from_numpy(np.abs(pooled)), None, True).numpy()
+        assert np.allclose(y, O.cvm(np.abs(pooled), True), rtol=1e-6, atol=1e-6)
+        # host buffers in, host buffers out, pinned memory from the library itself
+        pipe = ops.HostPipe(W, S, Bsz, 4000, "SUM", use_cvm=True, n_groups=2)
+        pin = [PinnedArray((i.size,), np.int64) for i in ids]
+        for p, i in zip(pin, ids):
+            p.array[:] = i
+        outs = pipe.run([p.array for p in pin], lods)
+        for s in range(S):
+            assert np.array_equal(outs[s][:, 2:], w[:, s, 2:])
+        assert "torch" not in sys.modules, "the host layer pulled torch in"
+        print("NO_TORCH_OK")
+    ''') % root
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "NO_TORCH_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
