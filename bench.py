@@ -513,7 +513,8 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
                                                                mode=args.e2e_mode)
     pinned = None if args.e2e_mode == "pipe" else [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
     if args.e2e_mode == "pipe":
-        fe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups)
+        fe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups,
+                          direct_out=args.e2e_direct_out)
         # a request's ids sit in ONE pinned feed buffer, slot after slot (per-slot views of it), its LoD
         # offsets in another; the pointer tables are built once per buffer set, as a serving loop would
         preps = []
@@ -781,6 +782,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--e2e-mode", default="pipe", choices=["pipe", "zero_copy", "copy"])
     ap.add_argument("--e2e-groups", type=int, default=4, help="slot groups of the host-buffer pipe")
+    ap.add_argument("--e2e-direct-out", action="store_true", help="host pipe: kernels write the rows into host memory themselves")
     ap.add_argument("--no-overlap", action="store_true",
                     help="timed loop without CTRFE_LAUNCH_OVERLAP_PREVIOUS (each launch waits for the one before)")
     ap.add_argument("--cpu-budget", type=float, default=12.0)

@@ -295,7 +295,10 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint6
  *           with row stride out_ld elements.  Pinned host memory keeps the copies asynchronous;
  *           the ids and the output must stay untouched until the run is through.  wait != 0:
  *           returns once the rows are on the host; wait == 0: `stream` is made to wait for them.
- *           Pooling kernels run on `stream`.  One run at a time per pipe. */
+ *           Pooling kernels run on `stream`.  One run at a time per pipe.
+ *   n_groups < 0 at create: |n_groups| groups with DIRECT output -- the kernels store the pooled rows
+ *           into out_host themselves (out_host must then be pinned, device-mapped memory such as
+ *           cudaHostAlloc returns, 16-byte aligned) and only the inputs use a copy engine. */
 typedef struct ctrfe_host_pipe ctrfe_host_pipe;
 int ctrfe_host_pipe_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, int64_t max_ids_per_slot, int n_groups,
                            ctrfe_host_pipe** out);

@@ -869,7 +869,9 @@ class HostPipe:
 
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
                  padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, n_groups: int = 4,
-                 ids_dtype="int64", ctx: Optional[Context] = None):
+                 ids_dtype="int64", direct_out: bool = False, ctx: Optional[Context] = None):
+        """direct_out: the kernels store the pooled rows straight into the pinned host block (PCIe writes
+        issued by the SMs) instead of a device block that a copy engine brings down."""
         sharded = W if _is_sharded(W) else None
         if sharded is not None:
             t0 = _sharded_like(sharded)
@@ -896,7 +898,8 @@ class HostPipe:
                 desc.hot_cache = C.pointer(sharded.hot.struct)
         self._keep = (tables, sharded)
         h = C.c_void_p()
-        B.check(B.lib().ctrfe_host_pipe_create(self.ctx.handle, C.byref(desc), int(max_ids_per_slot), int(n_groups), C.byref(h)))
+        B.check(B.lib().ctrfe_host_pipe_create(self.ctx.handle, C.byref(desc), int(max_ids_per_slot),
+                                               -int(n_groups) if direct_out else int(n_groups), C.byref(h)))
         self.handle = h
         np_dt = {"float32": np.float32, "float16": np.float16, "bfloat16": np.uint16}[t0.dtype]
         self._pinned = PinnedArray((n_slots, batch, self.d_out), np_dt)

@@ -274,3 +274,53 @@ class HotRowCache:
         self.hot_ids = hot_ids
         self.struct = B.HotCache(self.rows.data_ptr(), self.keys.data_ptr(), log2, n)
         self.nbytes = self.rows.numel() * self.rows.element_size() + 4 * (1 << log2)
+
+
+# ---- the bucket / all-to-all router (the exchange the reference's HeterComm performs) -----------------
+class RoutedForward:
+    """The north-star's shard router, built as the measured comparator of the peer-load kernel: ids
+    are bucketed by owner shard, exchanged with NCCL all-to-all, the owners gather the rows, the rows
+    come back the same way and the requester pools them in sequence order (so results stay
+    bit-identical).  Follows HeterComm's pull (framework/fleet/heter_ps/heter_comm_inl.h:1117-1171
+    split_input_to_shard = key % G bucket + sort; :1477-1607 pull_normal_sparse; :1296-1475 the
+    de-duplicating pull_merge_sparse) and the counted send/recv group of
+    operators/collective/global_scatter_op.cu.cc:109-135.  The bucketing uses torch's device sort and
+    scan (the reference uses cub's radix sort); the gather and the pooling are the library's kernels;
+    the exchanges are torch.distributed all_to_all_single (NCCL).  One host synchronisation per call
+    (the counts), as in the reference."""
+
+    def __init__(self, table: "ShardedTable", dedup: bool = False):
+        self.table, self.dedup = table, dedup
+        self.G, self.rank = table.n_shards, table.rank
+
+    def __call__(self, Ids: Sequence, lods: Sequence, pooltype="SUM", *, use_cvm=True, concat=True, pad_value=0.0,
+                 out=None, check: bool = False):
+        import torch
+        import torch.distributed as dist
+        from . import ops
+        G, grp = self.G, self.table.group
+        sizes = [int(i.numel()) for i in Ids]
+        all_ids = torch.cat([i.reshape(-1) for i in Ids]) if len(Ids) > 1 else Ids[0].reshape(-1)
+        if self.dedup:  # pull_merge_sparse: every distinct id crosses the link once
+            keys, inverse = torch.unique(all_ids, return_inverse=True)
+        else:
+            keys, inverse = all_ids, None
+        owner = keys % G
+        order = torch.argsort(owner, stable=True)            # bucket by owner shard
+        send_rows = (keys[order] // G).contiguous()           # local row at the owner
+        send_counts = torch.bincount(owner, minlength=G)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts, group=grp)
+        sc, rc = send_counts.tolist(), recv_counts.tolist()   # the one host synchronisation
+        recv_rows = torch.empty(sum(rc), dtype=torch.int64, device=all_ids.device)
+        dist.all_to_all_single(recv_rows, send_rows, output_split_sizes=rc, input_split_sizes=sc, group=grp)
+        rows_out = ops.lookup_table_v2(self.table.local, recv_rows, check=False)      # owner-side gather
+        rows_in = torch.empty((sum(sc), self.table.dim), dtype=self.table.dtype, device=all_ids.device)
+        dist.all_to_all_single(rows_in, rows_out, output_split_sizes=sc, input_split_sizes=rc, group=grp)
+        # position of every id's row in rows_in: the inverse of the bucket permutation (and of the dedup)
+        pos = torch.empty_like(order)
+        pos[order] = torch.arange(order.numel(), device=order.device)
+        back = pos[inverse] if inverse is not None else pos
+        back_slots = list(torch.split(back, sizes))
+        return ops.ctr_fused_emb_seqpool_cvm(rows_in, back_slots, lods, pooltype, use_cvm=use_cvm, concat=concat,
+                                             pad_value=pad_value, out=out, check=check)

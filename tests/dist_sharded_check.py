@@ -63,11 +63,16 @@ def main():
     cached = ops.ctr_fused_emb_seqpool_cvm(table, ids_t, lods, "SUM", use_cvm=True, concat=True)
     assert torch.equal(plain, cached)
     table.hot = None
+    # the bucket / NCCL all-to-all router (the measured comparator): same bits, with and without dedup
+    for dedup in (False, True):
+        routed = shard.RoutedForward(table, dedup=dedup)(ids_t, lods, "SUM", use_cvm=True, concat=True)
+        assert torch.equal(plain, routed), f"router (dedup={dedup}) differs from the peer-load kernel"
     frac_remote = float(np.mean(np.concatenate(ids) % world != rank))
     dist.barrier()
     table.close()
     if rank == 0:
-        print(f"sharded ok: {world} GPUs, {frac_remote:.0%} of rows fetched over NVLink, bit-exact vs the oracle")
+        print(f"sharded ok: {world} GPUs, {frac_remote:.0%} of rows fetched over NVLink, bit-exact vs the oracle; "
+              "hot-row replicas and the NCCL all-to-all router (with and without dedup) give the same bits")
     dist.destroy_process_group()
 
 
