@@ -290,10 +290,14 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint6
  * (ids [n_slots, max_ids_per_slot], outputs, LoD images); a run allocates nothing.
  *   create: desc gives the slots' tables, n_seg, pooltypes, id width (one for all slots) and the
  *           attributes; its ids / lod / out pointers are ignored.
- *   run:    ids_host[s] (n_ids[s] entries) and lods_host[s] ([n_seg + 1] offsets, validated as
- *           ctrfe_plan_create does) are read, out_host[s] receives slot s's [n_seg, D_out] rows
- *           with row stride out_ld elements.  Pinned host memory keeps the copies asynchronous;
- *           the ids and the output must stay untouched until the run is through.  wait != 0:
+ *   run:    ids_host[s] (n_ids[s] entries) and lods_host[s] ([n_seg + 1] offsets) are read,
+ *           out_host[s] receives slot s's [n_seg, D_out] rows with row stride out_ld elements.
+ *           The offsets go up as they are: only the last one is compared with n_ids on the host;
+ *           the kernels check every pair they read (as for CTRFE_LOD_DEVICE), pool an offending
+ *           sequence as empty and leave the record for ctrfe_check_ids.  Pinned host memory keeps
+ *           the copies asynchronous; arrays that follow each other in host memory (one feed buffer)
+ *           go up in one copy per group; ids, offsets and the output must stay untouched until the
+ *           run is through.  wait != 0:
  *           returns once the rows are on the host; wait == 0: `stream` is made to wait for them.
  *           Pooling kernels run on `stream`.  One run at a time per pipe.
  *   n_groups < 0 at create: |n_groups| groups with DIRECT output -- the kernels store the pooled rows

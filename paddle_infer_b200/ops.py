@@ -940,7 +940,7 @@ class HostPipe:
                 n = l.numel()
             if n != self.B + 1:
                 raise InvalidArgument("Batchsize of all inputs should be equal.")
-            h2d += n_ids[s] * self._id_es + n * 4
+            h2d += n_ids[s] * self._id_es + n * 8
         return (ids_ptrs, n_ids, lod_ptrs, keep, h2d)
 
     def run_prepared(self, prep, wait: bool = True):
