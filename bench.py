@@ -570,6 +570,30 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
                     "per-slot host outputs over PCIe inside the one launch, then the stream is synchronised"
                     if args.e2e_mode == "zero_copy" else "HostFrontEnd copy: H2D ids + LoD upload, launch, D2H output")}
     if args.e2e_mode == "zero_copy" and not args.quick:
+        # the same step through the library's copy-engine pipe (ctrfe_host_pipe_run): slower on this box
+        # (every H2D copy costs ~40 us before its first byte, and uploads slow down beside downloads)
+        try:
+            pipe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups)
+            hb = host_batches[0]
+            feed = torch.from_numpy(np.concatenate(hb.ids)).pin_memory()
+            offs = np.concatenate([[0], np.cumsum([i.size for i in hb.ids])])
+            lod_feed = torch.from_numpy(np.stack([l.astype(np.int64) for l in hb.lods])).pin_memory()
+            prep = pipe.prepare([feed[int(offs[s]):int(offs[s + 1])] for s in range(S)], [lod_feed[s] for s in range(S)])
+            for _ in range(3):
+                pipe.run_prepared(prep)
+            tp0 = time.perf_counter()
+            for _ in range(Ke):
+                pipe.run_prepared(prep)
+            tpp = (time.perf_counter() - tp0) * 1e3 / Ke
+            gp = np.stack([np.asarray(pipe.host_out[s]) for s in range(S)], axis=1)
+            rec["host_pipe"] = {"ms_per_step": tpp, "value": S * Bsz / (tpp * 1e-3), "groups": args.e2e_groups,
+                                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+                                "parity_ok": parity_check(cfg, hb, gp, 1 if cfg.shared_table else S, sample=8)["ok"],
+                                "note": "this rank only; ctrfe_host_pipe_run: copy-engine H2D per slot group, pooling, copy-engine "
+                                        "D2H, LoD checked by the kernels"}
+            pipe.close()
+        except Exception as ex:  # a secondary figure must not cost the run its headline
+            rec["host_pipe"] = {"error": repr(ex)[:200]}
         # three requests in flight: each has its own front end (own pinned output); request i + 1 is
         # submitted before request i is waited for
         fes = [fe] + [ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, mode="zero_copy")
@@ -822,8 +846,8 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
     ap.add_argument("--regions", type=int, default=15, help="timed regions of --steps launches; the median region is reported")
     ap.add_argument("--e2e-steps", type=int, default=40)
-    ap.add_argument("--e2e-mode", default="pipe", choices=["pipe", "zero_copy", "copy"])
-    ap.add_argument("--e2e-groups", type=int, default=4, help="slot groups of the host-buffer pipe")
+    ap.add_argument("--e2e-mode", default="zero_copy", choices=["pipe", "zero_copy", "copy"])
+    ap.add_argument("--e2e-groups", type=int, default=3, help="slot groups of the host-buffer pipe")
     ap.add_argument("--e2e-direct-out", action="store_true", help="host pipe: kernels write the rows into host memory themselves")
     ap.add_argument("--no-overlap", action="store_true",
                     help="timed loop without CTRFE_LAUNCH_OVERLAP_PREVIOUS (each launch waits for the one before)")
