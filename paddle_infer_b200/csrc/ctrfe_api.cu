@@ -259,17 +259,21 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     plan->fast = f;
     plan->cvm_use = d->cvm_mode == CTRFE_CVM_USE;
   }
-  // Bytes of a row one lane holds: 16 (one 128-bit load), or 32 (one 256-bit load) for rows of 128
-  // bytes and wider -- random rows of that width sustain 5.3 - 6.5 TB/s through 256-bit loads against
-  // 3.8 TB/s through 128-bit ones on B200 (profiles/r2_gather_sweep.txt); 64-byte rows gain nothing and
-  // lose warps.  CTRFE_LDG256=0 keeps 128-bit lanes, =1 also gives wide lanes to 32- and 64-byte rows.
-  // In the sharded mode only the specialised kernel has the wide form.
+  // Bytes of a row one lane holds: 16 (one 128-bit load) or 32 (one 256-bit load).  A stripped gather of
+  // uniform-random rows sustains far more through 256-bit loads once rows are 128 bytes wide (5.3 against
+  // 3.8 TB/s, 6.5 against 3.8 at 256 bytes: profiles/r2_gather_sweep.txt) -- but none of the five BASELINE
+  // configs is bound there: cfg3 / cfg4 on one GPU hold > 100 GB of tables and run at the TLB's page-walk
+  // rate (profiles/r2_gather_table_size.txt), cfg5 at the latency of its long sequences, and the wide form
+  // costs a third of the resident warps (40 - 48 registers).  Measured (profiles/r2_wide_lane_sweep.txt):
+  // cfg3 203 -> 206 us at best, cfg4 611 -> 617, cfg5 174 -> 195.  So 128-bit lanes stay the default;
+  // CTRFE_LDG256=1 selects 256-bit lanes for rows of 128 bytes and wider, =2 for every row of 32 bytes
+  // and up.  In the sharded mode only the specialised kernel has the wide form.
   int cb = 16;
   {
     const char* use256 = getenv("CTRFE_LDG256");
-    const long long min_row = (use256 && use256[0] == '1') ? 32 : 128;
-    if (v && row_bytes % 32 == 0 && row_bytes >= min_row && !(use256 && use256[0] == '0') &&
-        (!sharded || (plan->fast && !has_select))) {
+    const int wide = use256 && use256[0] ? atoi(use256) : 0;
+    const long long min_row = wide >= 2 ? 32 : 128;
+    if (wide >= 1 && v && row_bytes % 32 == 0 && row_bytes >= min_row && (!sharded || (plan->fast && !has_select))) {
       cb = 32;
       if (sharded) {
         for (int g = 0; g < d->n_shards; ++g)
@@ -534,12 +538,26 @@ void launch_fast_t(int gs, int cb, bool cvm, dim3 grid, cudaStream_t st, const c
   else launch_fast_c<DT, 16>(gs, cvm, grid, st, p, overlap);
 }
 
+// CTRFE_PREFETCH=1: an L2 prefetch of the launch's ids and offsets runs ahead of every pooling kernel
+// (l2_prefetch_kernel); an A/B switch until the measurements say which way the default goes.
+bool prefetch_on() {
+  static const bool on = [] {
+    const char* e = getenv("CTRFE_PREFETCH");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = false) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
     const int m = plan.modes[c];
     // the launches of one plan work on different slots: the second may always start while the
     // first drains; the first does so only if the caller said it may (overlap_first)
-    const bool overlap = overlap_first || c > 0;
+    bool overlap = overlap_first || c > 0;
+    if (prefetch_on() && plan.chunks[c].n_shards == 0) {
+      launch_k(ctrfe::l2_prefetch_kernel, dim3(16, static_cast<unsigned>(plan.chunks[c].n_slots), 1), st, plan.chunks[c], overlap);
+      overlap = true;  // the pooling kernel consumes nothing the prefetch produces
+    }
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
         case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.chunk_bytes, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;
