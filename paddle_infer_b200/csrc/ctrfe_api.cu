@@ -538,26 +538,12 @@ void launch_fast_t(int gs, int cb, bool cvm, dim3 grid, cudaStream_t st, const c
   else launch_fast_c<DT, 16>(gs, cvm, grid, st, p, overlap);
 }
 
-// CTRFE_PREFETCH=1: an L2 prefetch of the launch's ids and offsets runs ahead of every pooling kernel
-// (l2_prefetch_kernel); an A/B switch until the measurements say which way the default goes.
-bool prefetch_on() {
-  static const bool on = [] {
-    const char* e = getenv("CTRFE_PREFETCH");
-    return e && e[0] == '1';
-  }();
-  return on;
-}
-
 int launch_plan(const ctrfe_plan& plan, cudaStream_t st, bool overlap_first = false) {
   for (size_t c = 0; c < plan.chunks.size(); ++c) {
     const int m = plan.modes[c];
     // the launches of one plan work on different slots: the second may always start while the
     // first drains; the first does so only if the caller said it may (overlap_first)
-    bool overlap = overlap_first || c > 0;
-    if (prefetch_on() && plan.chunks[c].n_shards == 0) {
-      launch_k(ctrfe::l2_prefetch_kernel, dim3(16, static_cast<unsigned>(plan.chunks[c].n_slots), 1), st, plan.chunks[c], overlap);
-      overlap = true;  // the pooling kernel consumes nothing the prefetch produces
-    }
+    const bool overlap = overlap_first || c > 0;
     if (plan.fast && m == ctrfe::kModeAdd) {
       switch (plan.dtype) {
         case CTRFE_F32: launch_fast_t<CTRFE_F32>(plan.g_shift, plan.chunk_bytes, plan.cvm_use, plan.grids[c], st, plan.chunks[c], overlap); break;

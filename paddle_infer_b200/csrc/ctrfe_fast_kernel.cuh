@@ -121,6 +121,14 @@ struct RowSource {
     }
   }
 
+  // asks L2 for the whole row `rid` (every 128-byte line of it); SHARDED rows are left alone
+  __device__ __forceinline__ void prefetch_row(uint32_t rid) const {
+    const char* p = row_ptr(rid) - lane_off;
+    constexpr unsigned kRowBytes = 1u << kRowShift;
+#pragma unroll
+    for (unsigned o = 0; o < kRowBytes; o += 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+  }
+
   // row index of the id at position `pos` of the slot's id array; kSkip (and the error flag)
   // for an id outside the table
   __device__ __forceinline__ uint32_t resolve(unsigned pos) const {
@@ -196,6 +204,14 @@ __device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDE
     if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
 #pragma unroll
       for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(base + R + i * G + static_cast<int>(gl));
+      // A long sequence is a chain of row-load latencies, U rows at a time.  The lane that holds the
+      // id of a coming row asks L2 for that row now, so that when its turn comes (up to R / U steps
+      // later) the load finds it there: one DRAM latency per R rows instead of one per U rows.
+      if constexpr (!SHARDED) {
+#pragma unroll
+        for (int i = 0; i < NI; ++i)
+          if (nxt[i] != kSkip) src.prefetch_row(nxt[i]);
+      }
     }
 #pragma unroll
     for (int c = 0; c < R / U; ++c) {
@@ -265,28 +281,6 @@ fused_pool_fast_kernel(const __grid_constant__ KParams kp) {
   for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
   pool_rows_by_warp<DT, GS, SHARDED, HOT, CB>(src, start, len, gl, acc);
   finish_segment<DT, GS, CVM, CB>(kp, slp, acc, len, seg, gl, seg_ok);
-}
-
-// Pulls the ids and LoD offsets of a launch's slots into L2 ahead of the pooling kernel.  A warp of
-// that kernel lives through a chain of dependent latencies -- offsets, then ids, then rows -- and the
-// first two are plain streams: fetched here at streaming speed (a cfg2 batch: 12.5 MB, ~3 us), they
-// cost the pooling warps an L2 hit instead of a DRAM miss each.  Launched right before the pooling
-// kernel, which may start while this one drains (programmatic dependent launch); it only prefetches,
-// so there is nothing to wait for.
-__global__ void __launch_bounds__(256) l2_prefetch_kernel(const __grid_constant__ KParams kp) {
-  launch_dependents();
-  const SlotK* const slp = &kp.slots[blockIdx.y];
-  const unsigned long long lines_lod = (static_cast<unsigned long long>(slp->n_seg + 1) * (slp->lod32 ? 4u : 8u) + 127u) >> 7;
-  const unsigned idb = slp->id_kind == 1 ? 4u : 8u;
-  const unsigned long long lines_ids = slp->id_kind == 2 ? 0ull : (static_cast<unsigned long long>(slp->n_ids) * idb + 127u) >> 7;
-  const char* lod = reinterpret_cast<const char*>(slp->lod);
-  const char* ids = static_cast<const char*>(slp->ids);
-  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
-  for (unsigned long long i = static_cast<unsigned long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < lines_lod + lines_ids;
-       i += stride) {
-    const char* a = i < lines_lod ? lod + (i << 7) : ids + ((i - lines_lod) << 7);
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
-  }
 }
 
 // Fills a hot-row cache: one warp per hot id claims a hash slot (open addressing, linear
