@@ -121,14 +121,6 @@ struct RowSource {
     }
   }
 
-  // asks L2 for the whole row `rid` (every 128-byte line of it); SHARDED rows are left alone
-  __device__ __forceinline__ void prefetch_row(uint32_t rid) const {
-    const char* p = row_ptr(rid) - lane_off;
-    constexpr unsigned kRowBytes = 1u << kRowShift;
-#pragma unroll
-    for (unsigned o = 0; o < kRowBytes; o += 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
-  }
-
   // row index of the id at position `pos` of the slot's id array; kSkip (and the error flag)
   // for an id outside the table
   __device__ __forceinline__ uint32_t resolve(unsigned pos) const {
@@ -204,14 +196,6 @@ __device__ __forceinline__ void pool_rows_by_warp(const RowSource<DT, GS, SHARDE
     if (base + R < maxlen) {  // warp-uniform: only long sequences come back for more ids
 #pragma unroll
       for (int i = 0; i < NI; ++i) nxt[i] = fetch_rid(base + R + i * G + static_cast<int>(gl));
-      // A long sequence is a chain of row-load latencies, U rows at a time.  The lane that holds the
-      // id of a coming row asks L2 for that row now, so that when its turn comes (up to R / U steps
-      // later) the load finds it there: one DRAM latency per R rows instead of one per U rows.
-      if constexpr (!SHARDED) {
-#pragma unroll
-        for (int i = 0; i < NI; ++i)
-          if (nxt[i] != kSkip) src.prefetch_row(nxt[i]);
-      }
     }
 #pragma unroll
     for (int c = 0; c < R / U; ++c) {

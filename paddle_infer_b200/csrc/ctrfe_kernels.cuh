@@ -430,17 +430,6 @@ fused_pool_kernel(const __grid_constant__ KParams kp) {
 #pragma unroll
       for (int i = 0; i < NI; ++i)
         nxt[i] = fetch_rid(idp + static_cast<unsigned long long>(i * G) * id_step, base + R + i * G + gl);
-      // the lane that holds a coming row's id asks L2 for that row now (see pool_rows_by_warp)
-      if constexpr (!SHARDED && VECT) {
-        if (tiles == 1) {
-#pragma unroll
-          for (int i = 0; i < NI; ++i)
-            if (nxt[i] < kZero) {
-              const char* rp = row_ptr(nxt[i]) - lane_off;
-              for (unsigned o = 0; o < row_bytes; o += 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + o));
-            }
-        }
-      }
     }
 #pragma unroll
     for (int c = 0; c < R / U; ++c) {
