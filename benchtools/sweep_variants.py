@@ -23,15 +23,11 @@ BASE = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared", "-ge
 # name -> (extra nvcc flags, environment for the run)
 VARIANTS = {
     "base": ([], {}),
-    "ldg128": ([], {"CTRFE_LDG256": "0"}),          # 128-bit lanes for every row width (the round-1 kernels)
-    "ldg256_all": ([], {"CTRFE_LDG256": "1"}),      # 256-bit lanes also for 32- / 64-byte rows
-    "u2_w8_8": (["-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
-    "u2_w6_6": (["-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
-    "u2_w4_4": (["-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=4"], {}),
-    "u4_w6_6": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=6", "-DCTRFE_MINB_WIDE16=6"], {}),
-    "u4_w5_4": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=5", "-DCTRFE_MINB_WIDE16=4"], {}),
-    "u4_w4_3": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=4", "-DCTRFE_MINB_WIDE16=3"], {}),
-    "u4_w8_8": (["-DCTRFE_WIDE_U=4", "-DCTRFE_MINB_WIDE32=8", "-DCTRFE_MINB_WIDE16=8"], {}),
+    "u8_m8": (["-DCTRFE_UNROLL=8"], {}),
+    "u8_m6": (["-DCTRFE_UNROLL=8", "-DCTRFE_MINB16=6", "-DCTRFE_MINB32=6"], {}),
+    "u8_m5": (["-DCTRFE_UNROLL=8", "-DCTRFE_MINB16=5", "-DCTRFE_MINB32=5"], {}),
+    "u8_m4": (["-DCTRFE_UNROLL=8", "-DCTRFE_MINB16=4", "-DCTRFE_MINB32=4"], {}),
+    "u16_m3": (["-DCTRFE_UNROLL=16", "-DCTRFE_MINB16=3", "-DCTRFE_MINB32=3"], {}),
 }
 
 

@@ -41,7 +41,10 @@ namespace ctrfe {
 #define CTRFE_THREADS 256
 #endif
 constexpr int kThreads = CTRFE_THREADS; // threads per CTA of the pooling kernel
-constexpr int kUnroll = 4;             // row loads in flight per lane
+#ifndef CTRFE_UNROLL
+#define CTRFE_UNROLL 4
+#endif
+constexpr int kUnroll = CTRFE_UNROLL;   // row loads in flight per lane
 constexpr int kMaxSlotsPerLaunch = 64; // slot descriptors carried in the kernel parameters (block <= 4 KB)
 constexpr int kMaxShards = 8;           // GPUs of one NVSwitch box
 constexpr uint32_t kSkip = 0xffffffffu;  // row slot past the end of the sequence: no load, no add
