@@ -512,9 +512,9 @@ def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
     """The same metric through the host-buffer call: every step reads that step's ids + LoD
     offsets from pinned host memory and lands the pooled rows in pinned host memory."""
     if args.e2e_mode == "auto":
-        # the SMs' own PCIe traffic (zero_copy) wins on one GPU; with every GPU of the box busy the
-        # copy engines (pipe) do better -- both measured, see profiles/README.md
-        args.e2e_mode = "zero_copy" if world == 1 else "pipe"
+        # the SMs' own PCIe traffic (zero_copy) wins on one or two GPUs; with every GPU of the box busy
+        # the copy engines (pipe) do better -- both measured, see profiles/README.md
+        args.e2e_mode = "zero_copy" if world <= 2 else "pipe"
     S = cfg.slots
     host_batches, ctx = m["_host_batches"], m["_ctx"]
     n_batches = len(host_batches)
@@ -867,7 +867,8 @@ def main():
     ap.add_argument("--regions", type=int, default=15, help="timed regions of --steps launches; the median region is reported")
     ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--e2e-mode", default="auto", choices=["auto", "pipe", "zero_copy", "copy"],
-                    help="auto: zero_copy on one GPU, pipe on several (measured: 0.58 vs 0.66 ms at N = 1, 2.2 vs 1.5 ms at N = 8)")
+                    help="auto: zero_copy on 1-2 GPUs, pipe on more (measured ms per step, zero_copy vs pipe: N = 1 0.58 vs 0.66, "
+                         "N = 2 0.74 vs 0.82, N = 8 2.2 vs 1.5)")
     ap.add_argument("--e2e-groups", type=int, default=3, help="slot groups of the host-buffer pipe")
     ap.add_argument("--e2e-direct-out", action="store_true", help="host pipe: kernels write the rows into host memory themselves")
     ap.add_argument("--no-overlap", action="store_true",
