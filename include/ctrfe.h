@@ -167,8 +167,11 @@ typedef struct ctrfe_fused_desc {
                              bucket / walk_to_dest / gather / walk_to_src pull
                              (heter_comm_inl.h:1477-1607): rows are fetched by the pooling kernel
                              itself with loads through the peer mapping, in sequence order */
-  const struct ctrfe_hot_cache* hot_cache; /* sharded mode only, may be NULL: local replicas of the
-                             most frequently looked-up rows (see ctrfe_hot_cache_build) */
+  const struct ctrfe_hot_cache* hot_cache; /* may be NULL: replicas of the most frequently looked-up rows
+                             (see ctrfe_hot_cache_build).  Beside a sharded table they are local copies
+                             that save NVLink trips; beside ONE unsharded table that every slot reads they
+                             are a compact region the TLB and L2 can hold when the table itself is beyond
+                             the TLB's reach (> ~64 GB on B200: cold rows then cost a page walk each) */
   const struct ctrfe_keymap* keymap; /* may be NULL: ids are uint64 feasign keys looked up in this
                              map (not with sharded tables; ids_dtype must be CTRFE_I64) */
 } ctrfe_fused_desc;

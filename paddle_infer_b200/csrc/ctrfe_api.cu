@@ -200,17 +200,20 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     for (int g = 0; g < d->n_shards; ++g)
       if (!d->shard_tables[g] || reinterpret_cast<uintptr_t>(d->shard_tables[g]) % 16 != 0)
         return fail(CTRFE_ERR_ARG, "fused: shard_tables[%d] is null or not 16-byte aligned", g);
-    if (d->hot_cache && d->hot_cache->rows) {
-      const ctrfe_hot_cache* hc = d->hot_cache;
-      if (!hc->keys || hc->log2_slots < 4 || hc->log2_slots > 30 || hc->n_rows <= 0 ||
-          reinterpret_cast<uintptr_t>(hc->rows) % 16 != 0)
-        return fail(CTRFE_ERR_ARG, "fused: malformed hot_cache");
-      for (int s = 0; s < d->n_slots; ++s)
-        if (d->slots[s].table_rows >= 0x7fffffffLL)
-          return fail(CTRFE_ERR_UNSUPPORTED, "fused: a hot-row cache needs table_rows < 2^31");
+  }
+  if (d->hot_cache && d->hot_cache->rows) {
+    // replicas of the hottest rows: beside a sharded table they save NVLink trips, beside ONE big
+    // unsharded table they are a compact region the TLB and L2 can hold
+    const ctrfe_hot_cache* hc = d->hot_cache;
+    if (!hc->keys || hc->log2_slots < 4 || hc->log2_slots > 30 || hc->n_rows <= 0 ||
+        reinterpret_cast<uintptr_t>(hc->rows) % 16 != 0)
+      return fail(CTRFE_ERR_ARG, "fused: malformed hot_cache");
+    for (int s = 0; s < d->n_slots; ++s) {
+      if (d->slots[s].table_rows >= 0x7fffffffLL)
+        return fail(CTRFE_ERR_UNSUPPORTED, "fused: a hot-row cache needs table_rows < 2^31");
+      if (!sharded && (d->slots[s].table != d->slots[0].table || d->slots[s].table_rows != d->slots[0].table_rows))
+        return fail(CTRFE_ERR_ARG, "fused: a hot-row cache beside unsharded tables needs every slot to read the same table");
     }
-  } else if (d->hot_cache) {
-    return fail(CTRFE_ERR_ARG, "fused: hot_cache is only meaningful in the sharded table mode");
   }
   const ctrfe_keymap* km = d->keymap;
   if (km) {
@@ -273,7 +276,9 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     const char* use256 = getenv("CTRFE_LDG256");
     const int wide = use256 && use256[0] ? atoi(use256) : 0;
     const long long min_row = wide >= 2 ? 32 : 128;
-    if (wide >= 1 && v && row_bytes % 32 == 0 && row_bytes >= min_row && (!sharded || (plan->fast && !has_select))) {
+    const bool hot_unsharded = !sharded && d->hot_cache && d->hot_cache->rows;
+    if (wide >= 1 && !hot_unsharded && v && row_bytes % 32 == 0 && row_bytes >= min_row &&
+        (!sharded || (plan->fast && !has_select))) {
       cb = 32;
       if (sharded) {
         for (int g = 0; g < d->n_shards; ++g)
@@ -282,6 +287,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       } else {
         for (int s = 0; s < d->n_slots; ++s)
           if (reinterpret_cast<uintptr_t>(d->slots[s].table) % 32 != 0) cb = 16;
+        if (d->hot_cache && d->hot_cache->rows && reinterpret_cast<uintptr_t>(d->hot_cache->rows) % 32 != 0) cb = 16;
       }
     }
     if (cb == 16 && row_bytes > 512) plan->fast = false;  // 128-bit lanes cover at most 512 bytes with one warp
@@ -329,7 +335,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
       k.init_mode = d->init_mode;
       k.pad_value = d->pad_value;
       k.n_slots = 0;
-      if (sharded && plan->fast && d->hot_cache && d->hot_cache->rows && d->hot_cache->log2_slots > 0) {
+      if (plan->fast && d->hot_cache && d->hot_cache->rows && d->hot_cache->log2_slots > 0) {
         k.hot_rows = static_cast<const char*>(d->hot_cache->rows);
         k.hot_keys = d->hot_cache->keys;
         k.hot_mask = (1u << d->hot_cache->log2_slots) - 1u;
@@ -390,7 +396,7 @@ int plan_geometry(ctrfe_ctx* ctx, const ctrfe_fused_desc* d, ctrfe_plan* plan, s
     if (plan->fast && plan->modes[c] == ctrfe::kModeAdd)
       snprintf(buf, sizeof(buf), "ctrfe::fused_pool_fast_kernel<%s, %d-byte rows, cvm=%d, sharded=%d, hot=%d, %d-byte lanes>",
                dtn[plan->dtype], plan->chunk_bytes << plan->g_shift, plan->cvm_use ? 1 : 0, sh ? 1 : 0,
-               sh && plan->chunks[c].hot_rows ? 1 : 0, plan->chunk_bytes);
+               plan->chunks[c].hot_rows ? 1 : 0, plan->chunk_bytes);
     else
       snprintf(buf, sizeof(buf), "ctrfe::fused_pool_kernel<%s, vect=%d, lanes=%d, %s, %d-byte lanes, sharded=%d>", dtn[plan->dtype],
                plan->vect ? 1 : 0, 1 << plan->g_shift, plan->modes[c] == ctrfe::kModeSelect ? "select" : "add",
@@ -522,9 +528,13 @@ void launch_fast_g(int gs, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, 
 template <int DT, int CB>
 void launch_fast_c(int gs, bool cvm, dim3 grid, cudaStream_t st, const ctrfe::KParams& p, bool overlap) {
   const bool sh = p.n_shards > 0;
-  const bool hot = sh && p.hot_rows != nullptr;
-  if (hot) {
+  const bool hot = p.hot_rows != nullptr;
+  if (hot && sh) {
     if (cvm) launch_fast_g<DT, true, true, true, CB>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, true, true, CB>(gs, grid, st, p, overlap);
+  } else if (hot && CB == 16) {  // one unsharded table with a compact region of hot-row replicas (128-bit lanes only)
+    if constexpr (CB == 16) {
+      if (cvm) launch_fast_g<DT, true, false, true, 16>(gs, grid, st, p, overlap); else launch_fast_g<DT, false, false, true, 16>(gs, grid, st, p, overlap);
+    }
   } else if (cvm) {
     if (sh) launch_fast_g<DT, true, true, false, CB>(gs, grid, st, p, overlap); else launch_fast_g<DT, true, false, false, CB>(gs, grid, st, p, overlap);
   } else {

@@ -403,7 +403,7 @@ def _is_host_lod(l) -> bool:
 
 
 def _build_desc(tables, ids, lods, pooltypes, out_ptrs, out_ld, *, dim, dtype_code, pad_value, padding_idx, cvm_mode,
-                cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None, keymap=None):
+                cvm_offset, scale_mode, init_mode, lod_on_device, sharded=None, keymap=None, hot_cache=None):
     """tables: Arr / _TableRef per slot; ids: Arr or None per slot; lods: host sequences or device Arrs."""
     S = len(lods)
     slots = (B.Slot * S)()
@@ -435,6 +435,9 @@ def _build_desc(tables, ids, lods, pooltypes, out_ptrs, out_ld, *, dim, dtype_co
             desc.hot_cache = C.pointer(hot.struct)
             keep.append(hot)
         keep.append(sharded)
+    if hot_cache is not None and sharded is None:  # compact replicas of the hot rows beside ONE unsharded table
+        desc.hot_cache = C.pointer(hot_cache.struct)
+        keep.append(hot_cache)
     if keymap is not None:  # ids are uint64 feasign keys, resolved in the kernel (KeyMap)
         desc.keymap = C.pointer(keymap.struct)
         keep.append(keymap)
@@ -457,7 +460,7 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence, lods: Sequence, pooltype="SUM", 
                               pad_value: float = 0.0, padding_idx: int = -1, use_cvm: Optional[bool] = True,
                               cvm_offset: int = 2, concat: bool = False, scale_mode: int = B.SCALE_DIVIDE,
                               init_mode: int = B.INIT_ZERO, check: bool = True, plan_only: bool = False,
-                              out=None, ctx: Optional[Context] = None, keymap: Optional["KeyMap"] = None):
+                              out=None, ctx: Optional[Context] = None, keymap: Optional["KeyMap"] = None, hot_cache=None):
     """lookup_table_v2 -> sequence_pool -> cvm for every slot of a CTR batch in one launch.
 
     W         one table [N, D] shared by all slots, or a list with one table per slot, or a
@@ -472,6 +475,9 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence, lods: Sequence, pooltype="SUM", 
               None: no cvm op after the pool
     concat    write all slots into one [B, S*D_out] array (concat(axis=1) fused, as
               fusion_seqpool_cvm_concat does)
+    hot_cache a shard.HotRowCache built over W (one table read by every slot): lookups of the hottest rows
+              go to a compact replica region that the TLB and L2 can hold -- for a table beyond the
+              TLB's reach (> ~64 GB) where every cold row costs a page walk; results are bit-identical
     keymap    a KeyMap: Ids are then uint64 feasign keys (viewed as int64, as pull_box_sparse
               takes them) and W holds one row per key of the map; key 0 and unknown keys pool
               as zero rows
@@ -524,7 +530,7 @@ def ctr_fused_emb_seqpool_cvm(W, Ids: Sequence, lods: Sequence, pooltype="SUM", 
     desc, keep = _build_desc(tables, ids_a, lods, pools, out_ptrs, ld, dim=dim, dtype_code=t0.code,
                              pad_value=pad_value, padding_idx=padding_idx, cvm_mode=cvm_mode, cvm_offset=cvm_offset,
                              scale_mode=scale_mode, init_mode=init_mode, lod_on_device=lod_on_device, sharded=sharded,
-                             keymap=keymap)
+                             keymap=keymap, hot_cache=hot_cache)
     if plan_only:
         h = C.c_void_p()
         B.check(B.lib().ctrfe_plan_create(ctx.handle, C.byref(desc), ctx.stream(), C.byref(h)))

@@ -236,7 +236,9 @@ def pick_hot_ids(sample_ids, capacity: int):
 
 
 class HotRowCache:
-    """Local replicas of a sharded table's most frequently looked-up rows (ctrfe_hot_cache).
+    """Local replicas of a table's most frequently looked-up rows (ctrfe_hot_cache): beside a sharded
+    table (`table.hot = HotRowCache(table, ids)`), or beside one big unsharded table
+    (`ops.ctr_fused_emb_seqpool_cvm(W, ..., hot_cache=HotRowCache(W, ids))`).
 
     Peer memory is not cached by the local L2, so without this every look-up of a popular row
     crosses NVLink again; with Zipf ids a few hundred MB of replicas absorb most look-ups.  The
@@ -254,11 +256,14 @@ class HotRowCache:
             raise ValueError("no hot ids")
         ctx = ctx or ops.default_context(dev)
         lod = torch.arange(n + 1, dtype=torch.int64, device=dev)
-        saved, table.hot = getattr(table, "hot", None), None
-        try:
+        if isinstance(table, torch.Tensor):  # one unsharded table: the replicas are a compact, TLB-friendly region
             rows = ops.ctr_fused_emb_seqpool_cvm(table, [hot_ids], [lod], "FIRST", use_cvm=None, ctx=ctx)[0]
-        finally:
-            table.hot = saved
+        else:
+            saved, table.hot = getattr(table, "hot", None), None
+            try:
+                rows = ops.ctr_fused_emb_seqpool_cvm(table, [hot_ids], [lod], "FIRST", use_cvm=None, ctx=ctx)[0]
+            finally:
+                table.hot = saved
         src = rows.contiguous()
         log2 = max(4, int(np.ceil(np.log2(max(n, 1) * 2.0))))   # load factor <= 0.5
         self.log2_slots = log2

@@ -245,3 +245,35 @@ def test_host_layer_runs_without_torch(env):
     ''') % root
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, cwd=root)
     assert r.returncode == 0 and "NO_TORCH_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_hot_rows_beside_an_unsharded_table_change_nothing(env):
+    """shard.HotRowCache beside ONE unsharded table (a compact, TLB-friendly replica region for tables
+    beyond the TLB's reach): the same bits as without it, for hot ids, cold ids and a mix, fp32 and
+    bf16; slots reading different tables are refused."""
+    ops, O, B, dev = env
+    from paddle_infer_b200 import shard
+    rng = np.random.default_rng(123)
+    N, S, Bsz = 50_000, 4, 600
+    for dtype, D, use_cvm in ((torch.float32, 32, True), (torch.bfloat16, 64, None)):
+        table = torch.from_numpy(rng.uniform(-1, 1, (N, D)).astype(np.float32)).to(dev)
+        table[:, 0] = torch.randint(0, 16, (N,), device=dev).float()
+        table[:, 1] = torch.minimum(table[:, 0], torch.randint(0, 16, (N,), device=dev).float())
+        table = table.to(dtype)
+        lods, ids = [], []
+        for s in range(S):
+            l = rng.integers(0, 9, Bsz)
+            lods.append(np.concatenate([[0], np.cumsum(l)]).astype(np.uint64))
+            raw = rng.zipf(1.3, int(lods[-1][-1])) % N if s % 2 == 0 else rng.integers(0, N, int(lods[-1][-1]))
+            ids.append(torch.from_numpy(raw.astype(np.int64)).to(dev))
+        hot = shard.HotRowCache(table, shard.pick_hot_ids(torch.cat(ids), 3000))
+        plain = ops.ctr_fused_emb_seqpool_cvm(table, ids, lods, ["SUM", "AVERAGE", "SQRT", "SUM"], use_cvm=use_cvm, concat=True)
+        cached = ops.ctr_fused_emb_seqpool_cvm(table, ids, lods, ["SUM", "AVERAGE", "SQRT", "SUM"], use_cvm=use_cvm, concat=True,
+                                               hot_cache=hot)
+        assert torch.equal(plain, cached)
+        p = ops.ctr_fused_emb_seqpool_cvm(table, ids, lods, "SUM", use_cvm=use_cvm, concat=True, plan_only=True, hot_cache=hot)
+        assert "hot=1" in p.kernel_names()[0]
+        p.close()
+        other = table.clone()
+        with pytest.raises(B.CtrfeError, match="same table"):
+            ops.ctr_fused_emb_seqpool_cvm([table, other, table, table], ids, lods, "SUM", use_cvm=use_cvm, hot_cache=hot)
