@@ -686,12 +686,15 @@ def sharded_cfg4_block(torch, ops, synth, dist, rank, world, dev, args):
     # ---- the denominator: the whole table on one GPU, same global batch
     one = None
     if rank == 0:
-        one = config_record(torch, ops, synth, "cfg4", dev, args)
+        one = config_record(torch, ops, synth, "cfg4", dev, args, hot_rows=min(h for h in args.hot_rows_list if h) if any(args.hot_rows_list) else 0)
     dist.barrier()
     one_l = [one]
     dist.broadcast_object_list(one_l, src=0)
     one = one_l[0]
     block["one_gpu"] = {k: one.get(k) for k in ("value", "ms_per_step", "ms_per_step_isolated_median", "skipped")}
+    one_hot = one.get("with_hot_rows")
+    if one_hot:  # the same replicas beside the whole table on one GPU: the like-for-like denominator of the hot variants
+        block["one_gpu"]["with_hot_rows"] = {k: one_hot.get(k) for k in ("value", "ms_per_step", "hot_row_cache")}
     # ---- the sharded table
     tdt = torch.float32
     Bsz = cfg.batch // world
@@ -727,6 +730,8 @@ def sharded_cfg4_block(torch, ops, synth, dist, rank, world, dev, args):
         rec = {"value": value, "ms_per_step": ms, "ms_per_step_isolated_median": m["kernel_ms_isolated_median"],
                "steps": steps, "regions": m["regions"], "kernels": m["kernels"],
                "speedup_vs_one_gpu": (value / one["value"]) if one.get("value") else None,
+               "speedup_vs_one_gpu_with_the_same_replicas": (value / one_hot["value"]) if (one_hot and n_hot and
+                                                             n_hot == one_hot["hot_row_cache"]["rows"]) else None,
                "parity": {"checked_per_rank": m["parity"]["checked"], "ok": bool(okt[0].item() > 0.5),
                           "bit_exact": bool(okt[1].item() > 0.5), "max_rel_err": float(-okt[2].item()),
                           "pinned": m["parity"]["pinned"], "note": "every rank checks a sample of ITS last timed batch "
@@ -788,6 +793,9 @@ def sharded_cfg4_block(torch, ops, synth, dist, rank, world, dev, args):
     best = max(peer, key=lambda k: peer[k]["value"])
     block.update({"value": variants[best]["value"], "ms_per_step": variants[best]["ms_per_step"], "best_variant": best,
                   "speedup_vs_one_gpu": variants[best]["speedup_vs_one_gpu"],
+                  "speedup_vs_one_gpu_with_the_same_replicas": variants[best].get("speedup_vs_one_gpu_with_the_same_replicas"),
+                  "speedup_note": "speedup_vs_one_gpu: against one GPU holding the whole 128 GB table without replicas (TLB-bound); "
+                                  "..._with_the_same_replicas: against one GPU with the same hot-row replicas beside the table",
                   "parallelism": f"table row-sharded x{world} (row r on GPU r % {world}), global batch {cfg.batch} split x{world}, "
                                  "remote rows loaded by the pooling kernel through NVLink peer mappings; no data-path collective "
                                  "(the NCCL all-to-all router is measured beside it as variants.nccl_router*)"})
