@@ -419,13 +419,14 @@ def measure_device(torch, ops, synth, cfg, W, Bsz, *, rank, world, steps, warmup
         launch(arr8, K, fl8)
         b1.record(stream)
         torch.cuda.synchronize()
-        lod_bytes = int(sum(((l.size * 4 + 15) // 16) * 16 for l in host_batches[0].lods))
+        lod_bytes = int(sum(16 + (((l.size - 1) * 2 + 15) // 16) * 16 for l in host_batches[0].lods))
         out["survey_8d"] = {
             "isolated_ms_median": float(np.median(iso8)), "isolated_value": S * Bsz * world / (float(np.median(iso8)) * 1e-3),
             "back_to_back_ms_per_step": b0.elapsed_time(b1) / K, "back_to_back_value": S * Bsz * world * K / (b0.elapsed_time(b1) * 1e-3),
             "lod_upload_bytes_per_step": lod_bytes,
-            "what": "per step: the batch's LoD offsets (validated on the host beforehand, 32-bit image in pinned memory) "
-                    "-> ONE cudaMemcpyAsync -> the plan's launch; ids resident in HBM.  isolated = CUDA events around "
+            "what": "per step: the batch's LoD offsets (validated on the host beforehand; pinned image of 16-bit sequence "
+                    "lengths, expanded to offsets by a small kernel on the copy stream) -> ONE cudaMemcpyAsync -> the "
+                    "plan's launch; ids resident in HBM.  isolated = CUDA events around "
                     "upload + launch, one step at a time, median; back to back = K steps in one ctrfe_plan_launch_many "
                     "call, uploads on the library's copy stream beside the previous batch's kernel"}
         ctx.check_ids()

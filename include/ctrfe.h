@@ -69,9 +69,11 @@ enum {
 };
 /* ---- where a slot's LoD offsets live ------------------------------------------------- */
 enum {
-  CTRFE_LOD_HOST = 0,   /* as Paddle holds them (tensor_meta.h:43); uploaded once per call,
-                           all slots in ONE async copy, no stream sync (contrast
-                           mixed_vector.cc:57-76, which syncs per sequence_pool call) */
+  CTRFE_LOD_HOST = 0,   /* as Paddle holds them (tensor_meta.h:43); validated on the host, then uploaded
+                           once per call, all slots in ONE async copy, no stream sync (contrast
+                           mixed_vector.cc:57-76, which syncs per sequence_pool call).  The image that
+                           travels holds 32-bit offsets, or -- for a plan whose sequences are all shorter
+                           than 65536 -- 16-bit lengths that a small kernel expands on the device */
   CTRFE_LOD_DEVICE = 1  /* already resident in HBM (or in pinned host memory the GPU can read); cannot be
                            validated on the host, so the kernels check every pair of offsets they read
                            (non-decreasing, below 2^31, last <= n_ids: the CheckLoD rules,

@@ -94,7 +94,13 @@ struct ctrfe_plan {
   // host-LoD plans: the pinned image the offsets were uploaded from (re-filled by ctrfe_plan_update_lod,
   // re-uploaded by CTRFE_LAUNCH_UPLOAD_LOD) and what is needed to validate new offsets
   char* host_img = nullptr;
-  size_t img_bytes = 0;
+  size_t img_bytes = 0;      // bytes of the 32-bit offsets image (device `dev`; also the pinned buffer's capacity)
+  // the compact form of the image: 16-bit sequence lengths (+ a 16-byte header per slot), expanded on the
+  // device by lod_expand_kernel.  `compact` says which form the pinned image currently holds.
+  char* dev_c = nullptr;
+  size_t c_bytes = 0;
+  bool compact = false;
+  std::vector<ctrfe::ExpandParams> expand;
   struct SlotShape { int64_t n_seg; int64_t bound; bool has_ids; };
   std::vector<SlotShape> shapes;
   cudaEvent_t lod_ready = nullptr, done = nullptr;
@@ -443,6 +449,90 @@ int stage_one_lod(int s, const uint64_t* lod, int64_t n_seg, int64_t bound, bool
   return CTRFE_OK;
 }
 
+constexpr int kNeedWide = -1;  // a sequence of 65536 ids or more: the slot cannot travel as 16-bit lengths
+
+__attribute__((target_clones("avx2", "default")))
+uint64_t lengths_and_check(const uint64_t* lod, int64_t n_seg, uint16_t* dst) {
+  uint64_t any = 0;  // OR of all differences: a bit above 15 means "too long" or "decreasing" (wrapped)
+  for (int64_t i = 0; i < n_seg; ++i) {
+    const uint64_t d = lod[i + 1] - lod[i];
+    any |= d;
+    dst[i] = static_cast<uint16_t>(d);
+  }
+  return any;
+}
+
+// One slot's host offsets -> header (first offset) + 16-bit lengths, validated like stage_one_lod.
+int stage_one_lod_compact(int s, const uint64_t* lod, int64_t n_seg, int64_t bound, bool has_ids, char* dst) {
+  memset(dst, 0, 16);
+  if (n_seg == 0) {
+    *reinterpret_cast<uint32_t*>(dst) = lod ? static_cast<uint32_t>(lod[0]) : 0u;
+    return CTRFE_OK;
+  }
+  auto* len = reinterpret_cast<uint16_t*>(dst + 16);
+  const uint64_t any = lengths_and_check(lod, n_seg, len);
+  for (int64_t i = n_seg; i < static_cast<int64_t>(align_up(static_cast<size_t>(n_seg) * 2, 16) / 2); ++i) len[i] = 0;
+  if (any >> 16) {
+    for (int64_t i = 0; i < n_seg; ++i)
+      if (lod[i + 1] < lod[i]) return fail(CTRFE_ERR_ARG, "slot %d: LoD offsets must be non-decreasing", s);
+    return kNeedWide;
+  }
+  const uint64_t last = lod[n_seg];
+  if (last >= (1ull << 31))
+    return fail(CTRFE_ERR_ARG, "slot %d: LoD offset %llu too large (a slot holds fewer than 2^31 ids)", s, (unsigned long long)last);
+  if (has_ids && static_cast<int64_t>(last) > bound)
+    return fail(CTRFE_ERR_ARG, "slot %d: the last LoD offset (%llu) exceeds the number of ids (%lld)", s,
+                (unsigned long long)last, (long long)bound);
+  if (!has_ids && static_cast<int64_t>(last) > bound)
+    return fail(CTRFE_ERR_ARG, "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)", s,
+                (long long)bound, (unsigned long long)last);
+  *reinterpret_cast<uint32_t*>(dst) = static_cast<uint32_t>(lod[0]);
+  return CTRFE_OK;
+}
+
+size_t compact_slot_bytes(int64_t n_seg) { return 16 + align_up(static_cast<size_t>(n_seg) * 2, 16); }
+
+// Stages all slots of a plan into its pinned image: the compact form when every sequence allows it,
+// else 32-bit offsets.  lods[s] = host offsets of slot s.
+int plan_stage_image(ctrfe_plan* plan, const uint64_t* const* lods) {
+  const size_t S = plan->shapes.size();
+  bool compact = plan->dev_c != nullptr;
+  if (compact) {
+    size_t off = 0;
+    for (size_t s = 0; s < S && compact; ++s) {
+      const auto& sh = plan->shapes[s];
+      const int rc = stage_one_lod_compact(static_cast<int>(s), lods[s], sh.n_seg, sh.bound, sh.has_ids, plan->host_img + off);
+      if (rc == kNeedWide) compact = false;
+      else if (rc) return rc;
+      off += compact_slot_bytes(sh.n_seg);
+    }
+  }
+  if (!compact) {
+    size_t off = 0;
+    for (size_t s = 0; s < S; ++s) {
+      const auto& sh = plan->shapes[s];
+      const int rc = stage_one_lod(static_cast<int>(s), lods[s], sh.n_seg, sh.bound, sh.has_ids,
+                                   reinterpret_cast<uint32_t*>(plan->host_img + off));
+      if (rc) return rc;
+      off += align_up(static_cast<size_t>(sh.n_seg + 1) * 4, 16);
+    }
+  }
+  plan->compact = compact;
+  return CTRFE_OK;
+}
+
+// The plan's pinned image -> its device offsets, on `st`: one copy, plus the expansion when compact.
+int plan_upload_image(ctrfe_plan* plan, cudaStream_t st) {
+  if (!plan->compact) {
+    CU(cudaMemcpyAsync(plan->dev, plan->host_img, plan->img_bytes, cudaMemcpyHostToDevice, st));
+    return CTRFE_OK;
+  }
+  CU(cudaMemcpyAsync(plan->dev_c, plan->host_img, plan->c_bytes, cudaMemcpyHostToDevice, st));
+  for (const auto& ep : plan->expand) ctrfe::lod_expand_kernel<<<static_cast<unsigned>(ep.n), 256, 0, st>>>(ep);
+  CU(cudaGetLastError());
+  return CTRFE_OK;
+}
+
 // Copies the host LoDs into one pinned image of 32-bit offsets, validating them in the same pass,
 // and re-points the descriptors at the device image.
 int plan_stage_lods(const ctrfe_fused_desc* d, char* host_img, const char* dev_img, ctrfe_plan* plan) {
@@ -750,21 +840,49 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
   if (rc) { delete plan; return rc; }
   ctx->tag_ids[plan->tag] = plan->id_src;
   if (bytes) {
+    // device: the 32-bit offsets the kernels read (+ the compact image they are expanded from);
+    // pinned host: one image, in whichever of the two forms the current offsets allow
+    size_t cb = 0;
+    for (const auto& sh : plan->shapes) cb += compact_slot_bytes(sh.n_seg);
+    const char* nocompact = getenv("CTRFE_LOD_WIDE");
+    const bool want_compact = !(nocompact && nocompact[0] == '1');
     char* dev = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
-    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&plan->host_img), bytes, cudaHostAllocDefault);
+    if (e == cudaSuccess && want_compact) e = cudaMalloc(reinterpret_cast<void**>(&plan->dev_c), cb);
+    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&plan->host_img), bytes > cb ? bytes : cb, cudaHostAllocDefault);
     if (e != cudaSuccess) {
       if (dev) cudaFree(dev);
+      if (plan->dev_c) cudaFree(plan->dev_c);
       delete plan;
       return fail(CTRFE_ERR_CUDA, "plan_create: allocating %zu bytes for the LoD image: %s", bytes, cudaGetErrorString(e));
     }
     plan->owns_dev = true;
     plan->dev = dev;
     plan->img_bytes = bytes;
-    rc = plan_stage_lods(desc, plan->host_img, dev, plan);
-    if (rc == CTRFE_OK && cudaMemcpyAsync(dev, plan->host_img, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)) != cudaSuccess)
-      rc = fail(CTRFE_ERR_CUDA, "plan_create: LoD upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-    if (rc) { cudaFree(dev); cudaFreeHost(plan->host_img); delete plan; return rc; }
+    plan->c_bytes = cb;
+    // where each slot's offsets live on the device (as before), and how to expand them from the compact image
+    std::vector<const uint64_t*> lods(desc->n_slots);
+    size_t off = 0, coff = 0;
+    for (int s = 0; s < desc->n_slots; ++s) {
+      ctrfe::SlotK& o = plan->chunks[plan->where[s].first].slots[plan->where[s].second];
+      o.lod = reinterpret_cast<const unsigned long long*>(dev + off);
+      lods[s] = desc->slots[s].lod;
+      if (s % ctrfe::kMaxSlotsPerLaunch == 0) {
+        plan->expand.emplace_back();
+        memset(&plan->expand.back(), 0, sizeof(ctrfe::ExpandParams));
+        plan->expand.back().src = plan->dev_c;
+      }
+      ctrfe::ExpandParams& ep = plan->expand.back();
+      ep.s[ep.n].dst = reinterpret_cast<unsigned long long>(dev + off);
+      ep.s[ep.n].src_off = static_cast<unsigned>(coff);
+      ep.s[ep.n].n_seg = static_cast<unsigned>(desc->slots[s].n_seg);
+      ++ep.n;
+      off += align_up(static_cast<size_t>(desc->slots[s].n_seg + 1) * 4, 16);
+      coff += compact_slot_bytes(desc->slots[s].n_seg);
+    }
+    rc = plan_stage_image(plan, lods.data());
+    if (rc == CTRFE_OK) rc = plan_upload_image(plan, static_cast<cudaStream_t>(stream));
+    if (rc) { cudaFree(dev); if (plan->dev_c) cudaFree(plan->dev_c); cudaFreeHost(plan->host_img); delete plan; return rc; }
   }
   *out = plan;
   return CTRFE_OK;
@@ -786,16 +904,9 @@ int ctrfe_plan_launch_ex(ctrfe_plan* plan, void* stream, uint32_t flags) {
 int ctrfe_plan_update_lod(ctrfe_plan* plan, const uint64_t* const* lods) {
   if (!plan || !lods) return fail(CTRFE_ERR_ARG, "plan_update_lod: null argument");
   if (!plan->host_img) return fail(CTRFE_ERR_ARG, "plan_update_lod: the plan was not created from host LoD offsets");
-  size_t off = 0;
-  for (size_t s = 0; s < plan->shapes.size(); ++s) {
-    const auto& sh = plan->shapes[s];
-    if (sh.n_seg > 0 && !lods[s]) return fail(CTRFE_ERR_ARG, "plan_update_lod: slot %zu: null LoD", s);
-    const int rc = stage_one_lod(static_cast<int>(s), lods[s], sh.n_seg, sh.bound, sh.has_ids,
-                                 reinterpret_cast<uint32_t*>(plan->host_img + off));
-    if (rc) return rc;
-    off += align_up(static_cast<size_t>(sh.n_seg + 1) * 4, 16);
-  }
-  return CTRFE_OK;
+  for (size_t s = 0; s < plan->shapes.size(); ++s)
+    if (plan->shapes[s].n_seg > 0 && !lods[s]) return fail(CTRFE_ERR_ARG, "plan_update_lod: slot %zu: null LoD", s);
+  return plan_stage_image(plan, lods);
 }
 
 int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32_t flags) {
@@ -818,7 +929,10 @@ int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32
       // kernel of batch i; the image is not overwritten before the plan's previous launch is through
       if (!p->lod_ready) CU(cudaEventCreateWithFlags(&p->lod_ready, cudaEventDisableTiming));
       if (p->done) CU(cudaStreamWaitEvent(ctx->copy_stream, p->done, 0));
-      CU(cudaMemcpyAsync(p->dev, p->host_img, p->img_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+      {
+        const int urc = plan_upload_image(p, ctx->copy_stream);
+        if (urc) return urc;
+      }
       CU(cudaEventRecord(p->lod_ready, ctx->copy_stream));
       CU(cudaStreamWaitEvent(st, p->lod_ready, 0));
     }
@@ -840,6 +954,7 @@ int ctrfe_plan_destroy(ctrfe_plan* plan) {
     cudaFree(plan->dev);
   }
   if (plan->host_img) cudaFreeHost(plan->host_img);
+  if (plan->dev_c) cudaFree(plan->dev_c);
   if (plan->lod_ready) cudaEventDestroy(plan->lod_ready);
   if (plan->done) cudaEventDestroy(plan->done);
   delete plan;

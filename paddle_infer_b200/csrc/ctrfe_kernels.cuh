@@ -752,6 +752,67 @@ __global__ void cvm_f64_kernel(const double* __restrict__ x, long long rows, int
   y[t] = v;
 }
 
+// ---------------------------------------------------------------------------------------
+// LoD offsets of a plan travel to the device as 16-bit sequence LENGTHS when every sequence is shorter
+// than 65536 (a quarter of the 64-bit offsets Paddle holds, half of a 32-bit image): per slot a 16-byte
+// header holding the first offset, then n_seg lengths.  This kernel turns them back into the 32-bit
+// offsets the pooling kernels read: one CTA per slot, eight lengths per thread and step.
+// ---------------------------------------------------------------------------------------
+struct ExpandSlot {
+  unsigned long long dst;  // device uint32 [n_seg + 1]
+  unsigned src_off;        // byte offset of the slot's header in the compact image
+  unsigned n_seg;
+};
+struct ExpandParams {
+  const char* src;
+  int n;
+  int reserved;
+  ExpandSlot s[kMaxSlotsPerLaunch];
+};
+
+__global__ void __launch_bounds__(256) lod_expand_kernel(const __grid_constant__ ExpandParams p) {
+  const ExpandSlot& sl = p.s[blockIdx.x];
+  const unsigned n_seg = sl.n_seg;
+  const unsigned base = *reinterpret_cast<const unsigned*>(p.src + sl.src_off);
+  const uint4* len8 = reinterpret_cast<const uint4*>(p.src + sl.src_off + 16);
+  unsigned* dst = reinterpret_cast<unsigned*>(sl.dst);
+  __shared__ unsigned s_warp[8];
+  __shared__ unsigned s_carry;
+  const unsigned tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
+  if (tid == 0) { dst[0] = base; s_carry = base; }
+  __syncthreads();
+  for (unsigned c0 = 0; c0 < n_seg; c0 += 2048u) {
+    const unsigned i0 = c0 + tid * 8u;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (i0 < n_seg) v = __ldg(len8 + (i0 >> 3));
+    unsigned l[8] = {v.x & 0xffffu, v.x >> 16, v.y & 0xffffu, v.y >> 16, v.z & 0xffffu, v.z >> 16, v.w & 0xffffu, v.w >> 16};
+    unsigned run = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (i0 + k >= n_seg) l[k] = 0u;
+      run += l[k];
+      l[k] = run;  // inclusive prefix inside the thread
+    }
+    unsigned incl = run;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= static_cast<unsigned>(d)) incl += t;
+    }
+    if (lane == 31u) s_warp[w] = incl;
+    __syncthreads();
+    unsigned before = s_carry;
+    for (unsigned q = 0; q < w; ++q) before += s_warp[q];
+    const unsigned off = before + incl - run;  // offset of this thread's first sequence
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (i0 + k < n_seg) dst[i0 + k + 1] = off + l[k];
+    __syncthreads();
+    if (tid == 255u) s_carry = off + run;
+    __syncthreads();
+  }
+}
+
 // ids [K, W] row-major -> W contiguous arrays of K ids (column w at out + w * K): lets an Ids tensor
 // whose last dimension is wider than 1 (fused_embedding_seq_pool, refer.h:477-528 index_width) feed
 // the pooling kernels, which want one contiguous id run per slot.

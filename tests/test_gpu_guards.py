@@ -277,3 +277,44 @@ def test_hot_rows_beside_an_unsharded_table_change_nothing(env):
         other = table.clone()
         with pytest.raises(B.CtrfeError, match="same table"):
             ops.ctr_fused_emb_seqpool_cvm([table, other, table, table], ids, lods, "SUM", use_cvm=use_cvm, hot_cache=hot)
+
+
+def test_plan_lod_image_compact_and_wide_forms(env):
+    """A plan's host LoD travels as 16-bit lengths (expanded on the device) when every sequence is
+    shorter than 65536, else as 32-bit offsets; ctrfe_plan_update_lod may flip between the forms and
+    CTRFE_LAUNCH_UPLOAD_LOD re-uploads whichever is current.  Same bits as the one-shot call."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(77)
+    N, D = 5000, 16
+    table = torch.from_numpy(rng.uniform(-1, 1, (N, D)).astype(np.float32)).to(dev)
+    n_seg = 2500  # more than one 2048-sequence step of the expansion kernel
+
+    def make(long_seq):
+        l = rng.integers(0, 7, n_seg)
+        if long_seq:
+            l[1234] = 70000
+        lod = np.concatenate([[3], 3 + np.cumsum(l)]).astype(np.uint64)  # a LoD need not start at 0 here
+        return lod
+
+    lod_a, lod_b, lod_c = make(False), make(True), make(False)
+    n_ids = int(max(lod_a[-1], lod_b[-1], lod_c[-1]))
+    ids = torch.from_numpy(rng.integers(0, N, n_ids).astype(np.int64)).to(dev)
+    plan = ops.ctr_fused_emb_seqpool_cvm(table, [ids, ids], [lod_a, lod_a], ["SUM", "SQRT"], use_cvm=None, plan_only=True)
+    for lod in (lod_a, lod_b, lod_c, lod_b, lod_a):
+        want = ops.ctr_fused_emb_seqpool_cvm(table, [ids, ids], [lod, lod], ["SUM", "SQRT"], use_cvm=None)
+        plan.update_lod([lod, lod])
+        for o in plan.outs:
+            o.fill_(float("nan"))
+        ops.launch_many([plan], upload_lod=True)
+        torch.cuda.synchronize()
+        for g, w in zip(plan.outs, want):
+            assert torch.equal(g, w)
+    bad = lod_a.copy()
+    bad[100] = bad[101] + 1
+    with pytest.raises(B.CtrfeError, match="non-decreasing"):
+        plan.update_lod([lod_a, bad])
+    over = lod_a.copy()
+    over[-1] = n_ids + 1
+    with pytest.raises(B.CtrfeError, match="exceeds the number of ids"):
+        plan.update_lod([over, lod_a])
+    plan.close()
