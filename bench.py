@@ -419,7 +419,8 @@ def measure_device(torch, ops, synth, cfg, W, Bsz, *, rank, world, steps, warmup
         launch(arr8, K, fl8)
         b1.record(stream)
         torch.cuda.synchronize()
-        lod_bytes = int(sum(16 + (((l.size - 1) * 2 + 15) // 16) * 16 for l in host_batches[0].lods))
+        lod_bytes = int(sum((((l.size + 2046) // 2048 * 4 + 15) // 16) * 16 + (((l.size - 1) * 2 + 15) // 16) * 16
+                            for l in host_batches[0].lods))
         out["survey_8d"] = {
             "isolated_ms_median": float(np.median(iso8)), "isolated_value": S * Bsz * world / (float(np.median(iso8)) * 1e-3),
             "back_to_back_ms_per_step": b0.elapsed_time(b1) / K, "back_to_back_value": S * Bsz * world * K / (b0.elapsed_time(b1) * 1e-3),

@@ -462,14 +462,20 @@ uint64_t lengths_and_check(const uint64_t* lod, int64_t n_seg, uint16_t* dst) {
   return any;
 }
 
-// One slot's host offsets -> header (first offset) + 16-bit lengths, validated like stage_one_lod.
+size_t compact_chunks(int64_t n_seg) { return n_seg > 0 ? (static_cast<size_t>(n_seg) + ctrfe::kExpandChunk - 1) / ctrfe::kExpandChunk : 1; }
+size_t compact_base_bytes(int64_t n_seg) { return align_up(compact_chunks(n_seg) * 4, 16); }
+
+// One slot's host offsets -> chunk bases (the offset every kExpandChunk-th sequence starts at) + 16-bit
+// lengths, validated like stage_one_lod.
 int stage_one_lod_compact(int s, const uint64_t* lod, int64_t n_seg, int64_t bound, bool has_ids, char* dst) {
-  memset(dst, 0, 16);
+  auto* bases = reinterpret_cast<uint32_t*>(dst);
+  const size_t bb = compact_base_bytes(n_seg);
+  memset(dst, 0, bb);
   if (n_seg == 0) {
-    *reinterpret_cast<uint32_t*>(dst) = lod ? static_cast<uint32_t>(lod[0]) : 0u;
+    bases[0] = lod ? static_cast<uint32_t>(lod[0]) : 0u;
     return CTRFE_OK;
   }
-  auto* len = reinterpret_cast<uint16_t*>(dst + 16);
+  auto* len = reinterpret_cast<uint16_t*>(dst + bb);
   const uint64_t any = lengths_and_check(lod, n_seg, len);
   for (int64_t i = n_seg; i < static_cast<int64_t>(align_up(static_cast<size_t>(n_seg) * 2, 16) / 2); ++i) len[i] = 0;
   if (any >> 16) {
@@ -486,11 +492,11 @@ int stage_one_lod_compact(int s, const uint64_t* lod, int64_t n_seg, int64_t bou
   if (!has_ids && static_cast<int64_t>(last) > bound)
     return fail(CTRFE_ERR_ARG, "slot %d: the first dimension of Input(X) (%lld) must be >= the last LoD offset (%llu)", s,
                 (long long)bound, (unsigned long long)last);
-  *reinterpret_cast<uint32_t*>(dst) = static_cast<uint32_t>(lod[0]);
+  for (size_t c = 0; c < compact_chunks(n_seg); ++c) bases[c] = static_cast<uint32_t>(lod[c * ctrfe::kExpandChunk]);
   return CTRFE_OK;
 }
 
-size_t compact_slot_bytes(int64_t n_seg) { return 16 + align_up(static_cast<size_t>(n_seg) * 2, 16); }
+size_t compact_slot_bytes(int64_t n_seg) { return compact_base_bytes(n_seg) + align_up(static_cast<size_t>(n_seg) * 2, 16); }
 
 // Stages all slots of a plan into its pinned image: the compact form when every sequence allows it,
 // else 32-bit offsets.  lods[s] = host offsets of slot s.
@@ -528,7 +534,7 @@ int plan_upload_image(ctrfe_plan* plan, cudaStream_t st) {
     return CTRFE_OK;
   }
   CU(cudaMemcpyAsync(plan->dev_c, plan->host_img, plan->c_bytes, cudaMemcpyHostToDevice, st));
-  for (const auto& ep : plan->expand) ctrfe::lod_expand_kernel<<<static_cast<unsigned>(ep.n), 256, 0, st>>>(ep);
+  for (const auto& ep : plan->expand) ctrfe::lod_expand_kernel<<<static_cast<unsigned>(ep.n_blocks), 256, 0, st>>>(ep);
   CU(cudaGetLastError());
   return CTRFE_OK;
 }
@@ -874,8 +880,11 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
       }
       ctrfe::ExpandParams& ep = plan->expand.back();
       ep.s[ep.n].dst = reinterpret_cast<unsigned long long>(dev + off);
-      ep.s[ep.n].src_off = static_cast<unsigned>(coff);
+      ep.s[ep.n].base_off = static_cast<unsigned>(coff);
+      ep.s[ep.n].len_off = static_cast<unsigned>(coff + compact_base_bytes(desc->slots[s].n_seg));
       ep.s[ep.n].n_seg = static_cast<unsigned>(desc->slots[s].n_seg);
+      ep.s[ep.n].first_block = static_cast<unsigned>(ep.n_blocks);
+      ep.n_blocks += static_cast<int>(compact_chunks(desc->slots[s].n_seg));
       ++ep.n;
       off += align_up(static_cast<size_t>(desc->slots[s].n_seg + 1) * 4, 16);
       coff += compact_slot_bytes(desc->slots[s].n_seg);

@@ -754,63 +754,64 @@ __global__ void cvm_f64_kernel(const double* __restrict__ x, long long rows, int
 
 // ---------------------------------------------------------------------------------------
 // LoD offsets of a plan travel to the device as 16-bit sequence LENGTHS when every sequence is shorter
-// than 65536 (a quarter of the 64-bit offsets Paddle holds, half of a 32-bit image): per slot a 16-byte
-// header holding the first offset, then n_seg lengths.  This kernel turns them back into the 32-bit
-// offsets the pooling kernels read: one CTA per slot, eight lengths per thread and step.
+// than 65536 (a quarter of the 64-bit offsets Paddle holds, half of a 32-bit image): per slot the
+// 32-bit offset at which every chunk of kExpandChunk sequences starts (the host has them anyway), then
+// n_seg lengths.  This kernel turns them back into the 32-bit offsets the pooling kernels read: one CTA
+// per chunk, eight lengths per thread, one block-wide scan, no dependence between CTAs.
 // ---------------------------------------------------------------------------------------
+constexpr unsigned kExpandChunk = 2048;  // sequences per CTA of lod_expand_kernel (256 threads x 8)
 struct ExpandSlot {
   unsigned long long dst;  // device uint32 [n_seg + 1]
-  unsigned src_off;        // byte offset of the slot's header in the compact image
+  unsigned base_off;       // byte offset of the slot's chunk bases (uint32 per chunk) in the compact image
+  unsigned len_off;        // byte offset of the slot's lengths (uint16 per sequence, 16-byte aligned)
   unsigned n_seg;
+  unsigned first_block;    // blockIdx.x of the slot's first chunk
 };
 struct ExpandParams {
   const char* src;
-  int n;
-  int reserved;
+  int n;           // slots
+  int n_blocks;    // chunks of all slots
   ExpandSlot s[kMaxSlotsPerLaunch];
 };
 
 __global__ void __launch_bounds__(256) lod_expand_kernel(const __grid_constant__ ExpandParams p) {
-  const ExpandSlot& sl = p.s[blockIdx.x];
+  int j = 0;
+  while (j + 1 < p.n && p.s[j + 1].first_block <= blockIdx.x) ++j;
+  const ExpandSlot& sl = p.s[j];
   const unsigned n_seg = sl.n_seg;
-  const unsigned base = *reinterpret_cast<const unsigned*>(p.src + sl.src_off);
-  const uint4* len8 = reinterpret_cast<const uint4*>(p.src + sl.src_off + 16);
+  const unsigned chunk = blockIdx.x - sl.first_block;
+  const unsigned c0 = chunk * kExpandChunk;
+  const unsigned base = __ldg(reinterpret_cast<const unsigned*>(p.src + sl.base_off) + chunk);
+  const uint4* len8 = reinterpret_cast<const uint4*>(p.src + sl.len_off);
   unsigned* dst = reinterpret_cast<unsigned*>(sl.dst);
   __shared__ unsigned s_warp[8];
-  __shared__ unsigned s_carry;
   const unsigned tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
-  if (tid == 0) { dst[0] = base; s_carry = base; }
-  __syncthreads();
-  for (unsigned c0 = 0; c0 < n_seg; c0 += 2048u) {
-    const unsigned i0 = c0 + tid * 8u;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (i0 < n_seg) v = __ldg(len8 + (i0 >> 3));
-    unsigned l[8] = {v.x & 0xffffu, v.x >> 16, v.y & 0xffffu, v.y >> 16, v.z & 0xffffu, v.z >> 16, v.w & 0xffffu, v.w >> 16};
-    unsigned run = 0;
+  if (chunk == 0 && tid == 0) dst[0] = base;
+  const unsigned i0 = c0 + tid * 8u;
+  uint4 v = make_uint4(0u, 0u, 0u, 0u);
+  if (i0 < n_seg) v = __ldg(len8 + (i0 >> 3));
+  unsigned l[8] = {v.x & 0xffffu, v.x >> 16, v.y & 0xffffu, v.y >> 16, v.z & 0xffffu, v.z >> 16, v.w & 0xffffu, v.w >> 16};
+  unsigned run = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      if (i0 + k >= n_seg) l[k] = 0u;
-      run += l[k];
-      l[k] = run;  // inclusive prefix inside the thread
-    }
-    unsigned incl = run;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= static_cast<unsigned>(d)) incl += t;
-    }
-    if (lane == 31u) s_warp[w] = incl;
-    __syncthreads();
-    unsigned before = s_carry;
-    for (unsigned q = 0; q < w; ++q) before += s_warp[q];
-    const unsigned off = before + incl - run;  // offset of this thread's first sequence
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-      if (i0 + k < n_seg) dst[i0 + k + 1] = off + l[k];
-    __syncthreads();
-    if (tid == 255u) s_carry = off + run;
-    __syncthreads();
+  for (int k = 0; k < 8; ++k) {
+    if (i0 + k >= n_seg) l[k] = 0u;
+    run += l[k];
+    l[k] = run;  // inclusive prefix inside the thread
   }
+  unsigned incl = run;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= static_cast<unsigned>(d)) incl += t;
+  }
+  if (lane == 31u) s_warp[w] = incl;
+  __syncthreads();
+  unsigned before = base;
+  for (unsigned q = 0; q < w; ++q) before += s_warp[q];
+  const unsigned off = before + incl - run;  // offset of this thread's first sequence
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (i0 + k < n_seg) dst[i0 + k + 1] = off + l[k];
 }
 
 // ids [K, W] row-major -> W contiguous arrays of K ids (column w at out + w * K): lets an Ids tensor
