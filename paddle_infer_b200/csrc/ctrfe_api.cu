@@ -851,7 +851,10 @@ int ctrfe_plan_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, void* stream
     size_t cb = 0;
     for (const auto& sh : plan->shapes) cb += compact_slot_bytes(sh.n_seg);
     const char* nocompact = getenv("CTRFE_LOD_WIDE");
-    const bool want_compact = !(nocompact && nocompact[0] == '1');
+    // (below 256 KB the extra launch of the expansion kernel costs more than the bytes it saves: cfg1)
+    const char* cmin = getenv("CTRFE_LOD_COMPACT_MIN");  // bytes of the 32-bit image from which the compact form is used
+    const size_t compact_min = cmin && cmin[0] ? static_cast<size_t>(atoll(cmin)) : (256u << 10);
+    const bool want_compact = !(nocompact && nocompact[0] == '1') && bytes >= compact_min;
     char* dev = nullptr;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&dev), bytes);
     if (e == cudaSuccess && want_compact) e = cudaMalloc(reinterpret_cast<void**>(&plan->dev_c), cb);
@@ -931,26 +934,50 @@ int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32
   const bool upload = (flags & CTRFE_LAUNCH_UPLOAD_LOD) != 0;
   auto st = static_cast<cudaStream_t>(stream);
   if (upload && !ctx->copy_stream) CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-  for (int i = 0; i < n; ++i) {
-    ctrfe_plan* p = plans[i];
-    if (upload && p->host_img) {
-      // the offsets travel on the context's copy stream, so the upload of batch i + 1 runs beside the
-      // kernel of batch i; the image is not overwritten before the plan's previous launch is through
+  if (!upload) {
+    for (int i = 0; i < n; ++i) {
+      const int rc = launch_plan(*plans[i], st, overlap);
+      if (rc) return rc;
+    }
+    return CTRFE_OK;
+  }
+  // With uploads the list is walked in blocks of up to kUploadBlock distinct plans: the block's LoD
+  // images go up on the context's copy stream (beside the previous block's kernels), `stream` waits
+  // ONCE for the block's last upload, then the block's kernels follow each other without anything in
+  // between -- an event wait in front of a kernel would cost it the overlap with its predecessor.
+  constexpr int kUploadBlock = 8;
+  int i = 0;
+  while (i < n) {
+    int j = i;
+    while (j < n && j - i < kUploadBlock) {
+      bool repeat = false;
+      for (int q = i; q < j; ++q) repeat |= plans[q] == plans[j];
+      if (repeat) break;
+      ++j;
+    }
+    cudaEvent_t last_ready = nullptr;
+    for (int q = i; q < j; ++q) {
+      ctrfe_plan* p = plans[q];
+      if (!p->host_img) continue;
+      // the image is not overwritten before the plan's previous launch is through
       if (!p->lod_ready) CU(cudaEventCreateWithFlags(&p->lod_ready, cudaEventDisableTiming));
       if (p->done) CU(cudaStreamWaitEvent(ctx->copy_stream, p->done, 0));
-      {
-        const int urc = plan_upload_image(p, ctx->copy_stream);
-        if (urc) return urc;
-      }
+      const int urc = plan_upload_image(p, ctx->copy_stream);
+      if (urc) return urc;
       CU(cudaEventRecord(p->lod_ready, ctx->copy_stream));
-      CU(cudaStreamWaitEvent(st, p->lod_ready, 0));
+      last_ready = p->lod_ready;
     }
-    const int rc = launch_plan(*p, st, overlap);
-    if (rc) return rc;
-    if (upload && p->host_img) {
-      if (!p->done) CU(cudaEventCreateWithFlags(&p->done, cudaEventDisableTiming));
-      CU(cudaEventRecord(p->done, st));
+    if (last_ready) CU(cudaStreamWaitEvent(st, last_ready, 0));  // the copy stream is in order: the last upload covers the block
+    for (int q = i; q < j; ++q) {
+      ctrfe_plan* p = plans[q];
+      const int rc = launch_plan(*p, st, overlap);
+      if (rc) return rc;
+      if (p->host_img) {
+        if (!p->done) CU(cudaEventCreateWithFlags(&p->done, cudaEventDisableTiming));
+        CU(cudaEventRecord(p->done, st));
+      }
     }
+    i = j;
   }
   return CTRFE_OK;
 }

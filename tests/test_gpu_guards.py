@@ -299,7 +299,12 @@ def test_plan_lod_image_compact_and_wide_forms(env):
     lod_a, lod_b, lod_c = make(False), make(True), make(False)
     n_ids = int(max(lod_a[-1], lod_b[-1], lod_c[-1]))
     ids = torch.from_numpy(rng.integers(0, N, n_ids).astype(np.int64)).to(dev)
-    plan = ops.ctr_fused_emb_seqpool_cvm(table, [ids, ids], [lod_a, lod_a], ["SUM", "SQRT"], use_cvm=None, plan_only=True)
+    import os
+    os.environ["CTRFE_LOD_COMPACT_MIN"] = "0"  # small images take the compact form too (default: from 256 KB)
+    try:
+        plan = ops.ctr_fused_emb_seqpool_cvm(table, [ids, ids], [lod_a, lod_a], ["SUM", "SQRT"], use_cvm=None, plan_only=True)
+    finally:
+        del os.environ["CTRFE_LOD_COMPACT_MIN"]
     for lod in (lod_a, lod_b, lod_c, lod_b, lod_a):
         want = ops.ctr_fused_emb_seqpool_cvm(table, [ids, ids], [lod, lod], ["SUM", "SQRT"], use_cvm=None)
         plan.update_lod([lod, lod])
