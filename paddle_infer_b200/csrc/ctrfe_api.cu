@@ -933,7 +933,13 @@ int ctrfe_plan_launch_many(ctrfe_plan* const* plans, int n, void* stream, uint32
   const bool overlap = (flags & CTRFE_LAUNCH_OVERLAP_PREVIOUS) != 0;
   const bool upload = (flags & CTRFE_LAUNCH_UPLOAD_LOD) != 0;
   auto st = static_cast<cudaStream_t>(stream);
-  if (upload && !ctx->copy_stream) CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  if (upload && !ctx->copy_stream) {
+    // highest priority: the small expansion kernels of the next block must get SM slots while a chain
+    // of overlapped pooling kernels keeps every SM full
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&ctx->copy_stream, cudaStreamNonBlocking, hi));
+  }
   if (!upload) {
     for (int i = 0; i < n; ++i) {
       const int rc = launch_plan(*plans[i], st, overlap);
