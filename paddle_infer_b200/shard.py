@@ -294,9 +294,13 @@ class RoutedForward:
     the exchanges are torch.distributed all_to_all_single (NCCL).  One host synchronisation per call
     (the counts), as in the reference."""
 
-    def __init__(self, table: "ShardedTable", dedup: bool = False):
+    def __init__(self, table: "ShardedTable", dedup: bool = False, gather=None, pool=None):
+        """`gather(local_shard, rows)` and `pool(rows_in, back_slots, lods, pooltype, **kw)` default to
+        the library's kernels; tests on CPU (gloo) pass stand-ins to drive the routing and the three
+        exchanges without a GPU."""
         self.table, self.dedup = table, dedup
         self.G, self.rank = table.n_shards, table.rank
+        self._gather, self._pool = gather, pool
 
     def __call__(self, Ids: Sequence, lods: Sequence, pooltype="SUM", *, use_cvm=True, concat=True, pad_value=0.0,
                  out=None, check: bool = False):
@@ -319,7 +323,9 @@ class RoutedForward:
         sc, rc = send_counts.tolist(), recv_counts.tolist()   # the one host synchronisation
         recv_rows = torch.empty(sum(rc), dtype=torch.int64, device=all_ids.device)
         dist.all_to_all_single(recv_rows, send_rows, output_split_sizes=rc, input_split_sizes=sc, group=grp)
-        rows_out = ops.lookup_table_v2(self.table.local, recv_rows, check=False)      # owner-side gather
+        gather = self._gather or (lambda w, r: ops.lookup_table_v2(w, r, check=False))
+        pool = self._pool or ops.ctr_fused_emb_seqpool_cvm
+        rows_out = gather(self.table.local, recv_rows)                                # owner-side gather
         rows_in = torch.empty((sum(sc), self.table.dim), dtype=self.table.dtype, device=all_ids.device)
         dist.all_to_all_single(rows_in, rows_out, output_split_sizes=sc, input_split_sizes=rc, group=grp)
         # position of every id's row in rows_in: the inverse of the bucket permutation (and of the dedup)
@@ -327,5 +333,5 @@ class RoutedForward:
         pos[order] = torch.arange(order.numel(), device=order.device)
         back = pos[inverse] if inverse is not None else pos
         back_slots = list(torch.split(back, sizes))
-        return ops.ctr_fused_emb_seqpool_cvm(rows_in, back_slots, lods, pooltype, use_cvm=use_cvm, concat=concat,
-                                             pad_value=pad_value, out=out, check=check)
+        return pool(rows_in, back_slots, lods, pooltype, use_cvm=use_cvm, concat=concat,
+                    pad_value=pad_value, out=out, check=check)

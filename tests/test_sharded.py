@@ -92,6 +92,70 @@ def test_two_rank_gloo_sharding():
     assert sorted(res) == [(0, "ok"), (1, "ok")], res
 
 
+def _gloo_router_worker(rank, world, port, q, dedup):
+    """The all-to-all router (shard.RoutedForward) over gloo: bucketing by owner, the three counted
+    exchanges and the inverse permutation are the product's code; the owner-side gather and the
+    pooling are numpy / oracle stand-ins, since there is no GPU here."""
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        sys.path.insert(0, ROOT)
+        import types
+        import torch
+        import torch.distributed as dist
+        from benchtools import synth
+        from oracle import oracle as O
+        from paddle_infer_b200 import shard
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        N, D, seed, S = 3001, 8, 21, 3
+        mine = shard.global_rows_of_shard(N, world, rank)
+        local = torch.from_numpy(synth.table_rows_numpy(seed, mine, D, "f32"))
+        table = types.SimpleNamespace(n_shards=world, rank=rank, group=dist.group.WORLD, local=local, dim=D,
+                                      dtype=torch.float32)
+
+        def pool(rows_in, back_slots, lods, pooltype, **kw):
+            outs = O.fused_forward([rows_in.numpy()] * len(back_slots), [b.numpy() for b in back_slots], lods,
+                                   [pooltype] * len(back_slots), cvm_mode=O.CVM_USE)
+            return np.concatenate(outs, axis=1)
+
+        router = shard.RoutedForward(table, dedup=dedup, gather=lambda w, r: w[r], pool=pool)
+        rng = np.random.default_rng(500 + rank)          # every rank its own batch, ragged, one slot empty
+        lods, Ids = [], []
+        for s_ in range(S):
+            lens = rng.integers(0, 6, 40) if s_ != 1 or rank != 0 else np.zeros(40, np.int64)
+            lods.append(np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64))
+            Ids.append(torch.from_numpy(rng.integers(0, 64 if s_ == 0 else N, int(lods[-1][-1])).astype(np.int64)))
+        got = router(Ids, lods, "SUM")
+        full = synth.table_rows_numpy(seed, np.arange(N), D, "f32")
+        want = np.concatenate(O.fused_forward([full] * S, [i.numpy() for i in Ids], lods, ["SUM"] * S,
+                                              cvm_mode=O.CVM_USE), axis=1)
+        np.testing.assert_array_equal(got, want)
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "FAIL: " + traceback.format_exc()))
+        raise e
+
+
+@pytest.mark.parametrize("dedup", [False, True])
+def test_two_rank_gloo_router(dedup):
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_router_worker, args=(r, 2, port, q, dedup)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], res
+
+
 # ------------------------------------------------------------------ the kernel path, one GPU
 @pytest.mark.gpu
 @pytest.mark.parametrize("G", [2, 4, 8])
