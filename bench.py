@@ -248,7 +248,7 @@ def run_reference(args):
             "config": _config_block(cfg, 1, f"host threads x{base['cores']} (the reference's CPU kernels; rank 0 only)"),
             "cpu_baseline": base,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     return 0
 
 
@@ -885,11 +885,14 @@ def run_ours(args):
     elif rank == 0:
         line["cpu_baseline"] = None
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+_JSON_OUT = None
 
 
 def main():
@@ -920,6 +923,12 @@ def main():
     args.hot_rows_list = [int(x) for x in str(args.hot_rows).split(",") if x != ""]
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps
+    # stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner,
+    # compiler chatter from build()) are sent to stderr for the length of the run
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     return run_reference(args) if args.impl == "reference" else run_ours(args)
 
 
