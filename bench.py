@@ -41,6 +41,21 @@ if ROOT not in sys.path:
 
 METRIC = "pooled rows/sec (gather+seqpool+CVM)"
 UNIT = "pooled_rows/s"
+# e2e: which form of the host-buffer call `--e2e-mode auto` takes at N GPUs (mode, ids width, requests in
+# flight, slot groups) -- measured, see DESIGN.md section 6 -- and the forms reported beside it at N = 1
+# (this box's PCIe link is close to half duplex for GPU-initiated traffic -- uploads and SM reads of host memory
+# stall while rows stream down, profiles/r2_e2e_sweep.txt -- so a step costs about the SUM of its bytes at
+# 56 GB/s: 32-bit ids (the table has < 2^31 rows; lookup_table_v2 takes them) and a second request in flight
+# are what is left.  N = 1: zero_copy int64 0.59 ms, int32 0.53, int32 with 2 in flight 0.465; pipe 0.64 - 0.69)
+E2E_AUTO = {1: ("zero_copy", "int32", 2, 3), 2: ("zero_copy", "int32", 2, 3), 4: ("pipe", "int32", 1, 3), 8: ("pipe", "int32", 1, 3)}
+E2E_VARIANTS = {
+    "zero_copy_int64": dict(mode="zero_copy", ids="int64", inflight=1),
+    "zero_copy_int32": dict(mode="zero_copy", ids="int32", inflight=1),
+    "zero_copy_int32_3_in_flight": dict(mode="zero_copy", ids="int32", inflight=3),
+    "pipe_int64_3_groups": dict(mode="pipe", ids="int64", inflight=1, groups=3),
+    "pipe_int32_3_groups": dict(mode="pipe", ids="int32", inflight=1, groups=3),
+    "pipe_int32_1_group_2_in_flight": dict(mode="pipe", ids="int32", inflight=2, groups=1),
+}
 N_BATCHES = 16  # distinct pre-generated batches the timed loop rotates through
 NVLINK_PEAK_GBS = 770.0  # B200_PROFILING.md: measured peer copy, per direction per GPU
 
@@ -534,143 +549,164 @@ def config_record(torch, ops, synth, name, dev, args, traffic_key=None, hot_rows
     return rec
 
 
-def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
-    """The same metric through the host-buffer call: every step reads that step's ids + LoD
-    offsets from pinned host memory and lands the pooled rows in pinned host memory."""
-    if args.e2e_mode == "auto":
-        # the SMs' own PCIe traffic (zero_copy) wins on one or two GPUs; with every GPU of the box busy
-        # the copy engines (pipe) do better -- both measured, see profiles/README.md
-        args.e2e_mode = "zero_copy" if world <= 2 else "pipe"
+def _e2e_variant(torch, ops, cfg, W, m, Bsz, world, dist, args, dev, *, mode, ids="int64", inflight=1, groups=3, ramp=False,
+                 direct_in=False, direct_out=False, Ke=40, sync_ranks=True):
+    """One timed loop of host-buffer requests: every request reads that step's ids + LoD offsets from
+    pinned host memory and lands the pooled rows in pinned host memory.  `inflight` requests are in
+    flight at a time (1: a request is collected before the next is submitted)."""
+    from collections import deque
     S = cfg.slots
     host_batches, ctx = m["_host_batches"], m["_ctx"]
     n_batches = len(host_batches)
     stream = torch.cuda.current_stream(dev)
-    Ke = max(3, min(args.steps, args.e2e_steps))
     max_ids = max(int(i.size) for hb in host_batches for i in hb.ids)
-    fe = None if args.e2e_mode == "pipe" else ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx,
-                                                               mode=args.e2e_mode)
-    pinned = None if args.e2e_mode == "pipe" else [[torch.from_numpy(i).pin_memory() for i in hb.ids] for hb in host_batches]
-    if args.e2e_mode == "pipe":
-        fe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups,
-                          direct_out=args.e2e_direct_out)
+    id_np = np.int32 if ids == "int32" else np.int64
+    F = max(1, int(inflight))
+    if mode == "pipe":
+        units = [ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=groups, direct_out=direct_out,
+                              direct_in=direct_in, ramp=ramp, ids_dtype=ids) for _ in range(F)]
         # a request's ids sit in ONE pinned feed buffer, slot after slot (per-slot views of it), its LoD
         # offsets in another; the pointer tables are built once per buffer set, as a serving loop would
-        preps = []
+        preps, keep = [], []
         for hb in host_batches:
-            feed = torch.from_numpy(np.concatenate(hb.ids)).pin_memory()
+            feed = torch.from_numpy(np.concatenate(hb.ids).astype(id_np)).pin_memory()
             offs = np.concatenate([[0], np.cumsum([i.size for i in hb.ids])])
-            views = [feed[int(offs[s]):int(offs[s + 1])] for s in range(S)]
             lod_feed = torch.from_numpy(np.stack([l.astype(np.int64) for l in hb.lods])).pin_memory()
-            preps.append(fe.prepare(views, [lod_feed[s] for s in range(S)]))
-        step_fns = [(lambda b=b: fe.run_prepared(preps[b])) for b in range(n_batches)]
-        h2d_of = None
-    elif args.e2e_mode == "zero_copy":
-        e2e_lods = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
-        calls = [fe.bind(pinned[b], e2e_lods[b]) for b in range(n_batches)]
-        step_fns = [c.run for c in calls]
-        h2d_of = [c.h2d_bytes for c in calls]
+            keep.append((feed, lod_feed))
+            preps.append(units[0].prepare([feed[int(offs[s]):int(offs[s + 1])] for s in range(S)], [lod_feed[s] for s in range(S)]))
+
+        def submit(i):
+            u = units[i % F]
+            u.run_prepared(preps[i % n_batches], wait=None)
+            return u
+
+        def collect(u):
+            u.wait()
+
+        def h2d_of(i):
+            return preps[i % n_batches][4]
+
+        def result_of(i):
+            return [units[i % F].host_out[s] for s in range(S)]
     else:
-        step_fns = [(lambda b=b: fe.run(pinned[b], host_batches[b].lods)) for b in range(n_batches)]
-        h2d_of = [sum(i.numel() * 8 for i in pinned[b]) + sum(l.size * 8 for l in host_batches[b].lods)
-                  for b in range(n_batches)]
-    for i in range(3):
-        step_fns[i % n_batches]()
-    if dist is not None:
+        units = [ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, mode=mode) for _ in range(F)]
+        pinned = [[torch.from_numpy(i.astype(id_np)).pin_memory() for i in hb.ids] for hb in host_batches]
+        if mode == "zero_copy":
+            lods_p = [[torch.from_numpy(l.astype(np.int64)).pin_memory() for l in hb.lods] for hb in host_batches]
+            calls = [[units[j].bind(pinned[b], lods_p[b]) for j in range(F)] for b in range(n_batches)]
+
+            def submit(i):
+                c = calls[i % n_batches][i % F]
+                return (c, c.submit(overlap_previous=F > 1))
+
+            def collect(h):
+                h[0].result(h[1])
+
+            def h2d_of(i):
+                return calls[i % n_batches][0].h2d_bytes
+        else:
+            def submit(i):
+                units[0].run(pinned[i % n_batches], host_batches[i % n_batches].lods)
+                return None
+
+            def collect(h):
+                pass
+
+            def h2d_of(i):
+                b = i % n_batches
+                return sum(t.numel() * t.element_size() for t in pinned[b]) + sum(l.size * 8 for l in host_batches[b].lods)
+
+        def result_of(i):
+            return units[i % F]._result()
+
+    def loop(n):
+        pending = deque()
+        for i in range(n):
+            if len(pending) >= F:
+                collect(pending.popleft())
+            pending.append(submit(i))
+        while pending:
+            collect(pending.popleft())
+
+    loop(max(3, 2 * F))
+    if dist is not None and sync_ranks:
         dist.barrier()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_host0 = time.perf_counter()
-    e0.record(stream)
-    h2d = d2h = 0
-    for i in range(Ke):
-        step_fns[i % n_batches]()
-        h2d += h2d_of[i % n_batches] if h2d_of is not None else fe.h2d_bytes
-        d2h += fe.d2h_bytes
-    e1.record(stream)
+    loop(Ke)
     torch.cuda.synchronize()
-    t_host = (time.perf_counter() - t_host0) * 1e3
-    e2e_ms = max(e0.elapsed_time(e1), t_host)  # the call is synchronous: host time is the truth when larger
+    e2e_ms = (time.perf_counter() - t_host0) * 1e3   # requests are collected on the host: host time is the truth
     te = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
-    if dist is not None:
+    if dist is not None and sync_ranks:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    # the last step's result against the oracle: the host-buffer path is checked too
-    res = [fe.host_out[s] for s in range(S)] if args.e2e_mode == "pipe" else fe._result()
+    h2d = sum(h2d_of(i) for i in range(Ke))
+    d2h = units[0].d2h_bytes * Ke
+    # the last request's rows against the oracle: the host-buffer path is checked too
+    res = result_of(Ke - 1)
     got = np.stack([(r.view(torch.int16).numpy().view(np.uint16) if r.dtype == torch.bfloat16 else r.numpy()) for r in res], axis=1)
     par = parity_check(cfg, host_batches[(Ke - 1) % n_batches], got, 1 if cfg.shared_table else S, sample=16)
-    rec = {"value": S * Bsz * Ke * world / (float(te.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d // Ke,
-           "d2h_bytes_per_step": d2h // Ke, "steps": Ke, "ms_per_step": float(te.item()) / Ke, "parity": par,
-           "pcie_gbs_per_gpu": (h2d + d2h) / Ke / (float(te.item()) / Ke * 1e-3) / 1e9,
-           "path": (f"HostPipe (ctrfe_host_pipe_run, {args.e2e_groups} slot groups): per group the LoD image and ids go up on one "
-                    "copy engine (cudaMemcpyAsync from pinned memory), the group is pooled, its rows come down on the other copy "
-                    "engine; the call returns when the last rows are in pinned host memory; LoD validated on the host per call"
-                    if args.e2e_mode == "pipe" else
-                    "HostFrontEnd zero_copy (buffers bound once): the kernel reads pinned host ids/LoD and writes the pinned "
-                    "per-slot host outputs over PCIe inside the one launch, then the stream is synchronised"
-                    if args.e2e_mode == "zero_copy" else "HostFrontEnd copy: H2D ids + LoD upload, launch, D2H output")}
-    if args.e2e_mode == "zero_copy" and not args.quick:
-        # the same step through the library's copy-engine pipe (ctrfe_host_pipe_run): slower on this box
-        # (every H2D copy costs ~40 us before its first byte, and uploads slow down beside downloads)
-        try:
-            pipe = ops.HostPipe(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, n_groups=args.e2e_groups)
-            hb = host_batches[0]
-            feed = torch.from_numpy(np.concatenate(hb.ids)).pin_memory()
-            offs = np.concatenate([[0], np.cumsum([i.size for i in hb.ids])])
-            lod_feed = torch.from_numpy(np.stack([l.astype(np.int64) for l in hb.lods])).pin_memory()
-            prep = pipe.prepare([feed[int(offs[s]):int(offs[s + 1])] for s in range(S)], [lod_feed[s] for s in range(S)])
-            for _ in range(3):
-                pipe.run_prepared(prep)
-            tp0 = time.perf_counter()
-            for _ in range(Ke):
-                pipe.run_prepared(prep)
-            tpp = (time.perf_counter() - tp0) * 1e3 / Ke
-            gp = np.stack([np.asarray(pipe.host_out[s]) for s in range(S)], axis=1)
-            rec["host_pipe"] = {"ms_per_step": tpp, "value": S * Bsz / (tpp * 1e-3), "groups": args.e2e_groups,
-                                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-                                "parity_ok": parity_check(cfg, hb, gp, 1 if cfg.shared_table else S, sample=8)["ok"],
-                                "note": "this rank only; ctrfe_host_pipe_run: copy-engine H2D per slot group, pooling, copy-engine "
-                                        "D2H, LoD checked by the kernels"}
-            # the unbound shape of the call: fresh pageable numpy arrays every request, pointer tables
-            # built per call (ZeroCopyTensor::CopyFromCpu takes pageable user memory too)
-            t0u = time.perf_counter()
-            nu = max(3, Ke // 4)
-            for i in range(nu):
-                hbu = host_batches[i % n_batches]
-                pipe.run([np.array(x) for x in hbu.ids], hbu.lods)
-            rec["host_pipe"]["unbound_pageable_ms_per_step"] = (time.perf_counter() - t0u) * 1e3 / nu
-            pipe.close()
-        except Exception as ex:  # a secondary figure must not cost the run its headline
-            rec["host_pipe"] = {"error": repr(ex)[:200]}
-        # three requests in flight: each has its own front end (own pinned output); request i + 1 is
-        # submitted before request i is waited for
-        fes = [fe] + [ops.HostFrontEnd(W, S, Bsz, max_ids, cfg.pooltypes, use_cvm=cfg.use_cvm, ctx=ctx, mode="zero_copy")
-                      for _ in range(2)]
-        ring = [fes[j].bind(pinned[b], e2e_lods[b]) for b in range(n_batches) for j in range(3)]
+    ms = float(te.item()) / Ke
+    if mode == "pipe":
+        path = (f"HostPipe (ctrfe_host_pipe_run, {groups} slot group(s){', ramped' if ramp else ''}): "
+                + ("the kernels read the pinned ids / 64-bit offsets themselves" if direct_in else
+                   "ids and 64-bit offsets go up on one copy engine (cudaMemcpyAsync from pinned feed buffers)")
+                + ", the groups are pooled, "
+                + ("the kernels write the rows into pinned host memory" if direct_out else "the rows come down on the other copy engine")
+                + "; LoD pairs checked by the kernels")
+    elif mode == "zero_copy":
+        path = ("HostFrontEnd zero_copy (buffers bound once): the kernel reads pinned host ids / LoD and writes the pinned per-slot "
+                "host outputs over PCIe inside the one launch; LoD pairs checked by the kernel")
+    else:
+        path = "HostFrontEnd copy: H2D ids + host-validated LoD upload, launch, D2H output"
+    path += (f"; {F} requests in flight (request i + 1 is submitted before request i is collected; every request still "
+             "reads its inputs from and lands its rows in pinned host memory)" if F > 1 else
+             "; one request at a time (collected before the next is submitted)")
+    rec = {"value": S * Bsz * world / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d // Ke, "d2h_bytes_per_step": d2h // Ke,
+           "steps": Ke, "ms_per_step": ms, "parity": par, "pcie_gbs_per_gpu": (h2d + d2h) / Ke / (ms * 1e-3) / 1e9,
+           "mode": mode, "ids_dtype": ids, "requests_in_flight": F, "path": path}
+    for u in units:
+        if hasattr(u, "close"):
+            u.close()
+    return rec
 
-        def pick(i):
-            return ring[(i % n_batches) * 3 + (i % 3)]
-        for i in range(3):
-            pick(i).result(pick(i).submit())
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        pending = []
-        for i in range(Ke):
-            c = pick(i)
-            pending.append((c, c.submit(overlap_previous=True)))
-            if len(pending) > 2:
-                c0, ev0 = pending.pop(0)
-                c0.result(ev0)
-        for c0, ev0 in pending:
-            c0.result(ev0)
-        tp = (time.perf_counter() - t0) * 1e3
-        tpt = torch.tensor([tp], dtype=torch.float64, device=dev)
-        if dist is not None:
-            dist.all_reduce(tpt, op=dist.ReduceOp.MAX)
-        rec["pipelined"] = {"value": S * Bsz * Ke * world / (float(tpt.item()) * 1e-3), "ms_per_step": float(tpt.item()) / Ke,
-                            "requests_in_flight": 3,
-                            "note": "BoundHostCall.submit()/result(): a request is submitted before the two before it are "
-                                    "waited for; every request still reads its inputs from and writes its rows to pinned host memory"}
+
+def e2e_leg(torch, ops, cfg, W, m, Bsz, world, dist, args, dev):
+    """The same metric through the host-buffer call (`e2e`), plus -- N = 1, full run -- the other forms
+    of that call measured the same way (`e2e.variants`)."""
+    Ke = max(3, min(args.steps, args.e2e_steps))
+    common = dict(Ke=Ke, groups=args.e2e_groups, ramp=args.e2e_ramp, direct_in=args.e2e_direct_in, direct_out=args.e2e_direct_out)
+    mode, ids, inflight = args.e2e_mode, args.e2e_ids, args.e2e_inflight
+    if mode == "auto":
+        mode, ids, inflight, common["groups"] = E2E_AUTO[min(world, 8)] if world in E2E_AUTO else E2E_AUTO[8]
+    rec = _e2e_variant(torch, ops, cfg, W, m, Bsz, world, dist, args, dev, mode=mode, ids=ids, inflight=inflight, **common)
+    if world == 1 and (not args.quick or args.e2e_variants):
+        variants = {}
+        for name, kw in E2E_VARIANTS.items():
+            try:
+                v = _e2e_variant(torch, ops, cfg, W, m, Bsz, world, dist, args, dev, Ke=Ke, sync_ranks=False, **kw)
+                variants[name] = {k: v[k] for k in ("ms_per_step", "value", "h2d_bytes_per_step", "d2h_bytes_per_step", "mode",
+                                                    "ids_dtype", "requests_in_flight")}
+                variants[name]["parity_ok"] = v["parity"]["ok"]
+            except Exception as ex:  # a secondary figure must not cost the run its headline
+                variants[name] = {"error": repr(ex)[:200]}
+        # the unbound shape of the call: fresh pageable numpy arrays every request, pointer tables built
+        # per call (ZeroCopyTensor::CopyFromCpu takes pageable user memory too)
+        try:
+            S, hbs = cfg.slots, m["_host_batches"]
+            pipe = ops.HostPipe(W, S, Bsz, max(int(i.size) for hb in hbs for i in hb.ids), cfg.pooltypes, use_cvm=cfg.use_cvm,
+                                ctx=m["_ctx"], n_groups=3)
+            nu = max(3, Ke // 4)
+            pipe.run([np.array(x) for x in hbs[0].ids], hbs[0].lods)
+            t0u = time.perf_counter()
+            for i in range(nu):
+                hbu = hbs[i % len(hbs)]
+                pipe.run([np.array(x) for x in hbu.ids], hbu.lods)
+            variants["pipe_unbound_pageable"] = {"ms_per_step": (time.perf_counter() - t0u) * 1e3 / nu, "mode": "pipe",
+                                                 "note": "fresh pageable numpy arrays and pointer tables every request"}
+            pipe.close()
+        except Exception as ex:
+            variants["pipe_unbound_pageable"] = {"error": repr(ex)[:200]}
+        rec["variants"] = variants
     return rec
 
 
@@ -905,10 +941,16 @@ def main():
     ap.add_argument("--regions", type=int, default=15, help="timed regions of --steps launches; the median region is reported")
     ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--e2e-mode", default="auto", choices=["auto", "pipe", "zero_copy", "copy"],
-                    help="auto: zero_copy on 1-2 GPUs, pipe on more (measured ms per step, zero_copy vs pipe: N = 1 0.58 vs 0.66, "
-                         "N = 2 0.74 vs 0.82, N = 8 2.2 vs 1.5)")
+                    help="auto: E2E_AUTO[n_gpus] (zero_copy, 32-bit ids, 2 requests in flight on 1-2 GPUs; the copy-engine pipe on "
+                         "more); anything else takes --e2e-ids / --e2e-inflight / --e2e-groups as given")
     ap.add_argument("--e2e-groups", type=int, default=3, help="slot groups of the host-buffer pipe")
     ap.add_argument("--e2e-direct-out", action="store_true", help="host pipe: kernels write the rows into host memory themselves")
+    ap.add_argument("--e2e-variants", action="store_true", help="measure e2e.variants even with --quick")
+    ap.add_argument("--e2e-ramp", action="store_true", help="host pipe: group sizes grow 1 : 2 : 4 : ...")
+    ap.add_argument("--e2e-ids", default="int64", choices=["int64", "int32"], help="host pipe: width of the ids in the feed buffers")
+    ap.add_argument("--e2e-inflight", type=int, default=1, help="host pipe: requests in flight (one pipe each)")
+    ap.add_argument("--e2e-direct-in", action="store_true",
+                    help="host pipe: kernels read ids / LoD from pinned host memory themselves (no upload); rows come down on a copy engine")
     ap.add_argument("--no-overlap", action="store_true",
                     help="timed loop without CTRFE_LAUNCH_OVERLAP_PREVIOUS (each launch waits for the one before)")
     ap.add_argument("--cpu-budget", type=float, default=12.0)

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define CTRFE_VERSION 120 /* 0.2.0: ctrfe_slot.n_ids, LoD checks on the device, plan_launch_many, fp64 cvm, router */
+#define CTRFE_VERSION 121 /* 0.2.0: ctrfe_slot.n_ids, LoD checks on the device, plan_launch_many, fp64 cvm, router */
 
 /* ---- status codes ------------------------------------------------------------------ */
 enum {
@@ -307,12 +307,28 @@ int ctrfe_fused_forward_static(const ctrfe_fused_desc* desc, void* stream, uint6
  *           Pooling kernels run on `stream`.  One run at a time per pipe.
  *   n_groups < 0 at create: |n_groups| groups with DIRECT output -- the kernels store the pooled rows
  *           into out_host themselves (out_host must then be pinned, device-mapped memory such as
- *           cudaHostAlloc returns, 16-byte aligned) and only the inputs use a copy engine. */
+ *           cudaHostAlloc returns, 16-byte aligned) and only the inputs use a copy engine.
+ *   create_ex: the same with flags.  CTRFE_PIPE_DIRECT_OUT as above.  CTRFE_PIPE_DIRECT_IN: the
+ *           kernels read ids and offsets from the caller's host memory themselves (PCIe reads issued
+ *           by the SMs; nothing is uploaded, only the rows use a copy engine).  ids_host[s] and
+ *           lods_host[s] must then be pinned, device-mapped memory (cudaHostAlloc / cudaHostRegister);
+ *           run() looks each array up (once per run of arrays that follow each other in memory) and
+ *           returns CTRFE_ERR_ARG for pageable memory.  CTRFE_PIPE_RAMP: group sizes grow
+ *           1 : 2 : 4 : ... instead of being equal (the download engine idles until the first
+ *           group is pooled, so that group is kept small).
+ *   run with wait < 0: returns at once and leaves `stream` alone; ctrfe_host_pipe_wait(pipe) then
+ *           blocks until that run's rows are on the host.  Two pipes used in turn on one stream
+ *           keep two requests in flight: request i + 1 goes up and is pooled while request i's
+ *           rows come down. */
 typedef struct ctrfe_host_pipe ctrfe_host_pipe;
+enum { CTRFE_PIPE_DIRECT_OUT = 1, CTRFE_PIPE_DIRECT_IN = 2, CTRFE_PIPE_RAMP = 4 };
 int ctrfe_host_pipe_create(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, int64_t max_ids_per_slot, int n_groups,
                            ctrfe_host_pipe** out);
+int ctrfe_host_pipe_create_ex(ctrfe_ctx* ctx, const ctrfe_fused_desc* desc, int64_t max_ids_per_slot, int n_groups,
+                              uint32_t flags, ctrfe_host_pipe** out);
 int ctrfe_host_pipe_run(ctrfe_host_pipe* pipe, const void* const* ids_host, const int64_t* n_ids,
                         const uint64_t* const* lods_host, void* const* out_host, int64_t out_ld, void* stream, int wait);
+int ctrfe_host_pipe_wait(ctrfe_host_pipe* pipe);
 int ctrfe_host_pipe_destroy(ctrfe_host_pipe* pipe);
 
 /* ---- row-sharded tables across the GPUs of one box ------------------------------------

@@ -55,6 +55,7 @@ class CtrfeError(RuntimeError):
 COPY_H2D, COPY_D2H, COPY_D2D = 1, 2, 3
 LAUNCH_OVERLAP_PREVIOUS = 1
 LAUNCH_UPLOAD_LOD = 2
+PIPE_DIRECT_OUT, PIPE_DIRECT_IN, PIPE_RAMP = 1, 2, 4
 
 
 class BadIdError(CtrfeError, ValueError):
@@ -73,7 +74,7 @@ EXPORTS = [
     "ctrfe_version", "ctrfe_last_error", "ctrfe_malloc", "ctrfe_free", "ctrfe_host_alloc", "ctrfe_host_free",
     "ctrfe_memcpy", "ctrfe_stream_synchronize", "ctrfe_ctx_create", "ctrfe_ctx_destroy", "ctrfe_check_ids",
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
-    "ctrfe_plan_num_kernels", "ctrfe_fused_embedding_seq_pool", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create",
+    "ctrfe_plan_num_kernels", "ctrfe_fused_embedding_seq_pool", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create", "ctrfe_host_pipe_create_ex", "ctrfe_host_pipe_wait",
     "ctrfe_host_pipe_run", "ctrfe_host_pipe_destroy", "ctrfe_plan_kernel_name", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
     "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
@@ -110,8 +111,10 @@ def lib():
         L.ctrfe_plan_launch_many.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_uint32]
         L.ctrfe_plan_update_lod.argtypes = [vp, C.POINTER(vp)]
         L.ctrfe_host_pipe_create.argtypes = [vp, C.POINTER(FusedDesc), i64, C.c_int, C.POINTER(vp)]
+        L.ctrfe_host_pipe_create_ex.argtypes = [vp, C.POINTER(FusedDesc), i64, C.c_int, C.c_uint32, C.POINTER(vp)]
         L.ctrfe_host_pipe_run.argtypes = [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), i64, vp, C.c_int]
         L.ctrfe_host_pipe_destroy.argtypes = [vp]
+        L.ctrfe_host_pipe_wait.argtypes = [vp]
         L.ctrfe_plan_kernel_name.argtypes = [vp, C.c_int]
         L.ctrfe_plan_kernel_name.restype = C.c_char_p
         L.ctrfe_fused_embedding_seq_pool.argtypes = [vp, vp, i64, i64, i32, vp, i64, i64, vp, i64, i64, vp, vp]

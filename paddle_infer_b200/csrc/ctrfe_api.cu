@@ -819,11 +819,11 @@ int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* positi
     const IdSource& src = srcs[s];
     if (src.ids_i32) {
       int v = 0;
-      CU(cudaMemcpyAsync(&v, static_cast<const int*>(src.ids) + pos, 4, cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(&v, static_cast<const int*>(src.ids) + pos, 4, cudaMemcpyDefault, st));  // (the ids may sit in pinned host memory)
       CU(cudaStreamSynchronize(st));
       bad = v;
     } else {
-      CU(cudaMemcpyAsync(&bad, static_cast<const long long*>(src.ids) + pos, 8, cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(&bad, static_cast<const long long*>(src.ids) + pos, 8, cudaMemcpyDefault, st));
       CU(cudaStreamSynchronize(st));
     }
   }

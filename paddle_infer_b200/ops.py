@@ -875,9 +875,13 @@ class HostPipe:
 
     def __init__(self, W, n_slots: int, batch: int, max_ids_per_slot: int, pooltype="SUM", *, pad_value=0.0,
                  padding_idx=-1, use_cvm: Optional[bool] = True, cvm_offset: int = 2, n_groups: int = 4,
-                 ids_dtype="int64", direct_out: bool = False, ctx: Optional[Context] = None):
+                 ids_dtype="int64", direct_out: bool = False, direct_in: bool = False, ramp: bool = False,
+                 ctx: Optional[Context] = None):
         """direct_out: the kernels store the pooled rows straight into the pinned host block (PCIe writes
-        issued by the SMs) instead of a device block that a copy engine brings down."""
+        issued by the SMs) instead of a device block that a copy engine brings down.
+        direct_in: the kernels read ids and offsets from the caller's PINNED host arrays themselves
+        (`device.PinnedArray`, pinned torch tensors); nothing is uploaded.  Pageable arrays are refused.
+        ramp: group sizes grow 1 : 2 : 4 : ... (a small first group starts the download engine early)."""
         sharded = W if _is_sharded(W) else None
         if sharded is not None:
             t0 = _sharded_like(sharded)
@@ -904,8 +908,10 @@ class HostPipe:
                 desc.hot_cache = C.pointer(sharded.hot.struct)
         self._keep = (tables, sharded)
         h = C.c_void_p()
-        B.check(B.lib().ctrfe_host_pipe_create(self.ctx.handle, C.byref(desc), int(max_ids_per_slot),
-                                               -int(n_groups) if direct_out else int(n_groups), C.byref(h)))
+        flags = (B.PIPE_DIRECT_OUT if direct_out else 0) | (B.PIPE_DIRECT_IN if direct_in else 0) | (B.PIPE_RAMP if ramp else 0)
+        B.check(B.lib().ctrfe_host_pipe_create_ex(self.ctx.handle, C.byref(desc), int(max_ids_per_slot), int(n_groups),
+                                                  flags, C.byref(h)))
+        self.direct_in = direct_in
         self.handle = h
         np_dt = {"float32": np.float32, "float16": np.float16, "bfloat16": np.uint16}[t0.dtype]
         self._pinned = PinnedArray((n_slots, batch, self.d_out), np_dt)
@@ -949,13 +955,21 @@ class HostPipe:
             h2d += n_ids[s] * self._id_es + n * 8
         return (ids_ptrs, n_ids, lod_ptrs, keep, h2d)
 
-    def run_prepared(self, prep, wait: bool = True):
+    def run_prepared(self, prep, wait=True):
+        """wait=True: returns with the rows on the host; False: the context's stream waits for them;
+        None: neither -- call wait() before reading host_out (two pipes used in turn keep two requests
+        in flight: one goes up and is pooled while the other's rows come down)."""
         ids_ptrs, n_ids, lod_ptrs, _keep, self.h2d_bytes = prep
+        self._in_flight = prep   # the request's arrays stay alive until the next run replaces them
         B.check(B.lib().ctrfe_host_pipe_run(self.handle, ids_ptrs, n_ids, lod_ptrs, self._out_ptrs, self.d_out,
-                                            self.ctx.stream(), 1 if wait else 0))
+                                            self.ctx.stream(), -1 if wait is None else (1 if wait else 0)))
         return [self.host_out[s] for s in range(self.S)]
 
-    def run(self, ids_host: Sequence, lods_host: Sequence, wait: bool = True):
+    def wait(self):
+        B.check(B.lib().ctrfe_host_pipe_wait(self.handle))
+        return [self.host_out[s] for s in range(self.S)]
+
+    def run(self, ids_host: Sequence, lods_host: Sequence, wait=True):
         """ids_host[s]: int64 (or int32) numpy array or CPU tensor, pinned for asynchronous copies;
         lods_host[s]: the [B + 1] offsets as a numpy uint64 array or an int64 CPU tensor."""
         return self.run_prepared(self.prepare(ids_host, lods_host), wait)

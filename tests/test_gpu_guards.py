@@ -191,8 +191,86 @@ def test_host_pipe_equals_the_device_call(env, n_groups):
             pipe.run(ids, lods)
             with pytest.raises(ValueError) as e:
                 pipe.ctx.check_ids()
-            assert e.value.id_value == N + 3
+            assert e.value.id_value == N + 3 and e.value.slot == 3   # the caller's slot, not its place in the group
         pipe.close()
+
+
+@pytest.mark.parametrize("n_groups,direct_out", [(1, False), (4, False), (3, True)])
+def test_host_pipe_direct_input(env, n_groups, direct_out):
+    """CTRFE_PIPE_DIRECT_IN: the kernels read ids and 64-bit offsets from the caller's pinned host
+    memory themselves -- same bits as the device-resident call, from one feed buffer (arrays that
+    follow each other) and from separate pinned arrays; pageable memory is refused; a bad id is
+    fetched from the host array it sits in."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(70 + n_groups)
+    S, Bsz, N, D = 6, 257, 5000, 16
+    table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+    table[:, 0] = rng.integers(0, 16, N)
+    table[:, 1] = np.minimum(table[:, 0], rng.integers(0, 16, N))
+    tt = torch.from_numpy(table).to(dev)
+    pipe = ops.HostPipe(tt, S, Bsz, 4000, "SUM", use_cvm=True, n_groups=n_groups, direct_in=True, direct_out=direct_out)
+    for rep in range(3):
+        lens = [rng.integers(0, 9, Bsz) if s != 2 else np.zeros(Bsz, np.int64) for s in range(S)]   # slot 2: no ids at all
+        lods = [np.concatenate([[0], np.cumsum(l)]).astype(np.int64) for l in lens]
+        ids_np = [rng.integers(0, N, int(l[-1])).astype(np.int64) for l in lods]
+        if rep % 2 == 0:   # one feed buffer: the slots' arrays follow each other
+            feed = torch.from_numpy(np.concatenate(ids_np)).pin_memory()
+            offs = np.concatenate([[0], np.cumsum([i.size for i in ids_np])])
+            ids = [feed[int(offs[s]):int(offs[s + 1])] for s in range(S)]
+            lod_feed = torch.from_numpy(np.stack(lods)).pin_memory()
+            lod_t = [lod_feed[s] for s in range(S)]
+        else:
+            ids = [torch.from_numpy(i).pin_memory() for i in ids_np]
+            lod_t = [torch.from_numpy(l).pin_memory() for l in lods]
+        got = pipe.run(ids, lod_t)
+        want = ops.ctr_fused_emb_seqpool_cvm(tt, [torch.from_numpy(i).to(dev) for i in ids_np],
+                                             [l.astype(np.uint64) for l in lods], "SUM", use_cvm=True)
+        for s in range(S):
+            assert torch.equal(got[s], want[s].cpu()), (rep, s)
+    with pytest.raises(B.CtrfeError, match="pinned host memory"):
+        pipe.run([torch.from_numpy(i) for i in ids_np], lod_t)          # pageable ids
+    with pytest.raises(B.CtrfeError, match="pinned host memory"):
+        pipe.run(ids, [l.astype(np.uint64) for l in lods])               # pageable offsets
+    ids[4][1] = N + 9
+    pipe.run(ids, lod_t)
+    with pytest.raises(ValueError) as e:
+        pipe.ctx.check_ids()
+    assert e.value.id_value == N + 9 and e.value.slot == 4
+    pipe.close()
+
+
+@pytest.mark.parametrize("ids_dtype", ["int64", "int32"])
+def test_two_host_pipes_in_flight(env, ids_dtype):
+    """Two pipes used in turn on one stream (run with wait=None, wait() before the rows are read), ramped
+    group sizes, 32- and 64-bit ids: every request's rows equal the device-resident call's."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(91)
+    S, Bsz, N, D = 11, 200, 3000, 16
+    table = rng.uniform(-1, 1, (N, D)).astype(np.float32)
+    table[:, 0] = rng.integers(0, 16, N)
+    table[:, 1] = np.minimum(table[:, 0], rng.integers(0, 16, N))
+    tt = torch.from_numpy(table).to(dev)
+    pipes = [ops.HostPipe(tt, S, Bsz, 3000, "SUM", use_cvm=True, n_groups=4, ramp=True, ids_dtype=ids_dtype) for _ in range(2)]
+    npdt = np.int32 if ids_dtype == "int32" else np.int64
+    reqs = []
+    for _ in range(7):
+        lods = [np.concatenate([[0], np.cumsum(rng.integers(0, 8, Bsz))]).astype(np.uint64) for _s in range(S)]
+        ids = [torch.from_numpy(rng.integers(0, N, int(l[-1])).astype(npdt)).pin_memory() for l in lods]
+        reqs.append((ids, lods))
+    wants = [ops.ctr_fused_emb_seqpool_cvm(tt, [i.to(dev).long() for i in ids], lods, "SUM", use_cvm=True) for ids, lods in reqs]
+    pending = [None, None]
+    for r in range(len(reqs) + 2):
+        pp = pipes[r % 2]
+        if pending[r % 2] is not None:
+            got = pp.wait()
+            for s in range(S):
+                assert torch.equal(got[s], wants[pending[r % 2]][s].cpu()), (pending[r % 2], s)
+            pending[r % 2] = None
+        if r < len(reqs):
+            pp.run(reqs[r][0], reqs[r][1], wait=None)
+            pending[r % 2] = r
+    for pp in pipes:
+        pp.close()
 
 
 def test_host_layer_runs_without_torch(env):
