@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define CTRFE_VERSION 121 /* 0.2.0: ctrfe_slot.n_ids, LoD checks on the device, plan_launch_many, fp64 cvm, router */
+#define CTRFE_VERSION 122 /* 0.2.0: ctrfe_slot.n_ids, LoD checks on the device, plan_launch_many, fp64 cvm, router */
 
 /* ---- status codes ------------------------------------------------------------------ */
 enum {
@@ -42,7 +42,7 @@ enum {
 /* ---- element types (phi::DataType subset this path is registered for) --------------- */
 enum { CTRFE_F32 = 0, CTRFE_F16 = 1, CTRFE_BF16 = 2, CTRFE_F64 = 3 };
 /* ---- id types: embedding_kernel.cu:108-117 dispatches int32 / int64 ----------------- */
-enum { CTRFE_I64 = 0, CTRFE_I32 = 1 };
+enum { CTRFE_I64 = 0, CTRFE_I32 = 1, CTRFE_I16 = 2 /* ctrfe_embedding and ctrfe_embedding_grad_sparse only */ };
 /* ---- pooltype, in the order SequencePoolOpMaker lists them
  *      (sequence_ops/sequence_pool_op.cc:64-70) ---------------------------------------- */
 enum {
@@ -381,7 +381,8 @@ int ctrfe_fused_embedding_seq_pool(ctrfe_ctx* ctx, const void* table, int64_t ta
 /* ---- the three ops on their own (1:1 clones of the reference ops) -------------------- */
 
 /* lookup_table_v2 / phi embedding: out[k,:] = (ids[k]==padding_idx) ? 0 : table[ids[k],:].
- * Pure byte copy, any element size.  Replaces EmbeddingCUDAFunctor / EmbeddingFW
+ * Pure byte copy, any element size (fp64 tables included); ids int64, int32 or int16 as the reference
+ * GPU kernel takes them (embedding_kernel.cu:107-117).  Replaces EmbeddingCUDAFunctor / EmbeddingFW
  * (phi/kernels/gpu/embedding_kernel.cu:25-88). */
 int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes,
                     const void* ids, int32_t ids_dtype, int64_t n_ids, int64_t padding_idx,
@@ -425,9 +426,19 @@ int ctrfe_cvm_grad(ctrfe_ctx* ctx, const float* dy, const float* cvm, const uint
  * EmbeddingGradCUDAFunctor / EmbeddingGrad (phi/kernels/gpu/embedding_grad_kernel.cu:38-60,
  * 62-130).  Atomic adds as in the reference GPU kernel: the order of additions into a row is
  * not fixed, so results match the CPU kernel to rounding (<= 1e-6 relative), not bit for bit.
- * The SelectedRows (is_sparse) variant is not provided. */
+ * The SelectedRows (is_sparse) variant is ctrfe_embedding_grad_sparse below. */
 int ctrfe_embedding_grad(ctrfe_ctx* ctx, const float* dout, const void* ids, int32_t ids_dtype, int64_t n_ids,
                          int64_t table_rows, int64_t dim, int64_t padding_idx, float* dw, void* stream);
+
+/* lookup_table_v2_grad with is_sparse: W@GRAD as a SelectedRows -- rows (device, int64 [n_ids]) = the ids
+ * widened to int64, one entry per id and not merged; value (device, [n_ids, row_bytes]) = dout (any
+ * dtype; value == dout: no copy); the SelectedRows height is the table's row count, which the caller
+ * knows.  rows_host (may be NULL) receives the same rows once `stream` has reached this point -- the
+ * reference keeps the rows vector on the host (MixVector::CopyToCPU).  padding_idx is not applied and
+ * ids are not range-checked, as in the reference.  Replaces EmbeddingSparseGradCUDAFunctor
+ * (phi/kernels/gpu/embedding_grad_kernel.cu:141-214). */
+int ctrfe_embedding_grad_sparse(ctrfe_ctx* ctx, const void* dout, int64_t row_bytes, const void* ids, int32_t ids_dtype,
+                                int64_t n_ids, int64_t* rows, int64_t* rows_host, void* value, void* stream);
 
 #ifdef __cplusplus
 }

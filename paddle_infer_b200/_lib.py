@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("CTRFE_LIB") or os.path.join(_HERE, "libctrfe.so")  # 
 # enums of include/ctrfe.h
 OK, ERR_BAD_ID, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED, ERR_NCCL = range(6)
 F32, F16, BF16, F64 = 0, 1, 2, 3
-I64, I32 = 0, 1
+I64, I32, I16 = 0, 1, 2
 POOL_AVERAGE, POOL_SUM, POOL_SQRT, POOL_LAST, POOL_FIRST, POOL_MAX = range(6)
 POOLTYPES = {"AVERAGE": POOL_AVERAGE, "SUM": POOL_SUM, "SQRT": POOL_SQRT, "LAST": POOL_LAST,
              "FIRST": POOL_FIRST, "MAX": POOL_MAX}
@@ -76,7 +76,7 @@ EXPORTS = [
     "ctrfe_fused_forward", "ctrfe_plan_create", "ctrfe_plan_launch", "ctrfe_plan_launch_ex", "ctrfe_plan_destroy",
     "ctrfe_plan_num_kernels", "ctrfe_fused_embedding_seq_pool", "ctrfe_plan_launch_many", "ctrfe_plan_update_lod", "ctrfe_host_pipe_create", "ctrfe_host_pipe_create_ex", "ctrfe_host_pipe_wait",
     "ctrfe_host_pipe_run", "ctrfe_host_pipe_destroy", "ctrfe_plan_kernel_name", "ctrfe_embedding", "ctrfe_sequence_pool", "ctrfe_cvm",
-    "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad",
+    "ctrfe_fused_forward_static", "ctrfe_sequence_pool_grad", "ctrfe_cvm_grad", "ctrfe_embedding_grad", "ctrfe_embedding_grad_sparse",
     "ctrfe_shard_alloc", "ctrfe_shard_free", "ctrfe_shard_export", "ctrfe_shard_open", "ctrfe_shard_close",
     "ctrfe_shard_alloc_fd", "ctrfe_shard_open_fd", "ctrfe_shard_unmap", "ctrfe_hot_cache_build", "ctrfe_keymap_build",
 ]
@@ -124,6 +124,7 @@ def lib():
         L.ctrfe_sequence_pool_grad.argtypes = [vp, vp, i64, vp, i64, i64, i32, vp, vp, vp]
         L.ctrfe_cvm_grad.argtypes = [vp, vp, vp, vp, i64, i64, i64, i32, vp, vp]
         L.ctrfe_embedding_grad.argtypes = [vp, vp, vp, i32, i64, i64, i64, i64, vp, vp]
+        L.ctrfe_embedding_grad_sparse.argtypes = [vp, vp, i64, vp, i32, i64, vp, vp, vp, vp]
         L.ctrfe_fused_forward_static.argtypes = [C.POINTER(FusedDesc), vp, vp]
         L.ctrfe_shard_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(vp)]
         L.ctrfe_shard_free.argtypes = [C.c_int, vp]

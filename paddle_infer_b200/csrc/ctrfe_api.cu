@@ -48,7 +48,7 @@ struct Staging {
 
 struct IdSource {  // what ctrfe_check_ids needs to fetch the offending id value
   const void* ids;
-  int ids_i32;
+  int ids_i32;  // the id width as CTRFE_I64 (0) / CTRFE_I32 (1) / CTRFE_I16 (2)
 };
 
 }  // namespace
@@ -817,7 +817,12 @@ int ctrfe_check_ids(ctrfe_ctx* ctx, void* stream, int64_t* slot, int64_t* positi
   const std::vector<IdSource>& srcs = ctx->tag_ids[tag & 255u];
   if (s < static_cast<int64_t>(srcs.size()) && srcs[s].ids) {
     const IdSource& src = srcs[s];
-    if (src.ids_i32) {
+    if (src.ids_i32 == CTRFE_I16) {
+      short v = 0;
+      CU(cudaMemcpyAsync(&v, static_cast<const short*>(src.ids) + pos, 2, cudaMemcpyDefault, st));
+      CU(cudaStreamSynchronize(st));
+      bad = v;
+    } else if (src.ids_i32) {
       int v = 0;
       CU(cudaMemcpyAsync(&v, static_cast<const int*>(src.ids) + pos, 4, cudaMemcpyDefault, st));  // (the ids may sit in pinned host memory)
       CU(cudaStreamSynchronize(st));
@@ -1085,8 +1090,8 @@ int ctrfe_fused_embedding_seq_pool(ctrfe_ctx* ctx, const void* table, int64_t ta
 int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64_t row_bytes, const void* ids,
                     int32_t ids_dtype, int64_t n_ids, int64_t padding_idx, void* out, void* stream) {
   if (!ctx) return fail(CTRFE_ERR_ARG, "embedding: null ctx");
-  if (ids_dtype != CTRFE_I64 && ids_dtype != CTRFE_I32)
-    return fail(CTRFE_ERR_UNSUPPORTED, "emebdding input only support int32 and int64");
+  if (ids_dtype != CTRFE_I64 && ids_dtype != CTRFE_I32 && ids_dtype != CTRFE_I16)
+    return fail(CTRFE_ERR_UNSUPPORTED, "emebdding input only support int16, int32 and int64");
   if (row_bytes <= 0 || table_rows < 0 || n_ids < 0) return fail(CTRFE_ERR_ARG, "embedding: bad sizes");
   if (n_ids == 0) return CTRFE_OK;
   if (!table || !ids || !out) return fail(CTRFE_ERR_ARG, "embedding: null pointer");
@@ -1102,10 +1107,10 @@ int ctrfe_embedding(ctrfe_ctx* ctx, const void* table, int64_t table_rows, int64
   const long long cap = static_cast<long long>(ctx->sm_count) * 8 * 4;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  ctx->tag_ids[0].assign(1, IdSource{ids, ids_dtype == CTRFE_I32});  // the unfused ops record untagged keys
+  ctx->tag_ids[0].assign(1, IdSource{ids, ids_dtype});  // the unfused ops record untagged keys
   const char* t = static_cast<const char*>(table);
   char* o = static_cast<char*>(out);
-  const int i32 = ids_dtype == CTRFE_I32;
+  const int i32 = ids_dtype;  // CTRFE_I64 / I32 / I16
   const unsigned gb = static_cast<unsigned>(blocks);
 #define CTRFE_GATHER(UB) \
   ctrfe::gather_rows_kernel<UB><<<gb, ctrfe::kThreads, 0, st>>>(t, table_rows, row_bytes, ids, i32, n_ids, padding_idx, o, ctx->err_dev)
@@ -1307,6 +1312,26 @@ int ctrfe_embedding_grad(ctrfe_ctx* ctx, const float* dout, const void* ids, int
         dout, ids, ids_dtype == CTRFE_I32, n_ids, table_rows, static_cast<int>(dim), padding_idx, dw, ctx->err_dev);
     CU(cudaGetLastError());
   }
+  return CTRFE_OK;
+}
+
+int ctrfe_embedding_grad_sparse(ctrfe_ctx* ctx, const void* dout, int64_t row_bytes, const void* ids, int32_t ids_dtype,
+                                int64_t n_ids, int64_t* rows, int64_t* rows_host, void* value, void* stream) {
+  if (!ctx) return fail(CTRFE_ERR_ARG, "embedding_grad_sparse: null ctx");
+  if (ids_dtype != CTRFE_I64 && ids_dtype != CTRFE_I32 && ids_dtype != CTRFE_I16)
+    return fail(CTRFE_ERR_UNSUPPORTED, "emebdding input only support int16, int32 and int64");
+  if (n_ids < 0 || row_bytes <= 0) return fail(CTRFE_ERR_ARG, "embedding_grad_sparse: bad shape");
+  if (n_ids == 0) return CTRFE_OK;
+  if (!dout || !ids || !rows || !value) return fail(CTRFE_ERR_ARG, "embedding_grad_sparse: null pointer");
+  DeviceGuard g(ctx->device);
+  auto st = static_cast<cudaStream_t>(stream);
+  long long blocks = (n_ids + 255) / 256;
+  if (blocks > 148LL * 16) blocks = 148LL * 16;
+  ctrfe::ids_widen_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(ids, ids_dtype, n_ids, reinterpret_cast<long long*>(rows));
+  CU(cudaGetLastError());
+  if (rows_host) CU(cudaMemcpyAsync(rows_host, rows, static_cast<size_t>(n_ids) * 8, cudaMemcpyDeviceToHost, st));
+  if (value != dout)
+    CU(cudaMemcpyAsync(value, dout, static_cast<size_t>(n_ids) * static_cast<size_t>(row_bytes), cudaMemcpyDeviceToDevice, st));
   return CTRFE_OK;
 }
 

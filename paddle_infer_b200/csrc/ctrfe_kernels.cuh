@@ -679,8 +679,10 @@ __global__ void __launch_bounds__(kThreads) gather_rows_kernel(
       dst[u] = -1;
       if (i >= total) continue;
       const long long k = i / upr, c = i - k * upr;
-      const long long id = ids_i32 ? static_cast<long long>(__ldg(reinterpret_cast<const int*>(ids) + k))
-                                   : __ldg(reinterpret_cast<const long long*>(ids) + k);
+      // ids_i32: the CTRFE_I64 / I32 / I16 code of the id width
+      const long long id = ids_i32 == 1 ? static_cast<long long>(__ldg(reinterpret_cast<const int*>(ids) + k))
+                           : ids_i32 == 2 ? static_cast<long long>(__ldg(reinterpret_cast<const short*>(ids) + k))
+                                          : __ldg(reinterpret_cast<const long long*>(ids) + k);
       dst[u] = i;
       v[u] = T{};
       if (padding_idx != -1 && id == padding_idx) continue;
@@ -694,6 +696,16 @@ __global__ void __launch_bounds__(kThreads) gather_rows_kernel(
     for (int u = 0; u < kUnroll; ++u)
       if (dst[u] >= 0) reinterpret_cast<T*>(out)[dst[u]] = v[u];
   }
+}
+
+// ids of any supported width -> int64 rows (the rows vector of a SelectedRows W@GRAD,
+// phi/kernels/gpu/embedding_grad_kernel.cu:168-186 InputTypeConvert / Copy).
+__global__ void ids_widen_kernel(const void* __restrict__ ids, int kind, long long n, long long* __restrict__ out) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = kind == 1 ? static_cast<long long>(reinterpret_cast<const int*>(ids)[i])
+             : kind == 2 ? static_cast<long long>(reinterpret_cast<const short*>(ids)[i])
+                         : reinterpret_cast<const long long*>(ids)[i];
 }
 
 // ---------------------------------------------------------------------------------------

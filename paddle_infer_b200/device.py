@@ -21,12 +21,12 @@ from . import _lib as B
 _DTYPES = {
     "float32": (B.F32, 4, np.float32), "float16": (B.F16, 2, np.float16), "bfloat16": (B.BF16, 2, np.uint16),
     "float64": (B.F64, 8, np.float64), "int64": (None, 8, np.int64), "int32": (None, 4, np.int32),
-    "uint64": (None, 8, np.uint64), "uint32": (None, 4, np.uint32), "uint8": (None, 1, np.uint8),
+    "uint64": (None, 8, np.uint64), "uint32": (None, 4, np.uint32), "uint8": (None, 1, np.uint8), "int16": (None, 2, np.int16),
 }
 _TYPESTR = {"float32": "<f4", "float16": "<f2", "bfloat16": "<u2", "float64": "<f8", "int64": "<i8", "int32": "<i4",
-            "uint64": "<u8", "uint32": "<u4", "uint8": "|u1"}
+            "uint64": "<u8", "uint32": "<u4", "uint8": "|u1", "int16": "<i2"}
 _FROM_TYPESTR = {"<f4": "float32", "<f2": "float16", "<f8": "float64", "<i8": "int64", "<i4": "int32", "<u8": "uint64",
-                 "<u4": "uint32", "<u2": "bfloat16", "|u1": "uint8"}
+                 "<u4": "uint32", "<u2": "bfloat16", "|u1": "uint8", "<i2": "int16"}
 
 
 def current_device() -> int:

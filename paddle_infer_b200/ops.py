@@ -35,6 +35,7 @@ from .device import Arr, DeviceArray, PinnedArray, as_arr, empty, is_torch, stre
 
 _FLOATS = ("float32", "float16", "bfloat16")
 _IDS = {"int64": B.I64, "int32": B.I32}
+_IDS_GATHER = {"int64": B.I64, "int32": B.I32, "int16": B.I16}   # lookup_table_v2 on its own also takes int16 ids
 
 
 class InvalidArgument(ValueError):
@@ -175,11 +176,11 @@ def lookup_table_v2(W, Ids, padding_idx: int = -1, *, check: bool = True, ctx: O
     if len(w.shape) != 2:
         raise InvalidArgument(f"ShapeError: The dimensions of the 'lookup table' must be 2. But received "
                               f"lookup table's dimensions = {len(w.shape)}.")
-    if ids.dtype not in _IDS:
-        raise Unimplemented("emebdding input only support int32 and int64")
+    if ids.dtype not in _IDS_GATHER:
+        raise Unimplemented("emebdding input only support int16, int32 and int64")
     ctx = ctx or default_context(w.device)
     out, o = empty(ids.shape + (w.shape[1],), w.dtype, w)
-    B.check(B.lib().ctrfe_embedding(ctx.handle, w.ptr, w.shape[0], w.shape[1] * w.itemsize, ids.ptr, _IDS[ids.dtype],
+    B.check(B.lib().ctrfe_embedding(ctx.handle, w.ptr, w.shape[0], w.shape[1] * w.itemsize, ids.ptr, _IDS_GATHER[ids.dtype],
                                     ids.numel, int(padding_idx), o.ptr, ctx.stream()))
     if check:
         ctx.check_ids()
@@ -332,6 +333,28 @@ def lookup_table_v2_grad(OutGrad, Ids, table_rows: int, padding_idx: int = -1, *
     else:
         ctx._keep = (g.obj, ids.obj)
     return dw
+
+
+SelectedRows = namedtuple("SelectedRows", ["rows", "value", "height"])
+
+
+def lookup_table_v2_grad_sparse(OutGrad, Ids, table_rows: int, *, ctx: Optional[Context] = None) -> SelectedRows:
+    """W@GRAD of lookup_table_v2 with is_sparse=True, as the reference's SelectedRows: rows = the ids
+    as int64 (one entry per id, not merged), value = Out@GRAD as [n_ids, D] (a copy), height =
+    table_rows (phi/kernels/gpu/embedding_grad_kernel.cu:141-214; padding_idx is not applied there)."""
+    g, ids = as_arr(OutGrad, "Out@GRAD"), as_arr(Ids, "Ids")
+    if ids.dtype not in _IDS_GATHER:
+        raise Unimplemented("emebdding input only support int16, int32 and int64")
+    d = g.shape[-1]
+    if g.numel // max(d, 1) != ids.numel:
+        raise InvalidArgument("ShapeError: The shape of lookup_table@Grad and output@Grad should be same.")
+    ctx = ctx or default_context(g.device)
+    rows, ro = empty((ids.numel,), "int64", g)
+    value, vo = empty((ids.numel, d), g.dtype, g)
+    B.check(B.lib().ctrfe_embedding_grad_sparse(ctx.handle, g.ptr, d * g.itemsize, ids.ptr, _IDS_GATHER[ids.dtype], ids.numel,
+                                                ro.ptr, None, vo.ptr, ctx.stream()))
+    ctx._keep = (g.obj, ids.obj)
+    return SelectedRows(rows, value, int(table_rows))
 
 
 # ------------------------------------------------------------------------------------------

@@ -273,6 +273,41 @@ def test_two_host_pipes_in_flight(env, ids_dtype):
         pp.close()
 
 
+def test_int16_ids_and_sparse_grad(env):
+    """lookup_table_v2 takes int16 ids as the reference GPU kernel does (embedding_kernel.cu:107-117), also
+    over an fp64 table; the is_sparse gradient is the reference's SelectedRows: rows = the ids as int64, one per
+    id and unmerged, value = Out@GRAD (embedding_grad_kernel.cu:141-214)."""
+    ops, O, B, dev = env
+    rng = np.random.default_rng(17)
+    N, D, K = 300, 12, 1000
+    for np_dt, t_dt in ((np.float32, torch.float32), (np.float64, torch.float64), (np.float16, torch.float16)):
+        table = rng.uniform(-1, 1, (N, D)).astype(np_dt)
+        for id_dt in (np.int16, np.int32, np.int64):
+            ids = rng.integers(0, N, K).astype(id_dt)
+            ids[5] = 7
+            got = ops.lookup_table_v2(torch.from_numpy(table).to(dev), torch.from_numpy(ids).to(dev), padding_idx=7)
+            want = table[ids.astype(np.int64)]
+            want[ids == 7] = 0
+            assert got.dtype == t_dt and np.array_equal(got.cpu().numpy(), want), (np_dt, id_dt)
+    bad = rng.integers(0, N, 50).astype(np.int16)
+    bad[9] = -3
+    with pytest.raises(ValueError) as e:
+        ops.lookup_table_v2(torch.from_numpy(table).to(dev), torch.from_numpy(bad).to(dev))
+    assert e.value.id_value == -3 and e.value.position == 9
+    for id_dt in (np.int16, np.int32, np.int64):
+        ids = rng.integers(0, N, (K // 4, 4)).astype(id_dt)
+        dout = rng.uniform(-1, 1, (K // 4, 4, D)).astype(np.float32)
+        sr = ops.lookup_table_v2_grad_sparse(torch.from_numpy(dout).to(dev), torch.from_numpy(ids).to(dev), N)
+        assert sr.height == N and sr.rows.dtype == torch.int64
+        assert np.array_equal(sr.rows.cpu().numpy(), ids.reshape(-1).astype(np.int64))
+        assert np.array_equal(sr.value.cpu().numpy(), dout.reshape(-1, D))
+        # merged into a dense table it equals the dense gradient
+        dense = np.zeros((N, D), np.float64)
+        np.add.at(dense, ids.reshape(-1).astype(np.int64), dout.reshape(-1, D).astype(np.float64))
+        dw = ops.lookup_table_v2_grad(torch.from_numpy(dout).to(dev), torch.from_numpy(ids.astype(np.int64)).to(dev), N)
+        np.testing.assert_allclose(dw.cpu().numpy(), dense, rtol=1e-5, atol=1e-5)
+
+
 def test_host_layer_runs_without_torch(env):
     """The package core needs numpy and the library only: a child process that never imports torch
     runs the fused front end, the three ops on their own and the host pipe on device.DeviceArray /
