@@ -51,7 +51,10 @@ def test_python_enums_match_header(built):
              "CTRFE_CVM_NONE": B.CVM_NONE, "CTRFE_CVM_USE": B.CVM_USE, "CTRFE_CVM_STRIP": B.CVM_STRIP,
              "CTRFE_SCALE_DIVIDE": B.SCALE_DIVIDE, "CTRFE_SCALE_RECIPROCAL": B.SCALE_RECIPROCAL,
              "CTRFE_INIT_ZERO": B.INIT_ZERO, "CTRFE_INIT_PAD": B.INIT_PAD, "CTRFE_INIT_FIRST_ROW": B.INIT_FIRST_ROW,
-             "CTRFE_LOD_HOST": B.LOD_HOST, "CTRFE_LOD_DEVICE": B.LOD_DEVICE}
+             "CTRFE_LOD_HOST": B.LOD_HOST, "CTRFE_LOD_DEVICE": B.LOD_DEVICE, "CTRFE_I16": B.I16,
+             "CTRFE_PIPE_DIRECT_OUT": B.PIPE_DIRECT_OUT, "CTRFE_PIPE_DIRECT_IN": B.PIPE_DIRECT_IN, "CTRFE_PIPE_RAMP": B.PIPE_RAMP,
+             "CTRFE_LAUNCH_UPLOAD_LOD": B.LAUNCH_UPLOAD_LOD, "CTRFE_COPY_H2D": B.COPY_H2D, "CTRFE_COPY_D2H": B.COPY_D2H,
+             "CTRFE_COPY_D2D": B.COPY_D2D}
     for k, v in pairs.items():
         assert consts[k] == v, k
     # the oracle shares the numeric values (it is driven with the same descriptors in tests)
