@@ -486,10 +486,6 @@ def _free_measure(m):
     m.pop("_ctx", None)
 
 
-def _public(m):
-    return {k: v for k, v in m.items() if not k.startswith("_")}
-
-
 def make_tables(torch, synth, cfg, dev):
     tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[cfg.dtype]
     tables = []

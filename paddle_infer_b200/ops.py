@@ -26,12 +26,12 @@ from __future__ import annotations
 import ctypes as C
 import sys
 from collections import namedtuple
-from typing import List, Optional, Sequence, Union
+from typing import List, Optional, Sequence
 
 import numpy as np
 
 from . import _lib as B
-from .device import Arr, DeviceArray, PinnedArray, as_arr, empty, is_torch, stream_of
+from .device import Arr, DeviceArray, PinnedArray, as_arr, empty
 
 _FLOATS = ("float32", "float16", "bfloat16")
 _IDS = {"int64": B.I64, "int32": B.I32}
