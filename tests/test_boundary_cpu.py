@@ -162,3 +162,17 @@ def test_package_core_does_not_import_torch():
             "assert 'torch' not in sys.modules; print('ok')" % ROOT)
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+
+
+def test_paddle_shim_compiles_against_the_reference_headers():
+    """The PD_BUILD_OP shim is a syntax-only compile against the reference's own paddle/extension.h
+    closure (paddle_shim/check_syntax.sh).  /root/reference exists on the authoring box only."""
+    import shutil
+    import subprocess
+    ref = os.environ.get("CTRFE_REFERENCE_ROOT", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "paddle")) or shutil.which("g++") is None:
+        pytest.skip("reference tree or g++ not present")
+    script = os.path.join(ROOT, "paddle_infer_b200", "paddle_shim", "check_syntax.sh")
+    r = subprocess.run(["sh", script], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "syntax OK" in r.stdout
