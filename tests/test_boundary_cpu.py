@@ -176,3 +176,33 @@ def test_paddle_shim_compiles_against_the_reference_headers():
     r = subprocess.run(["sh", script], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "syntax OK" in r.stdout
+
+
+def test_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference` (the CPU arm the driver times beside the GPU arm) runs without a GPU,
+    loads neither CUDA nor libctrfe.so, and prints exactly one JSON line with the contract's keys.
+    Run on cfg1 so it takes seconds; the driver runs it on the default workload."""
+    import json
+    import subprocess
+    import sys
+    code = ("import atexit, sys, runpy\n"
+            "def _maps():\n"
+            "    print('LOADED_CTRFE' if 'libctrfe' in open('/proc/self/maps').read() else 'NO_CTRFE', file=sys.stderr)\n"
+            "atexit.register(_maps)\n"
+            "sys.argv = ['bench.py', '--impl', 'reference', '--workload', 'cfg1', '--steps', '3', '--warmup', '1']\n"
+            "runpy.run_path(%r, run_name='__main__')\n" % os.path.join(ROOT, "bench.py"))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, lines
+    line = json.loads(lines[0])
+    for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert k in line, k
+    assert line["impl"] == "reference" and line["value"] > 0 and line["vs_baseline"] is None
+    assert line["e2e"]["value"] == line["value"] and line["e2e"]["h2d_bytes_per_step"] == 0
+    cb = line["cpu_baseline"]
+    assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["value"] == line["value"] and cb["sample"]
+    assert "workload" in line["config"] and "model" not in line["config"]
+    assert "NO_CTRFE" in r.stderr
